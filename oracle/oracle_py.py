@@ -1,0 +1,240 @@
+"""ctypes view of oracle/liboracle.so (the CPU restatement) and a runner for
+oracle/_ref/lda (the unmodified reference binary).  TEST INFRASTRUCTURE: import
+this only from tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+HERE = Path(__file__).resolve().parent
+LIB_PATH = HERE / "liboracle.so"
+REF_BIN = HERE / "_ref" / "lda"
+
+_i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+_i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+_f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+
+
+class Settings(C.Structure):
+    _fields_ = [("var_max_iter", C.c_int), ("var_converged", C.c_float),
+                ("em_max_iter", C.c_int), ("em_converged", C.c_float),
+                ("estimate_alpha", C.c_int)]
+
+
+def build(force: bool = False) -> None:
+    """make liboracle.so, and _ref/lda when the reference sources are present."""
+    if force or not LIB_PATH.exists():
+        subprocess.run(["make", "-C", str(HERE), "liboracle.so"], check=True, capture_output=True)
+    if os.path.isdir("/root/reference/oni-ml/oni-lda-c") and (force or not REF_BIN.exists()):
+        subprocess.run(["make", "-C", str(HERE), "ref"], check=True, capture_output=True)
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    build()
+    L = C.CDLL(str(LIB_PATH))
+    L.oracle_log_sum.restype = C.c_double
+    L.oracle_log_sum.argtypes = [C.c_double, C.c_double]
+    for f in (L.oracle_digamma, L.oracle_trigamma):
+        f.restype = C.c_double
+        f.argtypes = [C.c_double]
+    L.oracle_mt_seed.argtypes = [C.c_ulong]
+    L.oracle_mt_next.restype = C.c_ulong
+    L.oracle_myrand.restype = C.c_double
+    L.oracle_read_settings.argtypes = [C.c_char_p, C.POINTER(Settings)]
+    L.oracle_read_dat.argtypes = [C.c_char_p, C.POINTER(C.POINTER(C.c_int64)), C.POINTER(C.POINTER(C.c_int32)),
+                                  C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.POINTER(C.c_int32)),
+                                  C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
+    L.oracle_free.argtypes = [C.c_void_p]
+    L.oracle_opt_alpha.restype = C.c_double
+    L.oracle_opt_alpha.argtypes = [C.c_double, C.c_int, C.c_int]
+    L.oracle_lda_mle.argtypes = [C.c_int, C.c_int, _f64p, _f64p, _f64p]
+    L.oracle_random_init.argtypes = [C.c_int, C.c_int, _f64p]
+    L.oracle_seeded_init.argtypes = [C.c_int, C.c_int, C.c_int64, _i64p, _i32p, _i32p, _f64p]
+    L.oracle_save_model.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_double, _f64p]
+    L.oracle_load_model_dims.argtypes = [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.oracle_load_model.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_double), _f64p]
+    L.oracle_save_gamma.argtypes = [C.c_char_p, C.c_int64, C.c_int, _f64p]
+    L.oracle_compute_likelihood.restype = C.c_double
+    L.oracle_compute_likelihood.argtypes = [C.c_int, _i32p, _i32p, C.c_int, C.c_int, C.c_double, _f64p, _f64p, _f64p]
+    L.oracle_lda_inference.restype = C.c_double
+    L.oracle_lda_inference.argtypes = [C.c_int, _i32p, _i32p, C.c_int, C.c_int, C.c_int, C.c_double, _f64p,
+                                       C.c_int, C.c_float, _f64p, _f64p, C.POINTER(C.c_int)]
+    L.oracle_e_step.restype = C.c_double
+    L.oracle_e_step.argtypes = [C.c_int64, _i64p, _i32p, _i32p, _i32p, C.c_int, C.c_int, C.c_double, _f64p,
+                                C.c_int, C.c_float, C.c_int, C.c_int, _f64p, _f64p, _f64p,
+                                C.POINTER(C.c_double), C.POINTER(C.c_int), C.c_void_p]
+    L.oracle_run_em.argtypes = [C.c_int64, _i64p, _i32p, _i32p, _i32p, C.c_int, C.c_int, C.POINTER(C.c_double),
+                                _f64p, C.POINTER(Settings), C.c_int, _f64p, _f64p, _f64p, C.POINTER(C.c_int)]
+    L.oracle_infer.argtypes = [C.c_int64, _i64p, _i32p, _i32p, _i32p, C.c_int, C.c_int, C.c_double, _f64p,
+                               C.POINTER(Settings), _f64p, _f64p]
+    L.oracle_set_threads.argtypes = [C.c_int]
+    L.oracle_theta_from_gamma.argtypes = [C.c_int64, C.c_int, _f64p, _f64p]
+    L.oracle_phi_from_logbeta.argtypes = [C.c_int, C.c_int, _f64p, _f64p]
+    L.oracle_score.argtypes = [C.c_int64, _i32p, _i32p, C.c_int64, C.c_int, C.c_int, _f64p, _f64p, _f64p]
+    L.oracle_score_flow_min.argtypes = [C.c_int64, _i32p, _i32p, _i32p, _i32p, C.c_int64, C.c_int, C.c_int,
+                                        _f64p, _f64p, _f64p]
+    L.oracle_topk.restype = C.c_int64
+    L.oracle_topk.argtypes = [C.c_int64, _f64p, C.c_double, C.c_int64, _i64p, _f64p]
+    _lib = L
+    return L
+
+
+def settings(var_max_iter=20, var_converged=1e-6, em_max_iter=20, em_converged=1e-6, estimate_alpha=1) -> Settings:
+    return Settings(var_max_iter, var_converged, em_max_iter, em_converged, estimate_alpha)
+
+
+def read_settings(path) -> Settings:
+    s = Settings()
+    if lib().oracle_read_settings(str(path).encode(), C.byref(s)) != 0:
+        raise FileNotFoundError(path)
+    return s
+
+
+def read_dat(path):
+    """-> (offsets int64[D+1], words int32[N], counts int32[N], totals int32[D], V)"""
+    L = lib()
+    po, pw, pc, pt = (C.POINTER(C.c_int64)(), C.POINTER(C.c_int32)(), C.POINTER(C.c_int32)(), C.POINTER(C.c_int32)())
+    D, N, V = C.c_int64(), C.c_int64(), C.c_int32()
+    if L.oracle_read_dat(str(path).encode(), C.byref(po), C.byref(pw), C.byref(pc), C.byref(pt),
+                         C.byref(D), C.byref(N), C.byref(V)) != 0:
+        raise FileNotFoundError(path)
+    off = np.ctypeslib.as_array(po, (D.value + 1,)).copy()
+    words = np.ctypeslib.as_array(pw, (max(N.value, 1),))[:N.value].copy()
+    counts = np.ctypeslib.as_array(pc, (max(N.value, 1),))[:N.value].copy()
+    totals = np.ctypeslib.as_array(pt, (max(D.value, 1),))[:D.value].copy()
+    for p in (po, pw, pc, pt):
+        L.oracle_free(C.cast(p, C.c_void_p))
+    return off, words, counts, totals, V.value
+
+
+def totals_of(offsets, counts):
+    # int32 wrap-around matches the reference's int `total` (lda.h:27)
+    cs = np.concatenate([[0], np.cumsum(counts.astype(np.int64))])
+    return (cs[offsets[1:]] - cs[offsets[:-1]]).astype(np.int32)
+
+
+def load_model(root):
+    L = lib()
+    K, V = C.c_int(), C.c_int()
+    if L.oracle_load_model_dims(str(root).encode(), C.byref(K), C.byref(V)) != 0:
+        raise FileNotFoundError(root)
+    lb = np.zeros((K.value, V.value))
+    a = C.c_double()
+    rc = L.oracle_load_model(str(root).encode(), K.value, V.value, C.byref(a), lb)
+    if rc != 0:
+        raise RuntimeError(f"oracle_load_model rc={rc}")
+    return a.value, lb
+
+
+def save_model(root, alpha, log_beta):
+    K, V = log_beta.shape
+    if lib().oracle_save_model(str(root).encode(), K, V, float(alpha), np.ascontiguousarray(log_beta)) != 0:
+        raise OSError(root)
+
+
+def run_em(offsets, words, counts, V, alpha, log_beta, st: Settings, nproc=1):
+    """-> dict(alpha, log_beta, gamma, lik, conv)"""
+    L = lib()
+    D = len(offsets) - 1
+    K = log_beta.shape[0]
+    lb = np.ascontiguousarray(log_beta, dtype=np.float64).copy()
+    gamma = np.zeros((D, K))
+    cap = st.em_max_iter + 2
+    lik, conv = np.zeros(cap), np.zeros(cap)
+    a = C.c_double(alpha)
+    n = C.c_int()
+    totals = totals_of(offsets, counts)
+    L.oracle_run_em(D, offsets, words, counts, totals, K, V, C.byref(a), lb, C.byref(st), nproc,
+                    gamma, lik, conv, C.byref(n))
+    return dict(alpha=a.value, log_beta=lb, gamma=gamma, lik=lik[:n.value].copy(), conv=conv[:n.value].copy())
+
+
+def e_step(offsets, words, counts, V, alpha, log_beta, var_max_iter, var_converged):
+    """One full E-step pass -> dict(gamma, class_word[K][V], class_total, alpha_ss, lik, doc_lik)"""
+    L = lib()
+    D = len(offsets) - 1
+    K = log_beta.shape[0]
+    gamma = np.zeros((D, K))
+    cw, ct = np.zeros((K, V)), np.zeros(K)
+    a_ss, nd = C.c_double(0.0), C.c_int(0)
+    doc_lik = np.zeros(D)
+    totals = totals_of(offsets, counts)
+    lik = L.oracle_e_step(D, offsets, words, counts, totals, K, V, alpha, np.ascontiguousarray(log_beta),
+                          var_max_iter, var_converged, 0, 1, gamma, cw, ct, C.byref(a_ss), C.byref(nd),
+                          doc_lik.ctypes.data_as(C.c_void_p))
+    return dict(gamma=gamma, class_word=cw, class_total=ct, alpha_ss=a_ss.value, num_docs=nd.value,
+                lik=lik, doc_lik=doc_lik)
+
+
+def infer(offsets, words, counts, V, alpha, log_beta, st: Settings):
+    L = lib()
+    D = len(offsets) - 1
+    K = log_beta.shape[0]
+    gamma, doc_lik = np.zeros((D, K)), np.zeros(D)
+    L.oracle_infer(D, offsets, words, counts, totals_of(offsets, counts), K, V, alpha,
+                   np.ascontiguousarray(log_beta), C.byref(st), gamma, doc_lik)
+    return gamma, doc_lik
+
+
+def theta_from_gamma(gamma):
+    D, K = gamma.shape
+    out = np.zeros_like(gamma)
+    lib().oracle_theta_from_gamma(D, K, np.ascontiguousarray(gamma), out)
+    return out
+
+
+def phi_from_logbeta(log_beta):
+    K, V = log_beta.shape
+    out = np.zeros((V, K))
+    lib().oracle_phi_from_logbeta(K, V, np.ascontiguousarray(log_beta), out)
+    return out
+
+
+def score(doc, word, theta, phi_wk, threads=1):
+    L = lib()
+    L.oracle_set_threads(threads)
+    out = np.zeros(len(doc))
+    L.oracle_score(len(doc), doc, word, theta.shape[0], phi_wk.shape[0], theta.shape[1], theta, phi_wk, out)
+    return out
+
+
+def score_flow_min(sdoc, sword, ddoc, dword, theta, phi_wk, threads=1):
+    L = lib()
+    L.oracle_set_threads(threads)
+    out = np.zeros(len(sdoc))
+    L.oracle_score_flow_min(len(sdoc), sdoc, sword, ddoc, dword, theta.shape[0], phi_wk.shape[0],
+                            theta.shape[1], theta, phi_wk, out)
+    return out
+
+
+def topk(scores, threshold, k):
+    n = len(scores)
+    idx, sc = np.zeros(max(n, 1), np.int64), np.zeros(max(n, 1))
+    m = lib().oracle_topk(n, np.ascontiguousarray(scores), threshold, k, idx, sc)
+    return idx[:m].copy(), sc[:m].copy()
+
+
+def run_ref(args, cwd, seed=None, nproc=1, timeout=3600):
+    """Run the unmodified reference binary (oracle/_ref/lda).  Returns CompletedProcess."""
+    if not REF_BIN.exists():
+        raise FileNotFoundError(f"{REF_BIN} not built (needs /root/reference; run make -C oracle ref)")
+    env = dict(os.environ)
+    if seed is not None:
+        env["ONI_ORACLE_SEED"] = str(seed)
+    if nproc > 1:
+        env["ONI_MPI_STUB_NP"] = str(nproc)
+    else:
+        env.pop("ONI_MPI_STUB_NP", None)
+    return subprocess.run([str(REF_BIN)] + [str(a) for a in args], cwd=str(cwd), env=env,
+                          capture_output=True, text=True, timeout=timeout, check=True)
