@@ -1,0 +1,439 @@
+#!/usr/bin/env python
+"""bench.py - LDA EM tokens/s per EM iteration (BASELINE.json's metric) on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A "step" is one EM iteration (E-step + sufficient-statistics sum + M-step) over
+the synthetic one-day netflow corpus of BASELINE.json configs[1]: 1M IP
+documents, ~100M tokens, V = 100k flow words, K = 20, lda-c's default settings.
+At N > 1 (torchrun, one rank per GPU) every rank holds its own 1M-document
+shard (weak scaling) and the packed statistics are summed with one NCCL
+all-reduce per iteration.
+
+Prints ONE JSON line (see the contract in the task statement).  `value` is
+measured with the corpus resident in HBM; `e2e` runs the same iterations through
+the C ABI with HOST buffers (corpus + model copied host->device and model + gamma
+device->host inside every timed step).  `roofline` is for the E-step kernel;
+`cpu_baseline` is the unmodified reference lda-c (oracle/_ref/lda) timed on this
+box's host cores on a bounded sample of the same corpus.
+
+PyTorch is plumbing here (synthetic-data generation on the GPU, pinned host
+buffers, torch.distributed/NCCL); every timed kernel is libonilda's.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+WORKLOADS = {
+    # BASELINE.json configs[1]
+    "netflow-1M-docs-100M-tokens-V100k-K20": dict(num_docs=1_000_000, mean_tokens=100, num_terms=100_000,
+                                                  num_topics=20, seed=20161102),
+}
+DEFAULT_WORKLOAD = "netflow-1M-docs-100M-tokens-V100k-K20"
+ALPHA0 = 2.5                     # OniLDACWrapper.scala:83
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# ----------------------------------------------------------------- synthetic corpus (torch on the GPU: plumbing)
+
+def gen_corpus_torch(num_docs, mean_tokens, num_terms, num_topics, seed, device, doc_seed=None, max_tokens=20_000,
+                     hub_frac=0.001, hub_tokens=20_000, dup_frac=0.01, chunk_docs=50_000):
+    """Same recipe as open-network-insight_b200/corpusgen.py (LDA generative model, lognormal
+    document sizes, hub documents, a few duplicated word ids), run on the GPU so that the
+    100M-token corpus takes seconds.  Returns host CSR arrays."""
+    import torch
+    cg = importlib.import_module("open-network-insight_b200.corpusgen")
+    D, V, K = num_docs, num_terms, num_topics
+    torch.manual_seed(seed)
+    beta = torch._standard_gamma(torch.full((K, V), 0.05, dtype=torch.float64, device=device)).clamp_min(1e-300)
+    cdf_w = torch.cumsum(beta / beta.sum(1, keepdim=True), 1)
+    cdf_w = cdf_w / cdf_w[:, -1:]
+    cdf_w_flat = (cdf_w + torch.arange(K, device=device, dtype=torch.float64)[:, None]).reshape(-1)
+    torch.manual_seed(seed if doc_seed is None else doc_seed)
+    sigma = 0.8
+    mu = np.log(mean_tokens) - 0.5 * sigma * sigma
+    n_tok = torch.exp(mu + sigma * torch.randn(D, device=device, dtype=torch.float64)).clamp(5, max_tokens).long()
+    n_hub = int(round(hub_frac * D))
+    if n_hub:
+        hubs = torch.randperm(D, device=device)[:n_hub]
+        n_tok[hubs] = torch.randint(hub_tokens // 4, hub_tokens + 1, (n_hub,), device=device)
+    lens, words, counts = [], [], []
+    for lo in range(0, D, chunk_docs):
+        hi = min(D, lo + chunk_docs)
+        nd = hi - lo
+        theta = torch._standard_gamma(torch.full((nd, K), 0.1, dtype=torch.float64, device=device)).clamp_min(1e-300)
+        cdf_t = torch.cumsum(theta / theta.sum(1, keepdim=True), 1)
+        cdf_t = cdf_t / cdf_t[:, -1:]
+        rows = torch.arange(nd, device=device, dtype=torch.float64)
+        cdf_t_flat = (cdf_t + rows[:, None]).reshape(-1)
+        doc = torch.repeat_interleave(torch.arange(nd, device=device), n_tok[lo:hi])
+        T = doc.numel()
+        z = torch.searchsorted(cdf_t_flat, torch.rand(T, device=device, dtype=torch.float64) + doc.double(), right=True)
+        z = (z - doc * K).clamp_(0, K - 1)
+        w = torch.searchsorted(cdf_w_flat, torch.rand(T, device=device, dtype=torch.float64) + z.double(), right=True)
+        w = (w - z * V).clamp_(0, V - 1)
+        key, cnt = torch.unique(doc * V + w, return_counts=True)
+        lens.append(torch.bincount(key // V, minlength=nd).cpu().numpy())
+        words.append((key % V).to(torch.int32).cpu().numpy())
+        counts.append(cnt.to(torch.int32).cpu().numpy())
+        del theta, cdf_t, cdf_t_flat, doc, z, w, key, cnt
+    lens = np.concatenate(lens).astype(np.int64)
+    words = np.concatenate(words)
+    counts = np.concatenate(counts)
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    rng = np.random.default_rng(seed + 17)
+    offsets, words, counts = cg.add_duplicates(offsets, words, counts, rng, dup_frac)
+    return offsets, words, counts
+
+
+# ----------------------------------------------------------------- clocks
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        self.thread.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------- reference lda-c on the host cores
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def time_reference(oni, corpus, model0, n_docs, n_iters, nproc, workdir):
+    """Runs the UNMODIFIED reference (oracle/_ref/lda; fork-based MPI stand-in with `nproc`
+    ranks) for n_iters EM iterations on the first n_docs documents, from the same start
+    model, and returns the per-iteration seconds read off its own progress lines."""
+    ref_bin = ROOT / "oracle" / "_ref" / "lda"
+    if not ref_bin.exists():
+        return None
+    work = Path(workdir)
+    corpus.save_dat(work / "sample.dat", 0, n_docs)
+    model0.save(work / "000")
+    (work / "settings.txt").write_text(
+        f"var max iter 20\nvar convergence 1e-6\nem max iter {n_iters - 1}\nem convergence 1e-6\nalpha estimate\n")
+    env = dict(os.environ, ONI_MPI_STUB_NP=str(nproc), ONI_MPI_STUB_MAXCOUNT=str(max(model0.num_terms, 1 << 16)))
+    cmd = ["stdbuf", "-oL", str(ref_bin), "est", str(ALPHA0), str(model0.num_topics), "settings.txt", str(nproc),
+           "sample.dat", "000", "out"]
+    starts, ends = [], []
+    p = subprocess.Popen(cmd, cwd=work, env=env, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+    for line in p.stdout:
+        now = time.perf_counter()
+        if line.startswith("**** em iteration"):
+            starts.append(now)
+        elif line.startswith("**** reducing likelihood"):
+            ends.append(now)
+    p.wait()
+    if p.returncode != 0 or not starts or len(ends) < len(starts):
+        return None
+    return [e - s for s, e in zip(starts, ends)]
+
+
+def reference_sample_docs(corpus_offsets, cores, target_seconds=8.0, nnz_per_core_second=120_000):
+    """Document prefix whose nnz gives roughly target_seconds per EM iteration on `cores` cores."""
+    want = int(cores * nnz_per_core_second * target_seconds)
+    n = int(np.searchsorted(corpus_offsets, want))
+    return max(min(n, len(corpus_offsets) - 1), 1)
+
+
+# ----------------------------------------------------------------- main
+
+def algorithmic_bytes(nnz, num_docs, K):
+    """B_EM = N(8 + 16K) + D(16 + 8K) per EM iteration."""
+    return nnz * (8 + 16 * K) + num_docs * (16 + 8 * K)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=18)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD)
+    ap.add_argument("--scale", type=float, default=1.0, help="development only: shrink the number of documents")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-scoring", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        log("warm-up raised to 3 (timing rules)")
+        args.warmup = 3
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference" and rank != 0:
+        return 0
+
+    import torch
+    oni = importlib.import_module("open-network-insight_b200")
+    cfg = dict(WORKLOADS[args.workload])
+    cfg["num_docs"] = max(1000, int(cfg["num_docs"] * args.scale))
+    K, V = cfg["num_topics"], cfg["num_terms"]
+
+    if not torch.cuda.is_available() or oni.device_count() < 1:
+        raise SystemExit("bench.py needs a CUDA device: libonilda has no CPU path")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1 and args.impl == "ours":
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+
+    t0 = time.time()
+    offsets, words, counts = gen_corpus_torch(device=device, doc_seed=cfg["seed"] + 1000 * rank, **cfg)
+    torch.cuda.empty_cache()
+    corpus = oni.Corpus.from_csr(offsets, words, counts, num_terms=V)
+    del words, counts
+    D, N, T = corpus.num_docs, corpus.nnz, corpus.tokens
+    log(f"[rank {rank}] corpus: D={D} N={N} T={T} V={corpus.num_terms} max_len={corpus.max_len} ({time.time() - t0:.1f}s)")
+    model0 = oni.Model.new(K, V)
+    model0.init_random(20161102)
+    model0.alpha = float(np.float32(ALPHA0))
+    settings = oni.Settings.default()
+    settings.em_max_iter = max(settings.em_max_iter, args.steps + args.warmup)
+
+    # ------------------------------------------------------------ reference arm
+    if args.impl == "reference":
+        cores = host_cores()
+        n_docs = reference_sample_docs(offsets, cores)
+        n_iters = args.steps + args.warmup
+        with tempfile.TemporaryDirectory() as td:
+            secs = time_reference(oni, corpus, model0, n_docs, n_iters, cores, td)
+        if secs is None:
+            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/lda missing or failed on this box"}))
+            return 0
+        timed = secs[args.warmup:] if len(secs) > args.warmup else secs
+        tok = int(np.asarray(corpus.csr()[2][:offsets[n_docs]], np.int64).sum())
+        val = tok / float(np.mean(timed))
+        sample = f"first {n_docs} docs ({int(offsets[n_docs])} nnz, {tok} tokens) of the workload, {len(timed)} timed EM iterations"
+        line = {"metric": "lda_em_tokens_per_sec_per_iter", "value": val, "unit": "tokens/s", "n_gpus": 0,
+                "steps": len(timed), "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(timed)),
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "impl": "reference",
+                "config": {"workload": args.workload, "sample": sample, "nnz_per_sec": offsets[n_docs] / float(np.mean(timed))},
+                "cpu_baseline": {"value": val, "unit": "tokens/s", "cores": cores, "kind": "reference", "sample": sample},
+                "e2e": {"value": val, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line, default=float))
+        return 0
+
+    # ------------------------------------------------------------ our arm: resident-in-HBM leg
+    em = oni.EM(corpus, model0, settings, device=local_rank)
+    ss_tensor = None
+    if dist is not None:
+        ptr, cnt = em.suffstats_device()
+
+        class _Buf:
+            __cuda_array_interface__ = {"shape": (cnt,), "typestr": "<f8", "data": (ptr, False), "version": 3}
+        ss_tensor = torch.as_tensor(_Buf(), device=device)
+
+    def em_step():
+        em.estep()
+        if dist is not None:
+            torch.cuda.synchronize()          # the library runs on its own stream
+            dist.all_reduce(ss_tensor)
+            torch.cuda.synchronize()
+        return em.mstep()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    liks = []
+    for _ in range(args.warmup):
+        liks.append(em_step()[0])
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    t_begin = time.perf_counter()
+    estep_ms, mstep_ms, launches = [], [], 0
+    for _ in range(args.steps):
+        liks.append(em_step()[0])
+        s = em.stats()
+        estep_ms.append(s["estep_ms"])
+        mstep_ms.append(s["mstep_ms"])
+        launches += s["launches"]
+    barrier()
+    elapsed = time.perf_counter() - t_begin
+    clocks = sampler.stop() if rank == 0 else None
+    if dist is not None:
+        t = torch.tensor([elapsed], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed = float(t.item())
+        tt = torch.tensor([float(T), float(N), float(D)], device=device, dtype=torch.float64)
+        dist.all_reduce(tt)
+        T_all, N_all, D_all = (int(x) for x in tt.tolist())
+    else:
+        T_all, N_all, D_all = T, N, D
+    ms_per_step = 1e3 * elapsed / args.steps
+    value = T_all / (elapsed / args.steps)
+    sweeps = em.stats(with_sweeps=True)["sweeps"]
+
+    # ------------------------------------------------------------ e2e leg: host buffers through the C ABI
+    corpus.pin()
+    g_host = torch.empty((D, K), dtype=torch.float64, pin_memory=True).numpy()
+    cur = oni.Model.new(K, V)
+    cur.log_beta[...] = model0.log_beta
+    cur.alpha = model0.alpha
+    lib = oni.lib()
+
+    def e2e_step():
+        em.reload(cur)                        # H2D: CSR words+counts+totals, model
+        em.estep()
+        if dist is not None:
+            torch.cuda.synchronize()
+            dist.all_reduce(ss_tensor)
+            torch.cuda.synchronize()
+        out = em.mstep()                      # D2H: likelihood + statistics tail
+        oni._check(lib.onilda_em_get_model(em._h, cur._h))      # D2H: new model
+        oni._check(lib.onilda_em_get_gamma(em._h, g_host))      # D2H: gamma
+        return out
+
+    # the EM loop state must follow the iterations, not restart: reload() resets it, so carry it here
+    e2e_liks = []
+    for _ in range(args.warmup):
+        e2e_liks.append(e2e_step()[0])
+    barrier()
+    t_begin = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_liks.append(e2e_step()[0])
+    barrier()
+    e2e_elapsed = time.perf_counter() - t_begin
+    if dist is not None:
+        t = torch.tensor([e2e_elapsed], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_elapsed = float(t.item())
+    h2d = N * 8 + D * 4 + K * V * 8
+    d2h = K * V * 8 + D * K * 8 + 32 + 4
+    e2e = {"value": T_all / (e2e_elapsed / args.steps), "unit": "tokens/s", "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * e2e_elapsed / args.steps}
+
+    if rank != 0:
+        if dist is not None:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
+
+    # ------------------------------------------------------------ roofline of the E-step kernel
+    peaks_path = ROOT / "MEASURED_PEAKS.json"
+    if peaks_path.exists():
+        peak, peak_src = json.loads(peaks_path.read_text())["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    b_em = algorithmic_bytes(N, D, K)
+    achieved = b_em / (np.mean(estep_ms) * 1e-3) / 1e9
+    traffic = None
+    prof = ROOT / "profiles" / "estep_traffic.json"
+    if prof.exists():
+        try:
+            traffic = json.loads(prof.read_text()).get("dram_bytes_per_launch")
+        except ValueError:
+            traffic = None
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic, "kernel": "estep_kernel<4,5>", "algorithmic_bytes_per_launch": b_em,
+                "kernel_ms": float(np.mean(estep_ms)), "peak_source": peak_src,
+                "note": "fp64-transcendental bound, not HBM bound: see DESIGN.md"}
+
+    # ------------------------------------------------------------ CPU baseline (reference lda-c on this box)
+    cpu_baseline = None
+    if not args.no_cpu_baseline:
+        cores = host_cores()
+        n_docs = reference_sample_docs(offsets, cores, target_seconds=6.0)
+        with tempfile.TemporaryDirectory() as td:
+            secs = time_reference(oni, corpus, model0, n_docs, 3, cores, td)
+        if secs:
+            tok = int(np.asarray(corpus.csr()[2][:offsets[n_docs]], np.int64).sum())
+            cpu_baseline = {"value": tok / float(np.mean(secs)), "unit": "tokens/s", "cores": cores, "kind": "reference",
+                            "sample": f"unmodified lda-c (oracle/_ref/lda, {cores} forked ranks), first {n_docs} docs "
+                                      f"({int(offsets[n_docs])} nnz, {tok} tokens), 3 EM iterations from the same start model",
+                            "nnz_per_sec": int(offsets[n_docs]) / float(np.mean(secs)),
+                            "sec_per_iter": [round(x, 3) for x in secs]}
+        else:
+            cpu_baseline = {"value": None, "unit": "tokens/s", "cores": cores, "kind": "reference",
+                            "sample": "oracle/_ref/lda missing or failed on this box"}
+
+    line = {"metric": "lda_em_tokens_per_sec_per_iter", "value": value, "unit": "tokens/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload, "num_docs": D_all, "nnz": N_all, "tokens": T_all, "num_terms": V,
+                       "num_topics": K, "docs_per_gpu": D, "settings": "var 20/1e-6, em 20/1e-6, alpha estimate",
+                       "start": "random (MT19937 seed 20161102), alpha 2.5",
+                       "l2": "inputs larger than L2 (CSR 0.7 GB + phi scratch 14 GB per GPU)",
+                       "parallelism": f"dp{world} over documents", "scale": args.scale},
+            "nnz_per_sec": N_all / (elapsed / args.steps),
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
+            "cpu_baseline": cpu_baseline,
+            "em": {"estep_ms": [round(x, 3) for x in estep_ms], "mstep_ms_mean": float(np.mean(mstep_ms)),
+                   "likelihood_first": liks[0], "likelihood_last": liks[-1], "sweeps_last_iter": int(sweeps),
+                   "e2e_likelihood_last": e2e_liks[-1]}}
+    print(json.dumps(line, default=float))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,232 @@
+/*
+ * onilda.h - C ABI of libonilda.so: the B200 (sm_100a) implementation of ONI's
+ * machine-learning hot path - the oni-lda-c variational-EM LDA and the post-LDA
+ * suspicious-connects scoring.
+ *
+ * The reference has NO foreign-function interface for this path: oni-ml shells
+ * out to the `lda` program and reads its text files back
+ * (oni-ml/src/main/scala/org/opennetworkinsight/OniLDACWrapper.scala:83-104).
+ * The drop-in boundary is therefore (1) the `lda est|inf` program built on this
+ * library (open-network-insight_b200/host/lda_main.c) and (2) the entry points
+ * below, which are what a cgo/JNI/ctypes binding of that path would bind.  Each
+ * declaration cites the reference function it replaces (paths relative to the
+ * reference checkout).  INTEGRATION.md shows the bindings.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative ONILDA_E* code otherwise;
+ *     onilda_last_error() gives the message for the calling thread.
+ *   - plain pointers and sizes only.  Unless a name ends in _device, pointers
+ *     are HOST pointers owned by the caller; the library owns all device memory.
+ *   - log_beta is row-major [K][V] (topic-major, the reference's
+ *     lda_model.log_prob_w, lda.h:40-47); gamma is [D][K]; theta is [D][K];
+ *     phi is word-major [V][K] (the transposed table the Scala scorer builds,
+ *     OniLDACWrapper.scala:178-195).
+ *   - a handle is bound to one CUDA device; calls on one handle are not
+ *     thread-safe, distinct handles are independent.
+ *   - there is no CPU fallback: every compute entry point fails with
+ *     ONILDA_ECUDA when no CUDA device is usable.
+ */
+#ifndef ONILDA_H
+#define ONILDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ONILDA_OK 0
+#define ONILDA_EINVAL (-1)   /* bad argument */
+#define ONILDA_EIO (-2)      /* file could not be opened / written */
+#define ONILDA_ECUDA (-3)    /* CUDA runtime error or no device */
+#define ONILDA_ENOMEM (-4)   /* host or device allocation failed */
+#define ONILDA_ENAN (-5)     /* NaN likelihood (the reference asserts: lda-inference.c:78) */
+
+typedef struct onilda_corpus onilda_corpus;
+typedef struct onilda_model onilda_model;
+typedef struct onilda_em onilda_em;
+typedef struct onilda_scorer onilda_scorer;
+
+/* The five values of the settings file.  Types as in the reference: both
+ * tolerances are `float` (lda-inference.h:10, lda-estimate.h:21). */
+typedef struct {
+    int var_max_iter;     /* -1 = until converged (lda-inference.c:46-47) */
+    float var_converged;
+    int em_max_iter;
+    float em_converged;
+    int estimate_alpha;   /* 1 unless the file says "alpha fixed" */
+} onilda_settings;
+
+const char* onilda_last_error(void);
+const char* onilda_version(void);
+/* Number of usable CUDA devices (0 when none; never fails). */
+int onilda_device_count(void);
+
+/* ------------------------------------------------------------------ settings
+ * replaces read_settings (oni-ml/oni-lda-c/lda-estimate.c:331-350): five literal
+ * lines "var max iter %d" / "var convergence %f" / "em max iter %d" /
+ * "em convergence %f" / "alpha %s". */
+int onilda_settings_read(const char* path, onilda_settings* out);
+
+/* -------------------------------------------------------------------- corpus
+ * replaces read_data / document / corpus (lda-data.c:22-59, lda.h:23-37).
+ * Token-based, newline-agnostic "%10d" then "%10d:%10d" per entry; duplicates
+ * kept in file order; num_terms = max word id + 1; per-document total is the
+ * int sum of counts.  The result is a CSR corpus on the host. */
+int onilda_corpus_from_dat(const char* path, onilda_corpus** out);
+/* Same corpus from caller CSR arrays (copied).  num_terms <= 0 derives it from
+ * the data as read_data does; a larger value is kept (vocabulary with unseen ids). */
+int onilda_corpus_from_csr(const int64_t* offsets, const int32_t* words, const int32_t* counts,
+                           int64_t num_docs, int32_t num_terms, onilda_corpus** out);
+int onilda_corpus_dims(const onilda_corpus* c, int64_t* num_docs, int64_t* nnz, int32_t* num_terms,
+                       int64_t* tokens, int32_t* max_len);
+/* Borrowed views of the CSR arrays (valid until onilda_corpus_free). */
+int onilda_corpus_csr(const onilda_corpus* c, const int64_t** offsets, const int32_t** words,
+                      const int32_t** counts, const int32_t** totals);
+/* Writes documents [doc_begin, doc_end) in the `.dat` form OniLDACWrapper.createModel
+ * emits (OniLDACWrapper.scala:146-168): "<#entries> <word>:<count> ...\n" per document. */
+int onilda_corpus_save_dat(const onilda_corpus* c, int64_t doc_begin, int64_t doc_end, const char* path);
+/* Page-locks the corpus' host arrays (cudaHostRegister) so that uploads run at
+ * full PCIe rate and asynchronously.  Optional; undone by onilda_corpus_free. */
+int onilda_corpus_pin(onilda_corpus* c);
+void onilda_corpus_free(onilda_corpus* c);
+
+/* --------------------------------------------------------------------- model
+ * replaces lda_model / new_lda_model / free_lda_model (lda.h:40-47,
+ * lda-model.c:151-185).  new: alpha = 1.0, log_beta = 0. */
+int onilda_model_new(int num_topics, int num_terms, onilda_model** out);
+int onilda_model_dims(const onilda_model* m, int* num_topics, int* num_terms);
+double onilda_model_alpha(const onilda_model* m);
+int onilda_model_set_alpha(onilda_model* m, double alpha);
+/* Borrowed host pointer to log_beta [K][V]. */
+double* onilda_model_log_beta(onilda_model* m);
+/* replaces seedMT + random_initialize_ss + lda_mle(.,.,0) (cokus.c:52-145,
+ * lda-model.c:104-117, lda-estimate.c:155-162): same MT19937 stream, so a given
+ * seed gives the reference's 000.beta.  alpha is left untouched (the caller
+ * sets INITIAL_ALPHA). */
+int onilda_model_init_random(onilda_model* m, uint32_t seed);
+/* replaces corpus_initialize_ss + lda_mle (lda-model.c:120-144, lda-estimate.c:147-154). */
+int onilda_model_init_seeded(onilda_model* m, const onilda_corpus* c, uint32_t seed);
+/* replaces load_lda_model (lda-model.c:220-251): alpha and every beta value are
+ * parsed as FLOAT and widened, as the reference does. */
+int onilda_model_load(const char* model_root, onilda_model** out);
+/* replaces save_lda_model (lda-model.c:193-217): <root>.beta (" %5.10f" per
+ * value, one line per topic) and <root>.other. Byte-identical formatting. */
+int onilda_model_save(const onilda_model* m, const char* model_root);
+void onilda_model_free(onilda_model* m);
+/* replaces save_gamma (lda-estimate.c:88-104): "%5.10f" then " %5.10f". */
+int onilda_gamma_save(const char* path, const double* gamma, int64_t num_docs, int num_topics);
+
+/* ------------------------------------------------------------------------ EM
+ * One handle = run_em's state for the documents [doc_begin, doc_end) of `c` on
+ * one device (lda-estimate.c:112-321).  The reference shards round-robin over
+ * MPI ranks (:201); here a shard is a contiguous document range, one per GPU.
+ * device < 0 selects the current device.  The start model is copied. */
+int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64_t doc_end, const onilda_model* start,
+                     const onilda_settings* settings, int device, onilda_em** out);
+void onilda_em_destroy(onilda_em* em);
+
+/* E-step over the shard: lda_inference + compute_likelihood + doc_e_step for
+ * every document (lda-inference.c:27-127, lda-estimate.c:28-60, 198-209), in
+ * sm_100a kernels.  Leaves the shard's sufficient statistics on the device. */
+int onilda_em_estep(onilda_em* em);
+/* The shard's sufficient statistics as ONE packed fp64 device buffer, the
+ * operand of the per-iteration sum over shards (replaces the 2K+3 MPI_Allreduce
+ * calls at lda-estimate.c:211-252):
+ *    [ class_word, word-major, V x kpad | likelihood | alpha_suffstats | num_docs | 0 ]
+ * Single shard: skip this.  Several shards: all-reduce (SUM) `count` doubles in
+ * place across the shards' buffers (NCCL or onilda_em_allreduce_peer), then
+ * call onilda_em_mstep on every shard. */
+int onilda_em_suffstats_device(onilda_em* em, double** dev_ptr, int64_t* count);
+/* M-step + convergence bookkeeping: lda_mle (lda-model.c:27-54, log-normalise
+ * on device; opt_alpha's scalar Newton on the host, lda-alpha.c:42-68), then
+ * converged = (old - new)/old, VAR_MAX_ITER doubling when negative, and the
+ * loop test of lda-estimate.c:186 / 260-262.
+ *   likelihood, converged : the values the reference prints to likelihood.dat
+ *   keep_going            : 1 while run_em's while-condition still holds */
+int onilda_em_mstep(onilda_em* em, double* likelihood, double* converged, int* keep_going);
+/* Re-sends the shard's CSR arrays (from the corpus given to onilda_em_create,
+ * which must still be alive) and `m` (alpha + log_beta) host -> device, and
+ * resets the EM loop state: the handle is then as freshly created, without
+ * reallocating.  With it one call sequence reload -> iterate -> get_model /
+ * get_gamma is a stateless EM step on HOST buffers. */
+int onilda_em_reload(onilda_em* em, const onilda_model* m);
+/* estep + mstep for a single shard. */
+int onilda_em_iterate(onilda_em* em, double* likelihood, double* converged, int* keep_going);
+/* In-process sum of the packed statistics of `n` handles (one per device, same
+ * process) over NVLink peer memory; each device reduces its slice of the buffer
+ * from all peers and writes the sum back to every peer. */
+int onilda_em_allreduce_peer(onilda_em** ems, int n);
+
+/* Current model (after the last mstep) and the variational gamma of the
+ * shard's documents from the last estep ([doc_end-doc_begin][K], row i is
+ * document doc_begin+i: line i of final.gamma). */
+int onilda_em_get_model(onilda_em* em, onilda_model* out);
+int onilda_em_get_gamma(onilda_em* em, double* gamma_out);
+/* Per-document likelihood bound from the last estep ([doc_end-doc_begin]). */
+int onilda_em_get_doc_likelihood(onilda_em* em, double* out);
+/* Counters of the last estep: kernel time in ms (CUDA events on the handle's
+ * stream), number of kernel launches issued by the last estep+mstep pair, and
+ * total variational sweeps summed over documents. */
+int onilda_em_stats(onilda_em* em, double* estep_ms, double* mstep_ms, int64_t* launches, int64_t* sweeps);
+/* The handle's stream as a cudaStream_t (for callers that enqueue their own
+ * collective on it). */
+void* onilda_em_stream(onilda_em* em);
+
+/* run_em end to end on `ndev` devices of this process (lda-estimate.c:112-321):
+ * writes <dir>/000.{beta,other}, likelihood.dat ("%10.10f\t%5.5e\n" per
+ * iteration), final.{beta,other,gamma}.  start is "random", "seeded" or a model
+ * root, as argv[7] of `lda est`.  seed feeds the MT19937 of the two inits. */
+int onilda_run_em(const char* start, const char* directory, const onilda_corpus* c, int num_topics,
+                  double initial_alpha, const onilda_settings* settings, int ndev, uint32_t seed);
+
+/* ----------------------------------------------------------------- inference
+ * replaces infer (lda-estimate.c:358-388): per-document lda_inference with a
+ * fixed model.  gamma_out [D][K], likelihood_out [D]. */
+int onilda_infer(const onilda_model* m, const onilda_corpus* c, const onilda_settings* settings, int device,
+                 double* gamma_out, double* likelihood_out);
+/* The file-writing form `lda inf` uses: <name>-lda-lhood.dat ("%5.5f\n") and
+ * <name>-gamma.dat. */
+int onilda_infer_files(const char* model_root, const char* name, const onilda_corpus* c,
+                       const onilda_settings* settings, int device);
+
+/* ------------------------------------------------------------------- scoring
+ * replaces OniLDACWrapper.getDocumentResults / getTopicDocument
+ * (OniLDACWrapper.scala:132-144, 170-176): theta = gamma / sum, zeros if sum <= 0. */
+int onilda_theta_from_gamma(const double* gamma, int64_t num_docs, int num_topics, int device, double* theta_out);
+/* replaces getWordProbabilitesFromTopicLine + getWordToProbPerTopicMap
+ * (OniLDACWrapper.scala:121-130, 178-195): phi[w][k] = exp(lb[k][w]) / sum_w exp(lb[k][w]). */
+int onilda_phi_from_log_beta(const double* log_beta, int num_topics, int num_terms, int device, double* phi_out);
+
+/* replaces the broadcast maps of SuspiciousConnectsScoreFunction
+ * (SuspiciousConnectsScoreFunction.scala:7-9): tables resident on one device. */
+int onilda_scorer_create(const double* theta, int64_t num_docs, const double* phi, int32_t num_terms,
+                         int num_topics, int device, onilda_scorer** out);
+void onilda_scorer_destroy(onilda_scorer* s);
+/* replaces SuspiciousConnectsScoreFunction.score (:11-23) for n (doc, word)
+ * pairs: sum_k theta[doc][k] * phi[word][k], products rounded then summed left
+ * to right as the Scala zip/map/sum does.  An id outside the table (e.g. -1)
+ * takes the uniform 1/K row.  Host buffers; copies are pipelined inside. */
+int onilda_score(onilda_scorer* s, const int32_t* doc, const int32_t* word, int64_t n, double* out);
+/* replaces FlowPostLDA.score x2 + minimumScore (netflow/FlowPostLDA.scala:94-125):
+ * min(score(sdoc, sword), score(ddoc, dword)) per flow event. */
+int onilda_score_flow_min(onilda_scorer* s, const int32_t* sdoc, const int32_t* sword, const int32_t* ddoc,
+                          const int32_t* dword, int64_t n, double* out);
+/* replaces filter(score <= threshold) + orderBy/takeOrdered(k)
+ * (netflow/FlowPostLDA.scala:79-80, dns/DNSPostLDA.scala:49-70,
+ * utilities/DataFrameUtils.scala:21-38): ascending, ties by event index,
+ * k == -1 keeps all.  idx_out/score_out need room for min(k, n) (n when k == -1). */
+int onilda_topk(onilda_scorer* s, const double* score, int64_t n, double threshold, int64_t k,
+                int64_t* idx_out, double* score_out, int64_t* n_out);
+/* Fused form for data already on the device (no host copies): scores the
+ * events, keeps the running top-k, returns only the k rows.  Device pointers. */
+int onilda_score_flow_topk_device(onilda_scorer* s, const int32_t* sdoc_dev, const int32_t* sword_dev,
+                                  const int32_t* ddoc_dev, const int32_t* dword_dev, int64_t n,
+                                  double threshold, int64_t k, int64_t* idx_out, double* score_out,
+                                  int64_t* n_out, double* score_dev_out /* may be NULL */);
+int onilda_scorer_stats(onilda_scorer* s, double* kernel_ms, int64_t* launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ONILDA_H */

@@ -98,31 +98,39 @@ def generate(num_docs, mean_tokens, num_terms, num_topics, seed, max_tokens=20_0
     counts = np.concatenate(counts_out)
     offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
 
-    # duplicate word ids inside a document: split one entry with count >= 2 into two
-    n_dup = int(round(dup_frac * num_docs))
-    if n_dup > 0:
-        docs = np.sort(rng.choice(num_docs, n_dup, replace=False))
-        ins_pos, ins_word, ins_cnt, ins_doc = [], [], [], []
-        for d in docs:
-            a, b = offsets[d], offsets[d + 1]
-            cand = np.nonzero(counts[a:b] >= 2)[0]
-            if len(cand) == 0:
-                continue
-            e = a + cand[rng.integers(len(cand))]
-            take = counts[e] // 2
-            counts[e] -= take
-            ins_pos.append(b)              # appended at the end of the doc (file order is kept)
-            ins_word.append(words[e])
-            ins_cnt.append(take)
-            ins_doc.append(d)
-        if ins_pos:
-            ins_pos = np.asarray(ins_pos)
-            words = np.insert(words, ins_pos, np.asarray(ins_word, np.int32))
-            counts = np.insert(counts, ins_pos, np.asarray(ins_cnt, np.int32))
-            add = np.zeros(num_docs + 1, np.int64)
-            np.add.at(add, np.asarray(ins_doc) + 1, 1)
-            offsets = offsets + np.cumsum(add)
+    offsets, words, counts = add_duplicates(offsets, words, counts, rng, dup_frac)
     return Corpus(offsets, words.astype(np.int32), counts.astype(np.int32), int(words.max()) + 1 if len(words) else 0)
+
+
+def add_duplicates(offsets, words, counts, rng, dup_frac):
+    """Duplicate word ids inside a document: in dup_frac of the documents one entry with
+    count >= 2 is split in two, the second half appended at the end of the document."""
+    num_docs = len(offsets) - 1
+    n_dup = int(round(dup_frac * num_docs))
+    if n_dup <= 0:
+        return offsets, words, counts
+    docs = np.sort(rng.choice(num_docs, n_dup, replace=False))
+    ins_pos, ins_word, ins_cnt, ins_doc = [], [], [], []
+    for d in docs:
+        a, b = offsets[d], offsets[d + 1]
+        cand = np.nonzero(counts[a:b] >= 2)[0]
+        if len(cand) == 0:
+            continue
+        e = a + cand[rng.integers(len(cand))]
+        take = counts[e] // 2
+        counts[e] -= take
+        ins_pos.append(b)
+        ins_word.append(words[e])
+        ins_cnt.append(take)
+        ins_doc.append(d)
+    if ins_pos:
+        ins_pos = np.asarray(ins_pos)
+        words = np.insert(words, ins_pos, np.asarray(ins_word, np.int32))
+        counts = np.insert(counts, ins_pos, np.asarray(ins_cnt, np.int32))
+        add = np.zeros(num_docs + 1, np.int64)
+        np.add.at(add, np.asarray(ins_doc) + 1, 1)
+        offsets = offsets + np.cumsum(add)
+    return offsets, words, counts
 
 
 def generate_named(name: str, scale: float = 1.0, **overrides) -> Corpus:

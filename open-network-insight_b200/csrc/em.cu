@@ -1,0 +1,449 @@
+// EM handle: run_em's state for one shard of documents on one device
+// (reference: oni-ml/oni-lda-c/lda-estimate.c:112-321) and `infer` (:358-388).
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <vector>
+
+#include "kernels.cuh"
+
+using namespace onilda;
+
+struct onilda_em {
+    const onilda_corpus* corpus;   // borrowed (for onilda_em_reload)
+    int device;
+    int sm_count;
+    cudaStream_t stream;
+    cudaEvent_t ev0, ev1, ev2, ev3;
+    // shard
+    int64_t doc_begin, doc_end, num_docs, nnz;
+    int K, V;
+    TopicLayout lay;
+    onilda_settings settings;
+    int var_max_iter;           // mutated as at lda-estimate.c:261
+    double alpha;
+    // EM loop state (lda-estimate.c:172-186)
+    int iteration;
+    double likelihood_old;
+    double converged;
+    // device buffers
+    int64_t* d_offsets;
+    int32_t *d_words, *d_counts, *d_totals, *d_order;
+    double *d_log_beta_wk, *d_beta_scaled, *d_lbmax;
+    double* d_ss;               // [V*kpad + SS_TAIL]
+    double* d_class_total;      // [kpad]
+    double* d_partial;
+    double* d_phi;              // [nnz][kpad]
+    double *d_gamma, *d_doc_lik, *d_doc_ass;
+    int32_t* d_doc_sweeps;
+    unsigned long long* d_queue;
+    int* d_error;
+    double* d_kv;               // [K][V] staging for import / export
+    // stats
+    double estep_ms, mstep_ms;
+    int64_t launches;
+    int64_t sweeps;
+    int estep_done;
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev;
+    bool ok;
+    explicit DeviceGuard(int dev) : prev(-1), ok(true)
+    {
+        if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+        if (dev != prev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+template <typename T>
+int dev_alloc(T** p, size_t n)
+{
+    *p = nullptr;
+    cudaError_t e = cudaMalloc((void**)p, sizeof(T) * (n ? n : 1));
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return onilda_fail(ONILDA_ENOMEM, "cudaMalloc of %zu bytes failed: %s", sizeof(T) * n, cudaGetErrorString(e));
+    }
+    return ONILDA_OK;
+}
+
+// documents by decreasing length (stable counting sort): longest first for the bundle queue
+void order_by_length(const int64_t* offsets, int64_t D, int32_t max_len, std::vector<int32_t>& order)
+{
+    std::vector<int64_t> start((size_t)max_len + 2, 0);
+    for (int64_t d = 0; d < D; d++) start[(size_t)(max_len - (offsets[d + 1] - offsets[d])) + 1]++;
+    for (size_t i = 1; i < start.size(); i++) start[i] += start[i - 1];
+    order.resize((size_t)D);
+    for (int64_t d = 0; d < D; d++) order[(size_t)start[(size_t)(max_len - (offsets[d + 1] - offsets[d]))]++] = (int32_t)d;
+}
+
+int upload_model(onilda_em* em, const double* log_beta_kv)
+{
+    const size_t kv = (size_t)em->K * em->V;
+    if (kv == 0) return ONILDA_OK;
+    ONILDA_CUDA(cudaMemcpyAsync(em->d_kv, log_beta_kv, sizeof(double) * kv, cudaMemcpyHostToDevice, em->stream));
+    int l = 0;
+    int rc = launch_tables_from_log_beta(em->d_kv, em->K, em->V, em->lay, em->d_log_beta_wk, em->d_beta_scaled,
+                                         em->d_lbmax, em->stream, &l);
+    em->launches += l;
+    return rc;
+}
+
+}  // namespace
+
+extern "C" int onilda_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+extern "C" int onilda_corpus_pin(onilda_corpus* c)
+{
+    if (!c) return onilda_fail(ONILDA_EINVAL, "corpus_pin: null corpus");
+    if (c->pinned) return ONILDA_OK;
+    if (onilda_device_count() == 0) return onilda_fail(ONILDA_ECUDA, "corpus_pin: no CUDA device is usable");
+    cudaError_t e = cudaSuccess;
+    if (c->nnz > 0) {
+        e = cudaHostRegister(c->words, sizeof(int32_t) * (size_t)c->nnz, cudaHostRegisterDefault);
+        if (e == cudaSuccess) {
+            e = cudaHostRegister(c->counts, sizeof(int32_t) * (size_t)c->nnz, cudaHostRegisterDefault);
+            if (e != cudaSuccess) cudaHostUnregister(c->words);
+        }
+    }
+    if (e != cudaSuccess) { cudaGetLastError(); return onilda_fail(ONILDA_ECUDA, "corpus_pin: %s", cudaGetErrorString(e)); }
+    c->pinned = 1;
+    return ONILDA_OK;
+}
+
+extern "C" void onilda_corpus_unpin(onilda_corpus* c)
+{
+    if (!c || !c->pinned) return;
+    if (c->nnz > 0) { cudaHostUnregister(c->words); cudaHostUnregister(c->counts); }
+    cudaGetLastError();
+    c->pinned = 0;
+}
+
+extern "C" void onilda_em_destroy(onilda_em* em)
+{
+    if (!em) return;
+    DeviceGuard g(em->device);
+    cudaFree(em->d_offsets); cudaFree(em->d_words); cudaFree(em->d_counts); cudaFree(em->d_totals); cudaFree(em->d_order);
+    cudaFree(em->d_log_beta_wk); cudaFree(em->d_beta_scaled); cudaFree(em->d_lbmax); cudaFree(em->d_ss);
+    cudaFree(em->d_class_total); cudaFree(em->d_partial); cudaFree(em->d_phi); cudaFree(em->d_gamma);
+    cudaFree(em->d_doc_lik); cudaFree(em->d_doc_ass); cudaFree(em->d_doc_sweeps); cudaFree(em->d_queue);
+    cudaFree(em->d_error); cudaFree(em->d_kv);
+    if (em->ev0) cudaEventDestroy(em->ev0);
+    if (em->ev1) cudaEventDestroy(em->ev1);
+    if (em->ev2) cudaEventDestroy(em->ev2);
+    if (em->ev3) cudaEventDestroy(em->ev3);
+    if (em->stream) cudaStreamDestroy(em->stream);
+    free(em);
+}
+
+extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64_t doc_end, const onilda_model* start,
+                                const onilda_settings* settings, int device, onilda_em** out)
+{
+    if (!c || !start || !settings || !out) return onilda_fail(ONILDA_EINVAL, "em_create: null argument");
+    if (doc_begin < 0 || doc_end > c->num_docs || doc_begin > doc_end)
+        return onilda_fail(ONILDA_EINVAL, "em_create: shard [%lld, %lld) outside the corpus of %lld documents",
+                           (long long)doc_begin, (long long)doc_end, (long long)c->num_docs);
+    if (c->num_terms > start->num_terms)
+        return onilda_fail(ONILDA_EINVAL, "em_create: corpus has %d terms, model only %d", c->num_terms, start->num_terms);
+    TopicLayout lay;
+    if (!choose_layout(start->num_topics, &lay))
+        return onilda_fail(ONILDA_EINVAL, "em_create: %d topics unsupported (1..256)", start->num_topics);
+    if (onilda_device_count() == 0)
+        return onilda_fail(ONILDA_ECUDA, "em_create: no CUDA device is usable and this library has no CPU path");
+    if (device < 0) ONILDA_CUDA(cudaGetDevice(&device));
+    DeviceGuard guard(device);
+    if (!guard.ok) return onilda_fail(ONILDA_ECUDA, "em_create: cannot select device %d", device);
+
+    onilda_em* em = (onilda_em*)calloc(1, sizeof *em);
+    if (!em) return onilda_fail(ONILDA_ENOMEM, "em_create: out of host memory");
+    em->corpus = c;
+    em->device = device;
+    em->doc_begin = doc_begin;
+    em->doc_end = doc_end;
+    em->num_docs = doc_end - doc_begin;
+    em->nnz = c->offsets[doc_end] - c->offsets[doc_begin];
+    em->K = start->num_topics;
+    em->V = start->num_terms;
+    em->lay = lay;
+    em->settings = *settings;
+    em->var_max_iter = settings->var_max_iter;
+    em->alpha = start->alpha;
+    em->iteration = 0;
+    em->likelihood_old = 0;
+    em->converged = 1;
+
+    int rc = ONILDA_OK;
+#define TRY(x) do { rc = (x); if (rc != ONILDA_OK) { onilda_em_destroy(em); return rc; } } while (0)
+#define TRYCUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { rc = onilda_fail(ONILDA_ECUDA, "%s: %s", #x, cudaGetErrorString(e_)); onilda_em_destroy(em); return rc; } } while (0)
+    TRYCUDA(cudaDeviceGetAttribute(&em->sm_count, cudaDevAttrMultiProcessorCount, device));
+    TRYCUDA(cudaStreamCreateWithFlags(&em->stream, cudaStreamNonBlocking));
+    TRYCUDA(cudaEventCreate(&em->ev0));
+    TRYCUDA(cudaEventCreate(&em->ev1));
+    TRYCUDA(cudaEventCreate(&em->ev2));
+    TRYCUDA(cudaEventCreate(&em->ev3));
+
+    const int64_t D = em->num_docs, N = em->nnz;
+    const size_t table = (size_t)em->V * lay.kpad;
+    TRY(dev_alloc(&em->d_offsets, (size_t)D + 1));
+    TRY(dev_alloc(&em->d_words, (size_t)N));
+    TRY(dev_alloc(&em->d_counts, (size_t)N));
+    TRY(dev_alloc(&em->d_totals, (size_t)D));
+    TRY(dev_alloc(&em->d_order, (size_t)D));
+    TRY(dev_alloc(&em->d_log_beta_wk, table));
+    TRY(dev_alloc(&em->d_beta_scaled, table));
+    TRY(dev_alloc(&em->d_lbmax, (size_t)em->V));
+    TRY(dev_alloc(&em->d_ss, table + SS_TAIL));
+    TRY(dev_alloc(&em->d_class_total, (size_t)lay.kpad));
+    TRY(dev_alloc(&em->d_partial, (size_t)mstep_partial_doubles(em->V, lay, D)));
+    TRY(dev_alloc(&em->d_phi, (size_t)N * lay.kpad));
+    TRY(dev_alloc(&em->d_gamma, (size_t)D * em->K));
+    TRY(dev_alloc(&em->d_doc_lik, (size_t)D));
+    TRY(dev_alloc(&em->d_doc_ass, (size_t)D));
+    TRY(dev_alloc(&em->d_doc_sweeps, (size_t)D));
+    TRY(dev_alloc(&em->d_queue, 1));
+    TRY(dev_alloc(&em->d_error, 1));
+    TRY(dev_alloc(&em->d_kv, (size_t)em->K * em->V));
+
+    // shard-local CSR
+    {
+        std::vector<int64_t> off((size_t)D + 1);
+        const int64_t base = c->offsets[doc_begin];
+        int32_t max_len = 0;
+        for (int64_t d = 0; d <= D; d++) off[(size_t)d] = c->offsets[doc_begin + d] - base;
+        for (int64_t d = 0; d < D; d++) {
+            int64_t len = off[(size_t)d + 1] - off[(size_t)d];
+            if (len > max_len) max_len = (int32_t)len;
+        }
+        std::vector<int32_t> order;
+        order_by_length(off.data(), D, max_len, order);
+        TRYCUDA(cudaMemcpyAsync(em->d_offsets, off.data(), sizeof(int64_t) * (size_t)(D + 1), cudaMemcpyHostToDevice, em->stream));
+        if (D > 0) {
+            TRYCUDA(cudaMemcpyAsync(em->d_totals, c->totals + doc_begin, sizeof(int32_t) * (size_t)D, cudaMemcpyHostToDevice, em->stream));
+            TRYCUDA(cudaMemcpyAsync(em->d_order, order.data(), sizeof(int32_t) * (size_t)D, cudaMemcpyHostToDevice, em->stream));
+        }
+        if (N > 0) {
+            TRYCUDA(cudaMemcpyAsync(em->d_words, c->words + base, sizeof(int32_t) * (size_t)N, cudaMemcpyHostToDevice, em->stream));
+            TRYCUDA(cudaMemcpyAsync(em->d_counts, c->counts + base, sizeof(int32_t) * (size_t)N, cudaMemcpyHostToDevice, em->stream));
+        }
+        TRYCUDA(cudaStreamSynchronize(em->stream));   // the host vectors go out of scope
+    }
+    TRYCUDA(cudaMemsetAsync(em->d_ss, 0, sizeof(double) * (table + SS_TAIL), em->stream));
+    TRYCUDA(cudaMemsetAsync(em->d_error, 0, sizeof(int), em->stream));
+    TRY(upload_model(em, start->log_beta));
+    TRYCUDA(cudaStreamSynchronize(em->stream));
+#undef TRY
+#undef TRYCUDA
+    *out = em;
+    return ONILDA_OK;
+}
+
+extern "C" int onilda_em_reload(onilda_em* em, const onilda_model* m)
+{
+    if (!em || !m) return onilda_fail(ONILDA_EINVAL, "em_reload: null argument");
+    if (m->num_topics != em->K || m->num_terms != em->V)
+        return onilda_fail(ONILDA_EINVAL, "em_reload: model is %d x %d, handle is %d x %d", m->num_topics, m->num_terms, em->K, em->V);
+    DeviceGuard g(em->device);
+    const onilda_corpus* c = em->corpus;
+    const int64_t base = c->offsets[em->doc_begin];
+    if (em->nnz > 0) {
+        ONILDA_CUDA(cudaMemcpyAsync(em->d_words, c->words + base, sizeof(int32_t) * (size_t)em->nnz, cudaMemcpyHostToDevice, em->stream));
+        ONILDA_CUDA(cudaMemcpyAsync(em->d_counts, c->counts + base, sizeof(int32_t) * (size_t)em->nnz, cudaMemcpyHostToDevice, em->stream));
+    }
+    if (em->num_docs > 0)
+        ONILDA_CUDA(cudaMemcpyAsync(em->d_totals, c->totals + em->doc_begin, sizeof(int32_t) * (size_t)em->num_docs, cudaMemcpyHostToDevice, em->stream));
+    int rc = upload_model(em, m->log_beta);
+    if (rc != ONILDA_OK) return rc;
+    em->alpha = m->alpha;
+    em->var_max_iter = em->settings.var_max_iter;
+    em->iteration = 0;
+    em->likelihood_old = 0;
+    em->converged = 1;
+    em->estep_done = 0;
+    return ONILDA_OK;
+}
+
+static int run_estep(onilda_em* em, bool accumulate)
+{
+    const size_t table = (size_t)em->V * em->lay.kpad;
+    int l = 0;
+    ONILDA_CUDA(cudaEventRecord(em->ev0, em->stream));
+    if (accumulate) {
+        ONILDA_CUDA(cudaMemsetAsync(em->d_ss, 0, sizeof(double) * (table + SS_TAIL), em->stream));   // zero_initialize_ss
+    }
+    EStepArgs a;
+    a.offsets = em->d_offsets; a.words = em->d_words; a.counts = em->d_counts; a.totals = em->d_totals;
+    a.order = em->d_order; a.num_docs = em->num_docs;
+    a.beta_scaled = em->d_beta_scaled; a.lbmax = em->d_lbmax; a.num_topics = em->K;
+    a.alpha = em->alpha;
+    a.lik_const = lgamma(em->alpha * em->K) - em->K * lgamma(em->alpha);
+    a.var_max_iter = em->var_max_iter;
+    a.var_converged = (double)em->settings.var_converged;
+    a.phi = em->d_phi; a.gamma = em->d_gamma; a.doc_lik = em->d_doc_lik; a.doc_alpha_ss = em->d_doc_ass;
+    a.doc_sweeps = em->d_doc_sweeps;
+    a.class_word = accumulate ? em->d_ss : nullptr;
+    a.queue = em->d_queue; a.error_flag = em->d_error;
+    int rc = launch_estep(em->lay, a, em->sm_count, em->stream, &l);
+    if (rc != ONILDA_OK) return rc;
+    rc = launch_reduce_doc_stats(em->d_doc_lik, em->d_doc_ass, em->num_docs, em->d_partial, em->d_ss + table, em->stream, &l);
+    if (rc != ONILDA_OK) return rc;
+    ONILDA_CUDA(cudaEventRecord(em->ev1, em->stream));
+    em->launches = l;
+    em->estep_done = 1;
+    return ONILDA_OK;
+}
+
+extern "C" int onilda_em_estep(onilda_em* em)
+{
+    if (!em) return onilda_fail(ONILDA_EINVAL, "em_estep: null handle");
+    DeviceGuard g(em->device);
+    return run_estep(em, true);
+}
+
+extern "C" int onilda_em_suffstats_device(onilda_em* em, double** dev_ptr, int64_t* count)
+{
+    if (!em || !dev_ptr || !count) return onilda_fail(ONILDA_EINVAL, "em_suffstats_device: null argument");
+    *dev_ptr = em->d_ss;
+    *count = (int64_t)em->V * em->lay.kpad + SS_TAIL;
+    return ONILDA_OK;
+}
+
+extern "C" void* onilda_em_stream(onilda_em* em) { return em ? (void*)em->stream : nullptr; }
+
+extern "C" int onilda_em_mstep(onilda_em* em, double* likelihood, double* converged, int* keep_going)
+{
+    if (!em) return onilda_fail(ONILDA_EINVAL, "em_mstep: null handle");
+    if (!em->estep_done) return onilda_fail(ONILDA_EINVAL, "em_mstep: call onilda_em_estep first");
+    DeviceGuard g(em->device);
+    const size_t table = (size_t)em->V * em->lay.kpad;
+    int l = 0;
+    ONILDA_CUDA(cudaEventRecord(em->ev2, em->stream));
+    int rc = launch_mstep(em->d_ss, em->K, em->V, em->lay, em->d_partial, em->d_class_total, em->d_log_beta_wk,
+                          em->d_beta_scaled, em->d_lbmax, em->stream, &l);
+    if (rc != ONILDA_OK) return rc;
+    double tail[SS_TAIL];
+    int err = 0;
+    ONILDA_CUDA(cudaMemcpyAsync(tail, em->d_ss + table, sizeof tail, cudaMemcpyDeviceToHost, em->stream));
+    ONILDA_CUDA(cudaMemcpyAsync(&err, em->d_error, sizeof err, cudaMemcpyDeviceToHost, em->stream));
+    ONILDA_CUDA(cudaEventRecord(em->ev3, em->stream));
+    ONILDA_CUDA(cudaStreamSynchronize(em->stream));
+    em->launches += l;
+    em->estep_done = 0;
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, em->ev0, em->ev1) == cudaSuccess) em->estep_ms = ms;
+    if (cudaEventElapsedTime(&ms, em->ev2, em->ev3) == cudaSuccess) em->mstep_ms = ms;
+    cudaGetLastError();
+    if (err || isnan(tail[SS_LIK])) return onilda_fail(ONILDA_ENAN, "NaN likelihood in the E-step (the reference asserts at lda-inference.c:78)");
+
+    const double lik = tail[SS_LIK];
+    // lda_mle's alpha part (lda-model.c:45-53): Newton on the host, D as int
+    if (em->settings.estimate_alpha == 1) em->alpha = onilda_opt_alpha(tail[SS_ALPHA], (int)llround(tail[SS_NDOCS]), em->K);
+    // lda-estimate.c:186-188, 260-262
+    em->iteration++;
+    em->converged = (em->likelihood_old - lik) / (em->likelihood_old);
+    if (em->converged < 0) em->var_max_iter = em->var_max_iter * 2;
+    em->likelihood_old = lik;
+    if (likelihood) *likelihood = lik;
+    if (converged) *converged = em->converged;
+    if (keep_going)
+        *keep_going = ((em->converged < 0) || (em->converged > em->settings.em_converged) || (em->iteration <= 2)) &&
+                      (em->iteration <= em->settings.em_max_iter);
+    return ONILDA_OK;
+}
+
+extern "C" int onilda_em_iterate(onilda_em* em, double* likelihood, double* converged, int* keep_going)
+{
+    int rc = onilda_em_estep(em);
+    if (rc != ONILDA_OK) return rc;
+    return onilda_em_mstep(em, likelihood, converged, keep_going);
+}
+
+extern "C" int onilda_em_get_model(onilda_em* em, onilda_model* out)
+{
+    if (!em || !out) return onilda_fail(ONILDA_EINVAL, "em_get_model: null argument");
+    if (out->num_topics != em->K || out->num_terms != em->V)
+        return onilda_fail(ONILDA_EINVAL, "em_get_model: model is %d x %d, handle is %d x %d", out->num_topics,
+                           out->num_terms, em->K, em->V);
+    DeviceGuard g(em->device);
+    int l = 0;
+    int rc = launch_export_log_beta(em->d_log_beta_wk, em->K, em->V, em->lay, em->d_kv, em->stream, &l);
+    if (rc != ONILDA_OK) return rc;
+    if ((size_t)em->K * em->V > 0)
+        ONILDA_CUDA(cudaMemcpyAsync(out->log_beta, em->d_kv, sizeof(double) * (size_t)em->K * em->V, cudaMemcpyDeviceToHost, em->stream));
+    ONILDA_CUDA(cudaStreamSynchronize(em->stream));
+    out->alpha = em->alpha;
+    return ONILDA_OK;
+}
+
+extern "C" int onilda_em_get_gamma(onilda_em* em, double* gamma_out)
+{
+    if (!em || (!gamma_out && em->num_docs > 0)) return onilda_fail(ONILDA_EINVAL, "em_get_gamma: null argument");
+    DeviceGuard g(em->device);
+    if (em->num_docs > 0)
+        ONILDA_CUDA(cudaMemcpyAsync(gamma_out, em->d_gamma, sizeof(double) * (size_t)em->num_docs * em->K, cudaMemcpyDeviceToHost, em->stream));
+    ONILDA_CUDA(cudaStreamSynchronize(em->stream));
+    return ONILDA_OK;
+}
+
+extern "C" int onilda_em_get_doc_likelihood(onilda_em* em, double* out)
+{
+    if (!em || (!out && em->num_docs > 0)) return onilda_fail(ONILDA_EINVAL, "em_get_doc_likelihood: null argument");
+    DeviceGuard g(em->device);
+    if (em->num_docs > 0)
+        ONILDA_CUDA(cudaMemcpyAsync(out, em->d_doc_lik, sizeof(double) * (size_t)em->num_docs, cudaMemcpyDeviceToHost, em->stream));
+    ONILDA_CUDA(cudaStreamSynchronize(em->stream));
+    return ONILDA_OK;
+}
+
+extern "C" int onilda_em_stats(onilda_em* em, double* estep_ms, double* mstep_ms, int64_t* launches, int64_t* sweeps)
+{
+    if (!em) return onilda_fail(ONILDA_EINVAL, "em_stats: null handle");
+    if (estep_ms) *estep_ms = em->estep_ms;
+    if (mstep_ms) *mstep_ms = em->mstep_ms;
+    if (launches) *launches = em->launches;
+    if (sweeps) {
+        DeviceGuard g(em->device);
+        std::vector<int32_t> sw((size_t)em->num_docs);
+        if (em->num_docs > 0)
+            ONILDA_CUDA(cudaMemcpy(sw.data(), em->d_doc_sweeps, sizeof(int32_t) * (size_t)em->num_docs, cudaMemcpyDeviceToHost));
+        int64_t tot = 0;
+        for (int32_t v : sw) tot += v;
+        *sweeps = tot;
+    }
+    return ONILDA_OK;
+}
+
+// infer (lda-estimate.c:358-388): E-step without sufficient statistics
+extern "C" int onilda_infer(const onilda_model* m, const onilda_corpus* c, const onilda_settings* settings, int device,
+                            double* gamma_out, double* likelihood_out)
+{
+    if (!m || !c || !settings) return onilda_fail(ONILDA_EINVAL, "infer: null argument");
+    onilda_em* em = nullptr;
+    int rc = onilda_em_create(c, 0, c->num_docs, m, settings, device, &em);
+    if (rc != ONILDA_OK) return rc;
+    {
+        DeviceGuard g(em->device);
+        rc = run_estep(em, false);
+        if (rc == ONILDA_OK) {
+            int err = 0;
+            cudaError_t e = cudaMemcpyAsync(&err, em->d_error, sizeof err, cudaMemcpyDeviceToHost, em->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(em->stream);
+            if (e != cudaSuccess) rc = onilda_fail(ONILDA_ECUDA, "infer: %s", cudaGetErrorString(e));
+            else if (err) rc = onilda_fail(ONILDA_ENAN, "NaN likelihood in inference (the reference asserts at lda-inference.c:78)");
+        }
+    }
+    if (rc == ONILDA_OK && gamma_out) rc = onilda_em_get_gamma(em, gamma_out);
+    if (rc == ONILDA_OK && likelihood_out) rc = onilda_em_get_doc_likelihood(em, likelihood_out);
+    onilda_em_destroy(em);
+    return rc;
+}

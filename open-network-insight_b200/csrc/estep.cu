@@ -1,0 +1,301 @@
+// E-step of variational-EM LDA on sm_100a: the per-document fixed point
+// (reference: oni-ml/oni-lda-c/lda-inference.c:27-85), its likelihood bound
+// (:93-127) and the sufficient-statistics update of doc_e_step
+// (lda-estimate.c:28-60), for every document of a shard in ONE launch.
+//
+// Mapping
+//   * a document is owned by a group of G lanes (G = 4 for K <= 32); lane j
+//     keeps topics k = t*G + j in registers (gamma, digamma(gamma), E).  A warp
+//     therefore advances 32/G documents at once.
+//   * words of a document are visited strictly in file order and gamma /
+//     digamma are refreshed after EVERY word (lda-inference.c:66-74): the
+//     Gauss-Seidel order of the reference is kept; parallelism is over topics
+//     and over documents only.
+//   * persistent warps pull "bundles" of 32/G consecutive documents of a
+//     length-sorted order from an atomic queue (longest first), so the groups
+//     of a warp run documents of near-equal length in lockstep and a warp that
+//     finishes early steals the next bundle.  Each document leaves the sweep
+//     loop on its own convergence test (in-kernel early exit).
+//
+// Arithmetic (all fp64).  With E_k = exp(psi(gamma_k) - shift) and the table
+// beta'[w][k] = exp(log_beta[k][w] - lbmax[w]) built once per EM iteration,
+//     phi_nk = E_k beta'_kw / s_n,   s_n = sum_j E_j beta'_jw
+// which is the reference's exp(psi_k + log_beta_kw - log_sum) without a
+// log_sum/exp per (word, topic): one log per WORD (log s_n) remains.  shift is
+// psi(alpha + total/K), the value every topic starts from, so E starts at 1 and
+// s_n can neither overflow nor vanish in practice; if it ever leaves
+// [1e-290, 1e290] that word is redone in log space (the reference's own form).
+// The bound needs log phi_nk = psi_k(at word n) + log_beta_kw - lse_n; inserting
+// it and gamma_k = alpha + sum_n c_n phi_nk into lda-inference.c:106-125 the
+// (psi_k - psi_sum) terms cancel exactly and
+//     L = lgamma(alpha K) - K lgamma(alpha) - lgamma(sum gamma) + sum_k lgamma(gamma_k)
+//         - sum_n sum_k c_n phi_nk psi_k(at word n) + sum_n c_n lse_n .
+// tests/ check it against the oracle to ~1e-13 relative per document.
+#include "device_math.cuh"
+#include "kernels.cuh"
+
+namespace onilda {
+
+template <int G>
+__device__ __forceinline__ double group_sum(double v, unsigned mask)
+{
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(mask, v, o);
+    return v;
+}
+
+template <int G>
+__device__ __forceinline__ double group_max(double v, unsigned mask)
+{
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(mask, v, o));
+    return v;
+}
+
+template <int TPL>
+struct WordItem {
+    int word;
+    double count;
+    double lbmax;
+    double beta[TPL];
+    double old_phi[TPL];
+};
+
+template <int G, int TPL>
+__global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long long num_bundles)
+{
+    constexpr int DPW = 32 / G;      // documents per warp
+    constexpr int KPAD = G * TPL;
+    const int lane = threadIdx.x & 31;
+    const int grp = lane / G;
+    const int j = lane % G;
+    const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (grp * G));
+    const int K = a.num_topics;
+    const double inv_K = 1.0 / K;
+    bool valid[TPL];
+#pragma unroll
+    for (int t = 0; t < TPL; t++) valid[t] = (t * G + j) < K;
+
+    for (;;) {
+        unsigned long long bundle = 0;
+        if (lane == 0) bundle = atomicAdd(a.queue, 1ull);
+        bundle = __shfl_sync(0xffffffffu, bundle, 0);
+        if (bundle >= num_bundles) break;
+
+        const int64_t slot = (int64_t)bundle * DPW + grp;
+        const bool has_doc = slot < a.num_docs;
+        const int64_t d = has_doc ? a.order[slot] : 0;
+        const int64_t beg = has_doc ? a.offsets[d] : 0;
+        const int len = has_doc ? (int)(a.offsets[d + 1] - beg) : 0;
+        const int total = has_doc ? a.totals[d] : 0;
+        int max_len = len;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) max_len = max(max_len, __shfl_xor_sync(0xffffffffu, max_len, o));
+
+        // posterior Dirichlet start (lda-inference.c:37-43)
+        const double gamma0 = a.alpha + (total / ((double)K));
+        const double shift = digamma(gamma0);
+        double gam[TPL], psi[TPL], E[TPL];
+#pragma unroll
+        for (int t = 0; t < TPL; t++) {
+            gam[t] = valid[t] ? gamma0 : 1.0;
+            psi[t] = valid[t] ? shift : 0.0;
+            E[t] = valid[t] ? 1.0 : 0.0;
+        }
+
+        double lik = 0.0, lik_old = 0.0, converged = 1.0;
+        int sweeps = 0;
+        bool active = has_doc && (converged > a.var_converged) && ((0 < a.var_max_iter) || (a.var_max_iter == -1));
+
+        const double* __restrict__ beta_scaled = a.beta_scaled;
+        double* __restrict__ phi = a.phi;
+
+        while (__any_sync(0xffffffffu, active)) {
+            if (active) sweeps++;
+            const bool first = (sweeps == 1);   // same for every active group of the warp
+            double acc_lse = 0.0, count_sum = 0.0;
+            double acc_psi[TPL];
+#pragma unroll
+            for (int t = 0; t < TPL; t++) acc_psi[t] = 0.0;
+
+            auto load_item = [&](int n, WordItem<TPL>& it) {
+                const bool on = active && n < len;
+                const int64_t e = beg + n;
+                it.word = on ? a.words[e] : 0;
+                it.count = on ? (double)a.counts[e] : 0.0;
+                it.lbmax = on ? a.lbmax[it.word] : 0.0;
+                const double* brow = beta_scaled + (int64_t)it.word * KPAD + j;
+                const double* prow = phi + e * KPAD + j;
+#pragma unroll
+                for (int t = 0; t < TPL; t++) {
+                    it.beta[t] = on ? __ldg(brow + t * G) : 0.0;
+                    it.old_phi[t] = first ? (valid[t] ? inv_K : 0.0) : (on ? prow[t * G] : 0.0);
+                }
+            };
+
+            WordItem<TPL> cur, nxt;
+            load_item(0, nxt);
+            for (int n = 0; n < max_len; n++) {
+                cur = nxt;
+                if (n + 1 < max_len) load_item(n + 1, nxt);
+                if (active && n < len) {
+                    double x[TPL], part = 0.0;
+#pragma unroll
+                    for (int t = 0; t < TPL; t++) {
+                        x[t] = E[t] * cur.beta[t];
+                        part += x[t];
+                    }
+                    double s = group_sum<G>(part, gmask);
+                    double lse;   // log sum_k exp(psi_k + log_beta_kw) minus shift
+                    if (s > 1e-290 && s < 1e290) {
+                        const double inv = 1.0 / s;
+#pragma unroll
+                        for (int t = 0; t < TPL; t++) x[t] *= inv;
+                        lse = cur.lbmax + log(s);
+                    } else {
+                        // rare: redo this word in log space, as the reference does (lda-inference.c:52-68)
+                        double av[TPL], m = -INFINITY;
+#pragma unroll
+                        for (int t = 0; t < TPL; t++) {
+                            av[t] = (valid[t] && cur.beta[t] > 0.0) ? (psi[t] - shift) + log(cur.beta[t]) : -INFINITY;
+                            m = fmax(m, av[t]);
+                        }
+                        m = group_max<G>(m, gmask);
+                        double ps = 0.0;
+#pragma unroll
+                        for (int t = 0; t < TPL; t++) {
+                            x[t] = (av[t] > -INFINITY) ? exp(av[t] - m) : 0.0;
+                            ps += x[t];
+                        }
+                        ps = group_sum<G>(ps, gmask);
+                        const double inv = 1.0 / ps;
+#pragma unroll
+                        for (int t = 0; t < TPL; t++) x[t] *= inv;
+                        lse = cur.lbmax + m + log(ps);
+                    }
+                    double* prow = phi + (beg + n) * KPAD + j;
+#pragma unroll
+                    for (int t = 0; t < TPL; t++) {
+                        const double p = x[t];
+                        prow[t * G] = p;
+                        acc_psi[t] = fma(cur.count * p, psi[t], acc_psi[t]);
+                        gam[t] = gam[t] + cur.count * (p - cur.old_phi[t]);
+                        const DigammaParts dp = digamma_rational(gam[t]);
+                        psi[t] = dp.rational + log(dp.y);
+                        E[t] = valid[t] ? exp(psi[t] - shift) : 0.0;
+                    }
+                    acc_lse = fma(cur.count, lse, acc_lse);
+                    count_sum += cur.count;
+                }
+            }
+
+            if (active) {
+                // likelihood bound of this sweep (lda-inference.c:93-127, see header)
+                double gs = 0.0, lg = 0.0, ap = 0.0;
+#pragma unroll
+                for (int t = 0; t < TPL; t++) {
+                    if (valid[t]) {
+                        gs += gam[t];
+                        lg += lgamma(gam[t]);
+                    }
+                    ap += acc_psi[t];
+                }
+                gs = group_sum<G>(gs, gmask);
+                lg = group_sum<G>(lg, gmask);
+                ap = group_sum<G>(ap, gmask);
+                lik = a.lik_const - lgamma(gs) + lg - ap + (acc_lse + shift * count_sum);
+                if (isnan(lik)) *a.error_flag = 1;   // the reference asserts here (lda-inference.c:78)
+                converged = (lik_old - lik) / lik_old;
+                lik_old = lik;
+                active = (converged > a.var_converged) && ((sweeps < a.var_max_iter) || (a.var_max_iter == -1));
+            }
+        }
+
+        if (has_doc) {
+            // doc_e_step (lda-estimate.c:40-46): alpha_suffstats += sum_k psi(gamma_k) - K psi(sum gamma)
+            double gs = 0.0, ps = 0.0;
+#pragma unroll
+            for (int t = 0; t < TPL; t++) {
+                if (valid[t]) {
+                    gs += gam[t];
+                    ps += psi[t];
+                    a.gamma[d * K + t * G + j] = gam[t];
+                }
+            }
+            gs = group_sum<G>(gs, gmask);
+            ps = group_sum<G>(ps, gmask);
+            if (j == 0) {
+                a.doc_lik[d] = lik;
+                a.doc_alpha_ss[d] = ps - K * digamma(gs);
+                a.doc_sweeps[d] = sweeps;
+            }
+            // class_word[k][w] += c_n phi_nk (lda-estimate.c:48-55); class_total is the column sum (mstep.cu)
+            if (a.class_word != nullptr) {
+                for (int n = 0; n < len; n++) {
+                    const int64_t e = beg + n;
+                    const int w = a.words[e];
+                    const double c = (double)a.counts[e];
+                    const double* prow = phi + e * KPAD + j;
+                    double* crow = a.class_word + (int64_t)w * KPAD + j;
+#pragma unroll
+                    for (int t = 0; t < TPL; t++) {
+                        if (valid[t]) {
+                            const double p = (sweeps == 0) ? inv_K : prow[t * G];
+                            atomicAdd(crow + t * G, c * p);
+                        }
+                    }
+                }
+            }
+        }
+    }
+}
+
+template <int G, int TPL>
+static int launch_one(const EStepArgs& args, int sm_count, cudaStream_t stream)
+{
+    constexpr int DPW = 32 / G;
+    const unsigned long long num_bundles = (unsigned long long)((args.num_docs + DPW - 1) / DPW);
+    if (num_bundles == 0) return ONILDA_OK;
+    int per_sm = 0;
+    ONILDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_kernel<G, TPL>, 128, 0));
+    if (per_sm < 1) per_sm = 1;
+    unsigned long long want = (num_bundles + 3) / 4;   // 4 warps per block
+    unsigned long long grid = (unsigned long long)sm_count * per_sm;
+    if (grid > want) grid = want;
+    estep_kernel<G, TPL><<<(unsigned)grid, 128, 0, stream>>>(args, num_bundles);
+    ONILDA_CUDA(cudaGetLastError());
+    return ONILDA_OK;
+}
+
+template <int G>
+static int launch_group(int tpl, const EStepArgs& args, int sm_count, cudaStream_t stream)
+{
+    switch (tpl) {
+        case 1: return launch_one<G, 1>(args, sm_count, stream);
+        case 2: return launch_one<G, 2>(args, sm_count, stream);
+        case 3: return launch_one<G, 3>(args, sm_count, stream);
+        case 4: return launch_one<G, 4>(args, sm_count, stream);
+        case 5: return launch_one<G, 5>(args, sm_count, stream);
+        case 6: return launch_one<G, 6>(args, sm_count, stream);
+        case 7: return launch_one<G, 7>(args, sm_count, stream);
+        case 8: return launch_one<G, 8>(args, sm_count, stream);
+    }
+    return onilda_fail(ONILDA_EINVAL, "unsupported topics-per-lane %d", tpl);
+}
+
+int launch_estep(const TopicLayout& lay, const EStepArgs& args, int sm_count, cudaStream_t stream, int* launches)
+{
+    ONILDA_CUDA(cudaMemsetAsync(args.queue, 0, sizeof(unsigned long long), stream));
+    int rc;
+    switch (lay.group) {
+        case 4: rc = launch_group<4>(lay.tpl, args, sm_count, stream); break;
+        case 8: rc = launch_group<8>(lay.tpl, args, sm_count, stream); break;
+        case 16: rc = launch_group<16>(lay.tpl, args, sm_count, stream); break;
+        case 32: rc = launch_group<32>(lay.tpl, args, sm_count, stream); break;
+        default: return onilda_fail(ONILDA_EINVAL, "unsupported lane group %d", lay.group);
+    }
+    if (rc == ONILDA_OK && launches && args.num_docs > 0) *launches += 1;
+    return rc;
+}
+
+}  // namespace onilda

@@ -1,0 +1,83 @@
+// Shared declarations between the CUDA translation units of libonilda.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "onilda_internal.h"
+
+#define ONILDA_CUDA(call)                                                                       \
+    do {                                                                                        \
+        cudaError_t e__ = (call);                                                               \
+        if (e__ != cudaSuccess)                                                                 \
+            return onilda_fail(ONILDA_ECUDA, "%s failed at %s:%d: %s", #call, __FILE__, __LINE__, \
+                               cudaGetErrorString(e__));                                        \
+    } while (0)
+
+namespace onilda {
+
+// Topic-to-lane layout.  A document is worked on by a group of G lanes of a
+// warp; lane j of the group owns topics k = t*G + j, t = 0..TPL-1, so that for
+// a fixed t the G lanes read G consecutive doubles of a word's topic row.
+// kpad = G*TPL >= K; padded topics carry beta' = 0 and stay inert.
+struct TopicLayout {
+    int group;   // G   in {4, 8, 16, 32}
+    int tpl;     // TPL in 1..8
+    int kpad;    // G*TPL
+};
+
+// K <= 32 -> 4 lanes, K <= 64 -> 8, K <= 128 -> 16, K <= 256 -> 32.
+inline bool choose_layout(int K, TopicLayout* out)
+{
+    if (K <= 0 || K > 256) return false;
+    int g = K <= 32 ? 4 : K <= 64 ? 8 : K <= 128 ? 16 : 32;
+    out->group = g;
+    out->tpl = (K + g - 1) / g;
+    out->kpad = out->group * out->tpl;
+    return true;
+}
+
+// Tail of the packed sufficient-statistics buffer, after the V*kpad table.
+enum { SS_LIK = 0, SS_ALPHA = 1, SS_NDOCS = 2, SS_SPARE = 3, SS_TAIL = 4 };
+
+struct EStepArgs {
+    // corpus shard, CSR, offsets local to the shard (offsets[0] == 0)
+    const int64_t* offsets;
+    const int32_t* words;
+    const int32_t* counts;
+    const int32_t* totals;
+    const int32_t* order;       // documents by decreasing length
+    int64_t num_docs;
+    // model tables, word-major [V][kpad]
+    const double* beta_scaled;  // exp(log_beta[w][k] - lbmax[w]); 0 in padding
+    const double* lbmax;        // [V] max_k log_beta[w][k]
+    int num_topics;
+    double alpha;
+    double lik_const;           // lgamma(alpha*K) - K*lgamma(alpha)
+    int var_max_iter;
+    double var_converged;       // the reference's float threshold, widened
+    // scratch and outputs
+    double* phi;                // [nnz][kpad]
+    double* gamma;              // [D][K]
+    double* doc_lik;            // [D]
+    double* doc_alpha_ss;       // [D]
+    int32_t* doc_sweeps;        // [D]
+    double* class_word;         // [V][kpad], accumulated with atomics; NULL: inference only
+    unsigned long long* queue;  // bundle counter
+    int* error_flag;            // set to 1 on a NaN likelihood
+};
+
+int launch_estep(const TopicLayout& lay, const EStepArgs& args, int sm_count, cudaStream_t stream, int* launches);
+
+// M-step and table kernels (mstep.cu)
+int launch_tables_from_log_beta(const double* log_beta_kv, int K, int V, const TopicLayout& lay, double* log_beta_wk,
+                                double* beta_scaled, double* lbmax, cudaStream_t stream, int* launches);
+int launch_reduce_doc_stats(const double* doc_lik, const double* doc_alpha_ss, int64_t num_docs, double* partial,
+                            double* ss_tail, cudaStream_t stream, int* launches);
+int launch_mstep(const double* class_word, int K, int V, const TopicLayout& lay, double* partial, double* class_total,
+                 double* log_beta_wk, double* beta_scaled, double* lbmax, cudaStream_t stream, int* launches);
+int launch_export_log_beta(const double* log_beta_wk, int K, int V, const TopicLayout& lay, double* log_beta_kv,
+                           cudaStream_t stream, int* launches);
+int mstep_partial_doubles(int V, const TopicLayout& lay, int64_t num_docs);
+
+}  // namespace onilda

@@ -1,0 +1,197 @@
+// M-step and model-table kernels (reference: lda_mle, oni-ml/oni-lda-c/lda-model.c:27-44;
+// the scalar alpha Newton stays on the host, lda-alpha.c:42-68).
+//
+// Device model layout: word-major [V][kpad] so one word's topic row is one
+// contiguous, sector-aligned vector for the E-step gather:
+//     log_beta_wk[w][k]   log p(w | k)                        (saved / exported)
+//     lbmax[w]            max_k log_beta_wk[w][k]
+//     beta_scaled[w][k]   exp(log_beta_wk[w][k] - lbmax[w])   (what the E-step reads)
+// Sufficient statistics class_word are kept in the same [V][kpad] layout and
+// class_total[k] is formed here as its column sum (fixed-order two-stage
+// reduction, so the result does not depend on atomics order).
+#include "kernels.cuh"
+
+namespace onilda {
+
+static constexpr int kColBlocks = 592;   // 4 x 148 SMs
+static constexpr int kColThreads = 256;
+
+// partial[b][k] = sum over this block's words of table[w][k]
+__global__ void __launch_bounds__(kColThreads) column_partial_kernel(const double* __restrict__ table, int V, int kpad,
+                                                                      double* __restrict__ partial)
+{
+    extern __shared__ double sh[];   // [rows_per_block][kpad]
+    const int rows = kColThreads / kpad;          // thread rows that each walk a strided set of words
+    const int k = threadIdx.x % kpad;
+    const int r = threadIdx.x / kpad;
+    double acc = 0.0;
+    if (r < rows) {
+        const int64_t chunk = ((int64_t)V + gridDim.x - 1) / gridDim.x;
+        const int64_t lo = chunk * blockIdx.x;
+        int64_t hi = lo + chunk;
+        if (hi > V) hi = V;
+        for (int64_t w = lo + r; w < hi; w += rows) acc += table[w * kpad + k];
+        sh[r * kpad + k] = acc;
+    }
+    __syncthreads();
+    if (r == 0) {
+        double tot = sh[k];
+        for (int i = 1; i < rows; i++) tot += sh[i * kpad + k];
+        partial[(int64_t)blockIdx.x * kpad + k] = tot;
+    }
+}
+
+__global__ void column_final_kernel(const double* __restrict__ partial, int nblocks, int kpad, double* __restrict__ total)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= kpad) return;
+    double acc = 0.0;
+    for (int b = 0; b < nblocks; b++) acc += partial[(int64_t)b * kpad + k];
+    total[k] = acc;
+}
+
+// one thread per word: log-normalise its K statistics and build the E-step row
+__global__ void __launch_bounds__(256) normalise_kernel(const double* __restrict__ class_word,
+                                                        const double* __restrict__ class_total, int K, int V, int kpad,
+                                                        double* __restrict__ log_beta_wk, double* __restrict__ beta_scaled,
+                                                        double* __restrict__ lbmax)
+{
+    const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= V) return;
+    const double* cw = class_word + w * kpad;
+    double* lb = log_beta_wk + w * kpad;
+    double* bs = beta_scaled + w * kpad;
+    double m = -INFINITY;
+    for (int k = 0; k < K; k++) {
+        const double x = cw[k];
+        // lda-model.c:35-43: log(cw) - log(ct) when cw > 0, else the -100 sentinel
+        const double v = x > 0 ? log(x) - log(class_total[k]) : -100.0;
+        lb[k] = v;
+        m = fmax(m, v);
+    }
+    lbmax[w] = m;
+    for (int k = 0; k < K; k++) bs[k] = exp(lb[k] - m);
+    for (int k = K; k < kpad; k++) { lb[k] = 0.0; bs[k] = 0.0; }
+}
+
+// host layout [K][V] -> device tables; one thread per word (coalesced over w for each k)
+__global__ void __launch_bounds__(256) tables_from_kv_kernel(const double* __restrict__ log_beta_kv, int K, int V, int kpad,
+                                                             double* __restrict__ log_beta_wk,
+                                                             double* __restrict__ beta_scaled, double* __restrict__ lbmax)
+{
+    const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= V) return;
+    double* lb = log_beta_wk + w * kpad;
+    double* bs = beta_scaled + w * kpad;
+    double m = -INFINITY;
+    for (int k = 0; k < K; k++) {
+        const double v = log_beta_kv[(int64_t)k * V + w];
+        lb[k] = v;
+        m = fmax(m, v);
+    }
+    lbmax[w] = m;
+    for (int k = 0; k < K; k++) bs[k] = exp(lb[k] - m);
+    for (int k = K; k < kpad; k++) { lb[k] = 0.0; bs[k] = 0.0; }
+}
+
+__global__ void __launch_bounds__(256) export_kv_kernel(const double* __restrict__ log_beta_wk, int K, int V, int kpad,
+                                                        double* __restrict__ log_beta_kv)
+{
+    const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= V) return;
+    for (int k = 0; k < K; k++) log_beta_kv[(int64_t)k * V + w] = log_beta_wk[w * kpad + k];
+}
+
+// fixed-order sum of the per-document likelihood and alpha statistics
+static constexpr int kDocBlocks = 296;
+static constexpr int kDocThreads = 256;
+
+__global__ void __launch_bounds__(kDocThreads) doc_partial_kernel(const double* __restrict__ doc_lik,
+                                                                  const double* __restrict__ doc_ass, int64_t D,
+                                                                  double* __restrict__ partial)
+{
+    __shared__ double sl[kDocThreads], sa[kDocThreads];
+    const int64_t chunk = (D + gridDim.x - 1) / gridDim.x;
+    const int64_t lo = chunk * blockIdx.x;
+    int64_t hi = lo + chunk;
+    if (hi > D) hi = D;
+    double l = 0.0, s = 0.0;
+    for (int64_t d = lo + threadIdx.x; d < hi; d += kDocThreads) { l += doc_lik[d]; s += doc_ass[d]; }
+    sl[threadIdx.x] = l;
+    sa[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = kDocThreads / 2; o > 0; o >>= 1) {
+        if (threadIdx.x < o) { sl[threadIdx.x] += sl[threadIdx.x + o]; sa[threadIdx.x] += sa[threadIdx.x + o]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { partial[2 * blockIdx.x] = sl[0]; partial[2 * blockIdx.x + 1] = sa[0]; }
+}
+
+__global__ void doc_final_kernel(const double* __restrict__ partial, int nblocks, int64_t D, double* __restrict__ tail)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double l = 0.0, s = 0.0;
+    for (int b = 0; b < nblocks; b++) { l += partial[2 * b]; s += partial[2 * b + 1]; }
+    tail[SS_LIK] = l;
+    tail[SS_ALPHA] = s;
+    tail[SS_NDOCS] = (double)D;
+    tail[SS_SPARE] = 0.0;
+}
+
+int mstep_partial_doubles(int V, const TopicLayout& lay, int64_t num_docs)
+{
+    (void)V; (void)num_docs;
+    int a = kColBlocks * lay.kpad, b = 2 * kDocBlocks;
+    return a > b ? a : b;
+}
+
+static int blocks_for(int64_t n, int threads) { return (int)((n + threads - 1) / threads); }
+
+int launch_tables_from_log_beta(const double* log_beta_kv, int K, int V, const TopicLayout& lay, double* log_beta_wk,
+                                double* beta_scaled, double* lbmax, cudaStream_t stream, int* launches)
+{
+    if (V == 0) return ONILDA_OK;
+    tables_from_kv_kernel<<<blocks_for(V, 256), 256, 0, stream>>>(log_beta_kv, K, V, lay.kpad, log_beta_wk, beta_scaled, lbmax);
+    ONILDA_CUDA(cudaGetLastError());
+    if (launches) *launches += 1;
+    return ONILDA_OK;
+}
+
+int launch_export_log_beta(const double* log_beta_wk, int K, int V, const TopicLayout& lay, double* log_beta_kv,
+                           cudaStream_t stream, int* launches)
+{
+    if (V == 0) return ONILDA_OK;
+    export_kv_kernel<<<blocks_for(V, 256), 256, 0, stream>>>(log_beta_wk, K, V, lay.kpad, log_beta_kv);
+    ONILDA_CUDA(cudaGetLastError());
+    if (launches) *launches += 1;
+    return ONILDA_OK;
+}
+
+int launch_reduce_doc_stats(const double* doc_lik, const double* doc_alpha_ss, int64_t num_docs, double* partial,
+                            double* ss_tail, cudaStream_t stream, int* launches)
+{
+    doc_partial_kernel<<<kDocBlocks, kDocThreads, 0, stream>>>(doc_lik, doc_alpha_ss, num_docs, partial);
+    ONILDA_CUDA(cudaGetLastError());
+    doc_final_kernel<<<1, 32, 0, stream>>>(partial, kDocBlocks, num_docs, ss_tail);
+    ONILDA_CUDA(cudaGetLastError());
+    if (launches) *launches += 2;
+    return ONILDA_OK;
+}
+
+int launch_mstep(const double* class_word, int K, int V, const TopicLayout& lay, double* partial, double* class_total,
+                 double* log_beta_wk, double* beta_scaled, double* lbmax, cudaStream_t stream, int* launches)
+{
+    if (V == 0) return ONILDA_OK;
+    const size_t shmem = sizeof(double) * (size_t)(kColThreads / lay.kpad) * lay.kpad;
+    column_partial_kernel<<<kColBlocks, kColThreads, shmem, stream>>>(class_word, V, lay.kpad, partial);
+    ONILDA_CUDA(cudaGetLastError());
+    column_final_kernel<<<blocks_for(lay.kpad, 64), 64, 0, stream>>>(partial, kColBlocks, lay.kpad, class_total);
+    ONILDA_CUDA(cudaGetLastError());
+    normalise_kernel<<<blocks_for(V, 256), 256, 0, stream>>>(class_word, class_total, K, V, lay.kpad, log_beta_wk,
+                                                             beta_scaled, lbmax);
+    ONILDA_CUDA(cudaGetLastError());
+    if (launches) *launches += 3;
+    return ONILDA_OK;
+}
+
+}  // namespace onilda

@@ -1,0 +1,571 @@
+// Post-LDA suspicious-connects scoring on sm_100a.
+//
+// Reference (Scala, Spark UDFs over broadcast maps):
+//   theta/phi normalisation  OniLDACWrapper.scala:121-144, 170-195
+//   score(ip, word)          SuspiciousConnectsScoreFunction.scala:11-23
+//   flow: two sides + min    netflow/FlowPostLDA.scala:94-125
+//   filter + ascending top-k netflow/FlowPostLDA.scala:79-80, dns/DNSPostLDA.scala:49-70,
+//                            utilities/DataFrameUtils.scala:21-38
+//
+// The scoring kernel is a streaming gather: per event side it reads two int32
+// ids, gathers one theta row and one phi row (K doubles each) and writes one
+// double.  A warp takes 32 events; its lanes first fetch the 32+32 rows
+// cooperatively (consecutive lanes read consecutive doubles of a row, so every
+// 32-byte sector that is fetched is used in full) into a per-warp shared-memory
+// tile, then each lane forms its own event's dot product from the tile with the
+// products rounded and added left to right - the order of Scala's
+// zip/map/sum - so the result is bit-identical to a sequential CPU evaluation.
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "kernels.cuh"
+
+struct onilda_scorer {
+    int device;
+    int sm_count;
+    int K;
+    int64_t D;
+    int32_t V;
+    double* d_theta;   // [(D+1)][K], row D = uniform 1/K (unknown ip)
+    double* d_phi;     // [(V+1)][K], row V = uniform 1/K (unknown word)
+    cudaStream_t stream[2];
+    cudaEvent_t ev0, ev1;
+    // staging for host-buffer calls (two chunks in flight)
+    int64_t chunk;
+    int32_t* d_ids[2];     // 4 * chunk
+    double* d_out[2];      // chunk
+    // selection scratch
+    unsigned long long* d_hist;   // [2048 + 8]
+    int64_t* d_sel_idx;
+    double* d_sel_score;
+    int64_t sel_cap;
+    double kernel_ms;
+    int64_t launches;
+};
+
+namespace {
+
+using namespace onilda;
+
+struct DeviceGuard {
+    int prev;
+    explicit DeviceGuard(int dev) : prev(-1) { cudaGetDevice(&prev); if (dev != prev) cudaSetDevice(dev); }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+constexpr int kScoreThreads = 256;            // 8 warps
+constexpr int kScoreWarps = kScoreThreads / 32;
+
+__device__ __forceinline__ int tile_stride(int K) { return K | 1; }   // odd stride: conflict-free 64-bit rows
+
+// Fetch 32 rows (one per lane's `row` index) of `table` into tile[32][stride].
+__device__ __forceinline__ void stage_rows(const double* __restrict__ table, int64_t row, int K, int stride,
+                                           double* tile, int lane)
+{
+    int r = 0, k = lane;
+    while (k >= K) { k -= K; r++; }
+    for (; r < 32;) {
+        const int64_t src_row = __shfl_sync(0xffffffffu, row, r & 31);
+        tile[r * stride + k] = __ldg(table + src_row * K + k);
+        k += 32;
+        while (k >= K) { k -= K; r++; }
+    }
+}
+
+__device__ __forceinline__ double dot_in_order(const double* a, const double* b, int K)
+{
+    double s = 0.0;
+    for (int k = 0; k < K; k++) s = __dadd_rn(s, __dmul_rn(a[k], b[k]));   // no fma: products are rounded first
+    return s;
+}
+
+template <bool FLOW>
+__global__ void __launch_bounds__(kScoreThreads) score_kernel(const double* __restrict__ theta, int64_t D,
+                                                              const double* __restrict__ phi, int32_t V, int K,
+                                                              const int32_t* __restrict__ sdoc,
+                                                              const int32_t* __restrict__ sword,
+                                                              const int32_t* __restrict__ ddoc,
+                                                              const int32_t* __restrict__ dword, int64_t n,
+                                                              double* __restrict__ out)
+{
+    extern __shared__ double smem[];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int stride = tile_stride(K);
+    double* tile_t = smem + (size_t)warp * 2 * 32 * stride;
+    double* tile_p = tile_t + 32 * stride;
+    const int64_t tiles = (n + 31) / 32;
+    const int64_t warps_total = (int64_t)gridDim.x * kScoreWarps;
+    for (int64_t tile = (int64_t)blockIdx.x * kScoreWarps + warp; tile < tiles; tile += warps_total) {
+        const int64_t i = tile * 32 + lane;
+        const bool live = i < n;
+        int32_t d0 = live ? sdoc[i] : -1, w0 = live ? sword[i] : -1;
+        // ids outside the tables (e.g. -1) take the uniform row (SuspiciousConnectsScoreFunction.scala:13-18)
+        int64_t drow = (d0 >= 0 && d0 < D) ? d0 : D;
+        int64_t wrow = (w0 >= 0 && w0 < V) ? w0 : V;
+        stage_rows(theta, drow, K, stride, tile_t, lane);
+        stage_rows(phi, wrow, K, stride, tile_p, lane);
+        __syncwarp();
+        double s = dot_in_order(tile_t + lane * stride, tile_p + lane * stride, K);
+        __syncwarp();
+        if (FLOW) {
+            int32_t d1 = live ? ddoc[i] : -1, w1 = live ? dword[i] : -1;
+            drow = (d1 >= 0 && d1 < D) ? d1 : D;
+            wrow = (w1 >= 0 && w1 < V) ? w1 : V;
+            stage_rows(theta, drow, K, stride, tile_t, lane);
+            stage_rows(phi, wrow, K, stride, tile_p, lane);
+            __syncwarp();
+            const double s2 = dot_in_order(tile_t + lane * stride, tile_p + lane * stride, K);
+            __syncwarp();
+            s = (s <= s2) ? s : s2;   // scala.math.min (FlowPostLDA.scala:117-119)
+        }
+        if (live) out[i] = s;
+    }
+}
+
+// theta row = gamma / sum (left-to-right sum), zeros when sum <= 0 (OniLDACWrapper.scala:132-144)
+__global__ void theta_kernel(const double* __restrict__ gamma, int64_t D, int K, double* __restrict__ theta)
+{
+    const int64_t d = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= D) return;
+    const double* g = gamma + d * K;
+    double s = 0.0;
+    for (int k = 0; k < K; k++) s = __dadd_rn(s, g[k]);
+    for (int k = 0; k < K; k++) theta[d * K + k] = (s > 0) ? g[k] / s : 0.0;
+}
+
+// phi: per topic exp, sum over the vocabulary, divide, transpose (OniLDACWrapper.scala:121-130, 178-195)
+__global__ void __launch_bounds__(256) phi_sum_kernel(const double* __restrict__ log_beta_kv, int V, double* __restrict__ sums)
+{
+    __shared__ double sh[256];
+    const int k = blockIdx.x;
+    double acc = 0.0;
+    for (int w = threadIdx.x; w < V; w += 256) acc += exp(log_beta_kv[(int64_t)k * V + w]);
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) sums[k] = sh[0];
+}
+
+__global__ void phi_norm_kernel(const double* __restrict__ log_beta_kv, const double* __restrict__ sums, int K, int V,
+                                double* __restrict__ phi_wk)
+{
+    const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= V) return;
+    for (int k = 0; k < K; k++) phi_wk[w * K + k] = exp(log_beta_kv[(int64_t)k * V + w]) / sums[k];
+}
+
+__global__ void fill_kernel(double* p, int n, double v)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+// ---- selection: k smallest (score, index) pairs with score <= threshold ----
+
+__device__ __forceinline__ unsigned long long order_key(double x)
+{
+    const unsigned long long b = (unsigned long long)__double_as_longlong(x);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+
+constexpr int kDigitBits = 11;
+constexpr int kBins = 1 << kDigitBits;
+
+// Histogram of one digit.  Items considered: key <= max_key, (key & key_mask) == key_prefix and,
+// when on_index, key == key_prefix exactly and (idx & idx_mask) == idx_prefix.
+__global__ void __launch_bounds__(256) select_hist_kernel(const double* __restrict__ score, int64_t n,
+                                                          unsigned long long max_key, unsigned long long key_prefix,
+                                                          unsigned long long key_mask, int on_index,
+                                                          unsigned long long idx_prefix, unsigned long long idx_mask,
+                                                          int shift, unsigned int digit_mask,
+                                                          unsigned long long* __restrict__ hist)
+{
+    __shared__ unsigned int sh[kBins];
+    for (int b = threadIdx.x; b < kBins; b += blockDim.x) sh[b] = 0;
+    __syncthreads();
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const unsigned long long key = order_key(score[i]);
+        if (key > max_key || (key & key_mask) != key_prefix) continue;
+        unsigned long long digit_src = key;
+        if (on_index) {
+            if (((unsigned long long)i & idx_mask) != idx_prefix) continue;
+            digit_src = (unsigned long long)i;
+        }
+        atomicAdd(&sh[(unsigned int)(digit_src >> shift) & digit_mask], 1u);
+    }
+    __syncthreads();
+    for (int b = threadIdx.x; b < kBins; b += blockDim.x)
+        if (sh[b]) atomicAdd(&hist[b], (unsigned long long)sh[b]);
+}
+
+// Collect every item with (key, idx) <= (cut_key, cut_idx) and key <= max_key (unordered).
+__global__ void __launch_bounds__(256) select_collect_kernel(const double* __restrict__ score, int64_t n,
+                                                             unsigned long long max_key, unsigned long long cut_key,
+                                                             unsigned long long cut_idx, int64_t cap,
+                                                             unsigned long long* __restrict__ counter,
+                                                             int64_t* __restrict__ idx_out, double* __restrict__ score_out)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const double s = score[i];
+        const unsigned long long key = order_key(s);
+        if (key > max_key) continue;
+        if (key < cut_key || (key == cut_key && (unsigned long long)i <= cut_idx)) {
+            const unsigned long long slot = atomicAdd(counter, 1ull);
+            if ((int64_t)slot < cap) { idx_out[slot] = i; score_out[slot] = s; }
+        }
+    }
+}
+
+unsigned long long host_order_key(double x)
+{
+    unsigned long long b;
+    memcpy(&b, &x, sizeof b);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+
+int ensure_sel(onilda_scorer* s, int64_t cap)
+{
+    if (cap <= s->sel_cap) return ONILDA_OK;
+    cudaFree(s->d_sel_idx); cudaFree(s->d_sel_score);
+    s->d_sel_idx = nullptr; s->d_sel_score = nullptr; s->sel_cap = 0;
+    if (cudaMalloc((void**)&s->d_sel_idx, sizeof(int64_t) * (size_t)cap) != cudaSuccess ||
+        cudaMalloc((void**)&s->d_sel_score, sizeof(double) * (size_t)cap) != cudaSuccess) {
+        cudaGetLastError();
+        return onilda_fail(ONILDA_ENOMEM, "top-k: cannot allocate room for %lld candidates on the device", (long long)cap);
+    }
+    s->sel_cap = cap;
+    return ONILDA_OK;
+}
+
+// k smallest of score_dev[0..n) (device) under `threshold`; ties by index.  Host outputs.
+// Radix select, most significant digit first, on the composite (order_key(score), index):
+// each pass is one histogram kernel over the scores plus an 16 KB read-back.
+int select_topk_device(onilda_scorer* s, const double* score_dev, int64_t n, double threshold, int64_t k,
+                       int64_t* idx_out, double* score_out, int64_t* n_out)
+{
+    cudaStream_t st = s->stream[0];
+    const unsigned long long max_key = isnan(threshold) ? 0ull : host_order_key(threshold);
+    const int blocks = s->sm_count * 4;
+    std::vector<unsigned long long> hist(kBins);
+    auto run_hist = [&](unsigned long long kp, unsigned long long km, int on_idx, unsigned long long ip,
+                        unsigned long long im, int shift, int bits) -> int {
+        ONILDA_CUDA(cudaMemsetAsync(s->d_hist, 0, sizeof(unsigned long long) * kBins, st));
+        select_hist_kernel<<<blocks, 256, 0, st>>>(score_dev, n, max_key, kp, km, on_idx, ip, im, shift,
+                                                   (1u << bits) - 1u, s->d_hist);
+        ONILDA_CUDA(cudaGetLastError());
+        ONILDA_CUDA(cudaMemcpyAsync(hist.data(), s->d_hist, sizeof(unsigned long long) * kBins, cudaMemcpyDeviceToHost, st));
+        ONILDA_CUDA(cudaStreamSynchronize(st));
+        s->launches++;
+        return ONILDA_OK;
+    };
+    // returns the bin holding the `remaining`-th item and subtracts what lies below it
+    auto pick = [&](unsigned long long& remaining) -> unsigned long long {
+        unsigned long long acc = 0;
+        int b = 0;
+        for (; b < kBins - 1; b++) { if (acc + hist[(size_t)b] >= remaining) break; acc += hist[(size_t)b]; }
+        remaining -= acc;
+        return (unsigned long long)b;
+    };
+    static const int key_pass[6][2] = { {53, 11}, {42, 11}, {31, 11}, {20, 11}, {9, 11}, {0, 9} };
+    static const int idx_pass[4][2] = { {33, 11}, {22, 11}, {11, 11}, {0, 11} };   // indices < 2^44
+
+    unsigned long long cut_key = max_key, cut_idx = ~0ull;
+    int64_t take = 0;
+    if (n > 0) {
+        // the first key pass also yields the number of events under the threshold
+        int rc = run_hist(0, 0, 0, 0, 0, key_pass[0][0], key_pass[0][1]);
+        if (rc != ONILDA_OK) return rc;
+        unsigned long long under = 0;
+        for (unsigned long long h : hist) under += h;
+        take = (k == -1 || (unsigned long long)k > under) ? (int64_t)under : k;
+        if (take > 0 && (unsigned long long)take < under) {
+            unsigned long long remaining = (unsigned long long)take, kp = 0, km = 0;
+            for (int p = 0; p < 6; p++) {
+                const int shift = key_pass[p][0], bits = key_pass[p][1];
+                if (p > 0) { rc = run_hist(kp, km, 0, 0, 0, shift, bits); if (rc != ONILDA_OK) return rc; }
+                const unsigned long long b = pick(remaining);
+                kp |= b << shift;
+                km |= ((1ull << bits) - 1ull) << shift;
+            }
+            cut_key = kp;
+            // among events whose score equals the cut, keep the `remaining` smallest indices
+            unsigned long long ip = 0, im = 0;
+            for (int p = 0; p < 4; p++) {
+                const int shift = idx_pass[p][0], bits = idx_pass[p][1];
+                rc = run_hist(cut_key, ~0ull, 1, ip, im, shift, bits);
+                if (rc != ONILDA_OK) return rc;
+                const unsigned long long b = pick(remaining);
+                ip |= b << shift;
+                im |= ((1ull << bits) - 1ull) << shift;
+            }
+            cut_idx = ip;
+        }
+    }
+    *n_out = take;
+    if (take == 0) return ONILDA_OK;
+    int rc = ensure_sel(s, take);
+    if (rc != ONILDA_OK) return rc;
+    ONILDA_CUDA(cudaMemsetAsync(s->d_hist, 0, sizeof(unsigned long long), st));
+    select_collect_kernel<<<blocks, 256, 0, st>>>(score_dev, n, max_key, cut_key, cut_idx, take, s->d_hist, s->d_sel_idx, s->d_sel_score);
+    ONILDA_CUDA(cudaGetLastError());
+    s->launches++;
+    std::vector<int64_t> idx((size_t)take);
+    std::vector<double> sc((size_t)take);
+    unsigned long long got = 0;
+    ONILDA_CUDA(cudaMemcpyAsync(&got, s->d_hist, sizeof got, cudaMemcpyDeviceToHost, st));
+    ONILDA_CUDA(cudaMemcpyAsync(idx.data(), s->d_sel_idx, sizeof(int64_t) * (size_t)take, cudaMemcpyDeviceToHost, st));
+    ONILDA_CUDA(cudaMemcpyAsync(sc.data(), s->d_sel_score, sizeof(double) * (size_t)take, cudaMemcpyDeviceToHost, st));
+    ONILDA_CUDA(cudaStreamSynchronize(st));
+    if ((int64_t)got != take)
+        return onilda_fail(ONILDA_ECUDA, "top-k selection collected %llu rows, expected %lld", got, (long long)take);
+    // ascending by (score, index): the at most `take` survivors are ordered on the host
+    std::vector<int64_t> perm((size_t)take);
+    for (int64_t i = 0; i < take; i++) perm[(size_t)i] = i;
+    std::sort(perm.begin(), perm.end(), [&](int64_t a, int64_t b) {
+        if (sc[(size_t)a] != sc[(size_t)b]) return sc[(size_t)a] < sc[(size_t)b];
+        return idx[(size_t)a] < idx[(size_t)b];
+    });
+    for (int64_t i = 0; i < take; i++) { idx_out[i] = idx[(size_t)perm[(size_t)i]]; score_out[i] = sc[(size_t)perm[(size_t)i]]; }
+    return ONILDA_OK;
+}
+
+size_t score_smem_bytes(int K) { return sizeof(double) * (size_t)kScoreWarps * 2 * 32 * (size_t)(K | 1); }
+
+int launch_score(onilda_scorer* s, cudaStream_t st, const int32_t* sdoc, const int32_t* sword, const int32_t* ddoc,
+                 const int32_t* dword, int64_t n, double* out)
+{
+    if (n <= 0) return ONILDA_OK;
+    const size_t shmem = score_smem_bytes(s->K);
+    int64_t tiles = (n + 31) / 32;
+    int64_t blocks = (tiles + kScoreWarps - 1) / kScoreWarps;
+    const int64_t cap = (int64_t)s->sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    if (ddoc) score_kernel<true><<<(unsigned)blocks, kScoreThreads, shmem, st>>>(s->d_theta, s->D, s->d_phi, s->V, s->K, sdoc, sword, ddoc, dword, n, out);
+    else score_kernel<false><<<(unsigned)blocks, kScoreThreads, shmem, st>>>(s->d_theta, s->D, s->d_phi, s->V, s->K, sdoc, sword, nullptr, nullptr, n, out);
+    ONILDA_CUDA(cudaGetLastError());
+    s->launches++;
+    return ONILDA_OK;
+}
+
+}  // namespace
+
+extern "C" void onilda_scorer_destroy(onilda_scorer* s)
+{
+    if (!s) return;
+    DeviceGuard g(s->device);
+    cudaFree(s->d_theta); cudaFree(s->d_phi);
+    for (int i = 0; i < 2; i++) { cudaFree(s->d_ids[i]); cudaFree(s->d_out[i]); if (s->stream[i]) cudaStreamDestroy(s->stream[i]); }
+    cudaFree(s->d_hist); cudaFree(s->d_sel_idx); cudaFree(s->d_sel_score);
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
+    free(s);
+}
+
+extern "C" int onilda_scorer_create(const double* theta, int64_t num_docs, const double* phi, int32_t num_terms,
+                                    int num_topics, int device, onilda_scorer** out)
+{
+    if (!out || num_docs < 0 || num_terms < 0 || num_topics <= 0 || (num_docs > 0 && !theta) || (num_terms > 0 && !phi))
+        return onilda_fail(ONILDA_EINVAL, "scorer_create: bad argument");
+    if (onilda_device_count() == 0)
+        return onilda_fail(ONILDA_ECUDA, "scorer_create: no CUDA device is usable and this library has no CPU path");
+    if (device < 0) ONILDA_CUDA(cudaGetDevice(&device));
+    DeviceGuard g(device);
+    onilda_scorer* s = (onilda_scorer*)calloc(1, sizeof *s);
+    if (!s) return onilda_fail(ONILDA_ENOMEM, "scorer_create: out of host memory");
+    s->device = device; s->K = num_topics; s->D = num_docs; s->V = num_terms;
+    s->chunk = 1 << 24;
+    const int K = num_topics;
+    cudaError_t e = cudaSuccess;
+#define STEP(x) if (e == cudaSuccess) e = (x)
+    STEP(cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device));
+    STEP(cudaStreamCreateWithFlags(&s->stream[0], cudaStreamNonBlocking));
+    STEP(cudaStreamCreateWithFlags(&s->stream[1], cudaStreamNonBlocking));
+    STEP(cudaEventCreate(&s->ev0));
+    STEP(cudaEventCreate(&s->ev1));
+    STEP(cudaMalloc((void**)&s->d_theta, sizeof(double) * (size_t)(num_docs + 1) * K));
+    STEP(cudaMalloc((void**)&s->d_phi, sizeof(double) * (size_t)(num_terms + 1) * K));
+    STEP(cudaMalloc((void**)&s->d_hist, sizeof(unsigned long long) * (kBins + 8)));
+    if (num_docs > 0) STEP(cudaMemcpyAsync(s->d_theta, theta, sizeof(double) * (size_t)num_docs * K, cudaMemcpyHostToDevice, s->stream[0]));
+    if (num_terms > 0) STEP(cudaMemcpyAsync(s->d_phi, phi, sizeof(double) * (size_t)num_terms * K, cudaMemcpyHostToDevice, s->stream[0]));
+    if (e == cudaSuccess) {
+        fill_kernel<<<(K + 63) / 64, 64, 0, s->stream[0]>>>(s->d_theta + (size_t)num_docs * K, K, 1.0 / K);
+        fill_kernel<<<(K + 63) / 64, 64, 0, s->stream[0]>>>(s->d_phi + (size_t)num_terms * K, K, 1.0 / K);
+        e = cudaGetLastError();
+    }
+    const size_t shmem = score_smem_bytes(K);
+    STEP(cudaFuncSetAttribute(score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
+    STEP(cudaFuncSetAttribute(score_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
+    STEP(cudaStreamSynchronize(s->stream[0]));
+#undef STEP
+    if (e != cudaSuccess) {
+        int rc = onilda_fail(e == cudaErrorMemoryAllocation ? ONILDA_ENOMEM : ONILDA_ECUDA, "scorer_create: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+        onilda_scorer_destroy(s);
+        return rc;
+    }
+    *out = s;
+    return ONILDA_OK;
+}
+
+static int ensure_staging(onilda_scorer* s)
+{
+    if (s->d_ids[0]) return ONILDA_OK;
+    for (int i = 0; i < 2; i++) {
+        ONILDA_CUDA(cudaMalloc((void**)&s->d_ids[i], sizeof(int32_t) * 4 * (size_t)s->chunk));
+        ONILDA_CUDA(cudaMalloc((void**)&s->d_out[i], sizeof(double) * (size_t)s->chunk));
+    }
+    return ONILDA_OK;
+}
+
+// host buffers: chunks alternate between two streams so copies overlap the kernel
+static int score_host(onilda_scorer* s, const int32_t* sdoc, const int32_t* sword, const int32_t* ddoc,
+                      const int32_t* dword, int64_t n, double* out)
+{
+    if (!s || n < 0 || (n > 0 && (!sdoc || !sword || !out))) return onilda_fail(ONILDA_EINVAL, "score: bad argument");
+    DeviceGuard g(s->device);
+    int rc = ensure_staging(s);
+    if (rc != ONILDA_OK) return rc;
+    const int64_t C = s->chunk;
+    int which = 0;
+    ONILDA_CUDA(cudaEventRecord(s->ev0, s->stream[0]));
+    for (int64_t lo = 0; lo < n; lo += C, which ^= 1) {
+        const int64_t m = (n - lo < C) ? n - lo : C;
+        cudaStream_t st = s->stream[which];
+        int32_t* ids = s->d_ids[which];
+        ONILDA_CUDA(cudaMemcpyAsync(ids, sdoc + lo, sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, st));
+        ONILDA_CUDA(cudaMemcpyAsync(ids + C, sword + lo, sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, st));
+        if (ddoc) {
+            ONILDA_CUDA(cudaMemcpyAsync(ids + 2 * C, ddoc + lo, sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, st));
+            ONILDA_CUDA(cudaMemcpyAsync(ids + 3 * C, dword + lo, sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, st));
+        }
+        rc = launch_score(s, st, ids, ids + C, ddoc ? ids + 2 * C : nullptr, ddoc ? ids + 3 * C : nullptr, m, s->d_out[which]);
+        if (rc != ONILDA_OK) return rc;
+        ONILDA_CUDA(cudaMemcpyAsync(out + lo, s->d_out[which], sizeof(double) * (size_t)m, cudaMemcpyDeviceToHost, st));
+    }
+    ONILDA_CUDA(cudaStreamSynchronize(s->stream[1]));
+    ONILDA_CUDA(cudaEventRecord(s->ev1, s->stream[0]));
+    ONILDA_CUDA(cudaStreamSynchronize(s->stream[0]));
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, s->ev0, s->ev1) == cudaSuccess) s->kernel_ms = ms;
+    return ONILDA_OK;
+}
+
+extern "C" int onilda_score(onilda_scorer* s, const int32_t* doc, const int32_t* word, int64_t n, double* out)
+{
+    return score_host(s, doc, word, nullptr, nullptr, n, out);
+}
+
+extern "C" int onilda_score_flow_min(onilda_scorer* s, const int32_t* sdoc, const int32_t* sword, const int32_t* ddoc,
+                                     const int32_t* dword, int64_t n, double* out)
+{
+    if (n > 0 && (!ddoc || !dword)) return onilda_fail(ONILDA_EINVAL, "score_flow_min: null destination ids");
+    return score_host(s, sdoc, sword, ddoc, dword, n, out);
+}
+
+extern "C" int onilda_topk(onilda_scorer* s, const double* score, int64_t n, double threshold, int64_t k,
+                           int64_t* idx_out, double* score_out, int64_t* n_out)
+{
+    if (!s || n < 0 || (n > 0 && !score) || !n_out || k < -1) return onilda_fail(ONILDA_EINVAL, "topk: bad argument");
+    DeviceGuard g(s->device);
+    double* d_score = nullptr;
+    if (n > 0) {
+        ONILDA_CUDA(cudaMalloc((void**)&d_score, sizeof(double) * (size_t)n));
+        cudaError_t e = cudaMemcpyAsync(d_score, score, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, s->stream[0]);
+        if (e != cudaSuccess) { cudaFree(d_score); return onilda_fail(ONILDA_ECUDA, "topk: %s", cudaGetErrorString(e)); }
+    }
+    int rc = select_topk_device(s, d_score, n, threshold, k, idx_out, score_out, n_out);
+    cudaFree(d_score);
+    return rc;
+}
+
+extern "C" int onilda_score_flow_topk_device(onilda_scorer* s, const int32_t* sdoc_dev, const int32_t* sword_dev,
+                                             const int32_t* ddoc_dev, const int32_t* dword_dev, int64_t n,
+                                             double threshold, int64_t k, int64_t* idx_out, double* score_out,
+                                             int64_t* n_out, double* score_dev_out)
+{
+    if (!s || n < 0 || !n_out || k < -1 || (n > 0 && (!sdoc_dev || !sword_dev)))
+        return onilda_fail(ONILDA_EINVAL, "score_flow_topk_device: bad argument");
+    DeviceGuard g(s->device);
+    double* d_score = score_dev_out;
+    if (!d_score && n > 0) ONILDA_CUDA(cudaMalloc((void**)&d_score, sizeof(double) * (size_t)n));
+    cudaStream_t st = s->stream[0];
+    cudaEventRecord(s->ev0, st);
+    int rc = launch_score(s, st, sdoc_dev, sword_dev, ddoc_dev, dword_dev, n, d_score);
+    cudaEventRecord(s->ev1, st);
+    if (rc == ONILDA_OK) rc = select_topk_device(s, d_score, n, threshold, k, idx_out, score_out, n_out);
+    if (rc == ONILDA_OK) {
+        cudaStreamSynchronize(st);
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, s->ev0, s->ev1) == cudaSuccess) s->kernel_ms = ms;
+    }
+    if (!score_dev_out) cudaFree(d_score);
+    return rc;
+}
+
+extern "C" int onilda_scorer_stats(onilda_scorer* s, double* kernel_ms, int64_t* launches)
+{
+    if (!s) return onilda_fail(ONILDA_EINVAL, "scorer_stats: null handle");
+    if (kernel_ms) *kernel_ms = s->kernel_ms;
+    if (launches) *launches = s->launches;
+    return ONILDA_OK;
+}
+
+extern "C" int onilda_theta_from_gamma(const double* gamma, int64_t num_docs, int num_topics, int device, double* theta_out)
+{
+    if (num_docs < 0 || num_topics <= 0 || (num_docs > 0 && (!gamma || !theta_out)))
+        return onilda_fail(ONILDA_EINVAL, "theta_from_gamma: bad argument");
+    if (num_docs == 0) return ONILDA_OK;
+    if (onilda_device_count() == 0) return onilda_fail(ONILDA_ECUDA, "theta_from_gamma: no CUDA device is usable");
+    if (device < 0) ONILDA_CUDA(cudaGetDevice(&device));
+    DeviceGuard g(device);
+    const size_t bytes = sizeof(double) * (size_t)num_docs * num_topics;
+    double *d_in = nullptr, *d_out = nullptr;
+    ONILDA_CUDA(cudaMalloc((void**)&d_in, bytes));
+    if (cudaMalloc((void**)&d_out, bytes) != cudaSuccess) { cudaFree(d_in); cudaGetLastError(); return onilda_fail(ONILDA_ENOMEM, "theta_from_gamma: device memory"); }
+    cudaError_t e = cudaMemcpy(d_in, gamma, bytes, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        theta_kernel<<<(unsigned)((num_docs + 255) / 256), 256>>>(d_in, num_docs, num_topics, d_out);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(theta_out, d_out, bytes, cudaMemcpyDeviceToHost);
+    cudaFree(d_in); cudaFree(d_out);
+    if (e != cudaSuccess) return onilda_fail(ONILDA_ECUDA, "theta_from_gamma: %s", cudaGetErrorString(e));
+    return ONILDA_OK;
+}
+
+extern "C" int onilda_phi_from_log_beta(const double* log_beta, int num_topics, int num_terms, int device, double* phi_out)
+{
+    if (num_topics <= 0 || num_terms < 0 || (num_terms > 0 && (!log_beta || !phi_out)))
+        return onilda_fail(ONILDA_EINVAL, "phi_from_log_beta: bad argument");
+    if (num_terms == 0) return ONILDA_OK;
+    if (onilda_device_count() == 0) return onilda_fail(ONILDA_ECUDA, "phi_from_log_beta: no CUDA device is usable");
+    if (device < 0) ONILDA_CUDA(cudaGetDevice(&device));
+    DeviceGuard g(device);
+    const size_t bytes = sizeof(double) * (size_t)num_topics * num_terms;
+    double *d_in = nullptr, *d_out = nullptr, *d_sum = nullptr;
+    ONILDA_CUDA(cudaMalloc((void**)&d_in, bytes));
+    if (cudaMalloc((void**)&d_out, bytes) != cudaSuccess || cudaMalloc((void**)&d_sum, sizeof(double) * num_topics) != cudaSuccess) {
+        cudaFree(d_in); cudaFree(d_out); cudaGetLastError();
+        return onilda_fail(ONILDA_ENOMEM, "phi_from_log_beta: device memory");
+    }
+    cudaError_t e = cudaMemcpy(d_in, log_beta, bytes, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        phi_sum_kernel<<<num_topics, 256>>>(d_in, num_terms, d_sum);
+        phi_norm_kernel<<<(num_terms + 255) / 256, 256>>>(d_in, d_sum, num_topics, num_terms, d_out);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(phi_out, d_out, bytes, cudaMemcpyDeviceToHost);
+    cudaFree(d_in); cudaFree(d_out); cudaFree(d_sum);
+    if (e != cudaSuccess) return onilda_fail(ONILDA_ECUDA, "phi_from_log_beta: %s", cudaGetErrorString(e));
+    return ONILDA_OK;
+}

@@ -1,0 +1,299 @@
+"""Parity of the CUDA path (through the C ABI) with the oracle and with the
+golden files the unmodified reference wrote.  All tests here need a B200.
+
+Tolerances are BASELINE.json's: per-iteration corpus log-likelihood 1e-6
+relative, final beta / gamma 1e-4 max relative (with an absolute floor for
+values near zero), bit-exact for parsing, scores and indices.
+"""
+import subprocess
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+GOLD = Path(__file__).resolve().parent / "golden"
+CASES = ["k5", "k20", "k20_fixed", "k50"]
+
+LIK_RTOL = 1e-6        # north_star: per-iteration likelihood
+MODEL_RTOL = 1e-4      # north_star: final beta / gamma max relative error
+
+
+def rel_err(a, b, floor):
+    return np.max(np.abs(a - b) / np.maximum(np.abs(b), floor))
+
+
+def read_matrix(path):
+    return np.array([[float(x) for x in line.split()] for line in Path(path).read_text().splitlines()])
+
+
+def load_case(oni, case):
+    d = GOLD / case
+    return d, oni.Corpus.from_dat(d / "c.dat"), oni.Model.load(d / "000"), oni.read_settings(d / "settings.txt")
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_single_estep_against_oracle(oni, oracle, case):
+    """One E-step from the 000 model: per-document bound, gamma, class_word, alpha statistics."""
+    d, c, m, st = load_case(oni, case)
+    off, w, cn, tot, V = oracle.read_dat(d / "c.dat")
+    alpha, lb = oracle.load_model(d / "000")
+    ref = oracle.e_step(off, w, cn, V, alpha, lb, st.var_max_iter, st.var_converged)
+    em = oni.EM(c, m, st)
+    em.estep()
+    lik = em.doc_likelihood()
+    gam = em.gamma()
+    assert rel_err(lik, ref["doc_lik"], 1e-9) < 1e-10
+    assert rel_err(gam, ref["gamma"], 1e-9) < 1e-9
+    lik_sum, conv, keep = em.mstep()
+    assert abs(lik_sum - ref["lik"]) / abs(ref["lik"]) < 1e-12
+    # M-step result against lda_mle on the oracle's statistics
+    lb_ref = np.zeros_like(lb)
+    oracle.lib().oracle_lda_mle(lb.shape[0], V, ref["class_word"], ref["class_total"], lb_ref)
+    got = em.model()
+    assert rel_err(got.log_beta, lb_ref, 1e-6) < 1e-8
+    if st.estimate_alpha:
+        a_ref = oracle.lib().oracle_opt_alpha(ref["alpha_ss"], ref["num_docs"], lb.shape[0])
+        assert abs(got.alpha - a_ref) / a_ref < 1e-9
+    else:
+        assert got.alpha == alpha
+    em.close()
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_full_em_against_reference_files(oni, case, tmp_path):
+    """The whole run from 000 against what the reference binary wrote (likelihood.dat, final.*)."""
+    d, c, m, st = load_case(oni, case)
+    ref_lik = np.loadtxt(d / "likelihood.dat", ndmin=2)
+    em = oni.EM(c, m, st)
+    liks, convs = [], []
+    keep = True
+    while keep:
+        lik, conv, keep = em.iterate()
+        liks.append(lik)
+        convs.append(conv)
+    assert len(liks) == len(ref_lik), "EM iteration count differs from the reference"
+    liks = np.array(liks)
+    assert np.max(np.abs(liks - ref_lik[:, 0]) / np.abs(ref_lik[:, 0])) < LIK_RTOL
+    assert np.isinf(convs[0])
+    final = em.model()
+    beta_ref = read_matrix(d / "final.beta")
+    gamma_ref = read_matrix(d / "final.gamma")
+    assert rel_err(final.log_beta, beta_ref, 1e-2) < MODEL_RTOL
+    assert rel_err(em.gamma(), gamma_ref, 1e-3) < MODEL_RTOL
+    alpha_ref = float((d / "final.other").read_text().split()[-1])
+    assert abs(final.alpha - alpha_ref) <= MODEL_RTOL * alpha_ref + 1e-10
+    em.close()
+
+
+@pytest.mark.parametrize("case", ["k5", "k20"])
+def test_lda_program_drop_in(oni, case, tmp_path):
+    """`lda est` / `lda inf` with the reference's argv, files compared with the reference's."""
+    d = GOLD / case
+    K = int((d / "000.other").read_text().split()[1])
+    out = tmp_path / "out"
+    r = subprocess.run([str(oni.LDA_BIN), "est", "2.5", str(K), str(d / "settings.txt"), "1", str(d / "c.dat"),
+                        str(d / "000"), str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert (out / "000.beta").read_bytes() == (d / "000.beta").read_bytes()     # float-parsed model re-serialises identically
+    assert (out / "000.other").read_bytes() == (d / "000.other").read_bytes()
+    mine, ref = np.loadtxt(out / "likelihood.dat", ndmin=2), np.loadtxt(d / "likelihood.dat", ndmin=2)
+    assert mine.shape == ref.shape
+    assert np.max(np.abs(mine[:, 0] - ref[:, 0]) / np.abs(ref[:, 0])) < LIK_RTOL
+    assert rel_err(read_matrix(out / "final.beta"), read_matrix(d / "final.beta"), 1e-2) < MODEL_RTOL
+    assert rel_err(read_matrix(out / "final.gamma"), read_matrix(d / "final.gamma"), 1e-3) < MODEL_RTOL
+    first = (out / "final.gamma").read_text().splitlines()[0]
+    assert not first.startswith(" ") and (out / "final.beta").read_text().startswith(" ")   # OniLDACWrapper.scala:88-112
+    # inference with the reference's final model
+    r = subprocess.run([str(oni.LDA_BIN), "inf", str(d / "inf-settings.txt"), str(d / "final"), str(d / "c.dat"),
+                        str(tmp_path / "inf")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    g, gr = read_matrix(tmp_path / "inf-gamma.dat"), read_matrix(d / "inf-gamma.dat")
+    assert rel_err(g, gr, 1e-3) < MODEL_RTOL
+    l, lr = np.loadtxt(tmp_path / "inf-lda-lhood.dat"), np.loadtxt(d / "inf-lda-lhood.dat")
+    assert np.max(np.abs(l - lr) / np.maximum(np.abs(lr), 1.0)) < 1e-5      # files carry 5 decimals
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_infer_against_reference_files(oni, case):
+    d = GOLD / case
+    c = oni.Corpus.from_dat(d / "c.dat")
+    m = oni.Model.load(d / "final")
+    st = oni.read_settings(d / "inf-settings.txt")
+    gamma, lik = oni.infer(m, c, st)
+    assert rel_err(gamma, read_matrix(d / "inf-gamma.dat"), 1e-3) < MODEL_RTOL
+    lr = np.loadtxt(d / "inf-lda-lhood.dat")
+    assert np.max(np.abs(lik - lr) / np.maximum(np.abs(lr), 1.0)) < 1e-5
+
+
+def test_medium_corpus_two_iterations_against_oracle(oni, oracle, corpusgen):
+    """cfg-1-shaped corpus (scaled to what the oracle does in seconds), random start with a fixed seed."""
+    g = corpusgen.generate(2500, 100, 5000, 20, seed=20161101, hub_tokens=8000)
+    c = oni.Corpus.from_csr(g.offsets, g.words, g.counts)
+    m = oni.Model.new(20, c.num_terms)
+    m.init_random(12345)
+    m.alpha = 2.5
+    st = oni.Settings(20, 1e-6, 1, 1e-6, 1)          # em max iter 1 -> two iterations (lda-estimate.c:186)
+    ref = oracle.run_em(g.offsets, g.words, g.counts, c.num_terms, 2.5, m.log_beta.copy(), oracle.settings(20, 1e-6, 1, 1e-6, 1))
+    em = oni.EM(c, m, st)
+    liks, keep = [], True
+    while keep:
+        lik, conv, keep = em.iterate()
+        liks.append(lik)
+    assert len(liks) == len(ref["lik"]) == 2
+    assert np.max(np.abs(np.array(liks) - ref["lik"]) / np.abs(ref["lik"])) < LIK_RTOL
+    final = em.model()
+    assert rel_err(final.log_beta, ref["log_beta"], 1e-2) < MODEL_RTOL
+    assert rel_err(em.gamma(), ref["gamma"], 1e-3) < MODEL_RTOL
+    assert abs(final.alpha - ref["alpha"]) / ref["alpha"] < MODEL_RTOL
+    em.close()
+
+
+def test_invariants_at_scale(oni, corpusgen):
+    """Properties that hold at any size: gamma rows sum to K*alpha + total; class_word sums to the token count."""
+    g = corpusgen.generate(60000, 60, 20000, 20, seed=5, hub_tokens=20000)
+    c = oni.Corpus.from_csr(g.offsets, g.words, g.counts)
+    m = oni.Model.new(20, c.num_terms)
+    m.init_random(99)
+    m.alpha = 0.7
+    em = oni.EM(c, m, oni.Settings(20, 1e-6, 20, 1e-6, 0))
+    em.estep()
+    gam = em.gamma()
+    totals = np.add.reduceat(g.counts.astype(np.float64), g.offsets[:-1])
+    assert np.max(np.abs(gam.sum(axis=1) - (20 * 0.7 + totals)) / (20 * 0.7 + totals)) < 1e-12
+    assert np.all(gam > 0)
+    lik, conv, keep = em.mstep()
+    assert np.isfinite(lik) and lik < 0 and keep
+    beta = np.exp(em.model().log_beta)
+    assert np.max(np.abs(beta.sum(axis=1) - 1.0)) < 1e-9          # rows of exp(log_beta) are distributions
+    lik2, conv2, _ = em.iterate()
+    assert lik2 > lik and conv2 > 0                                # EM increases the bound
+    st = em.stats(with_sweeps=True)
+    assert st["launches"] >= 4 and st["sweeps"] >= c.num_docs and st["estep_ms"] > 0
+    em.close()
+
+
+def test_var_max_iter_special_values(oni, oracle):
+    """-1 = unbounded; 0 or below -1 = the sweep loop is never entered (lda-inference.c:46-47)."""
+    d = GOLD / "k5"
+    off, w, cn, tot, V = oracle.read_dat(d / "c.dat")
+    alpha, lb = oracle.load_model(d / "000")
+    c, m = oni.Corpus.from_dat(d / "c.dat"), oni.Model.load(d / "000")
+    for vmi in (-1, 0, -2, 1, 3):
+        ref = oracle.e_step(off, w, cn, V, alpha, lb, vmi, 1e-6)
+        em = oni.EM(c, m, oni.Settings(vmi, 1e-6, 5, 1e-6, 1))
+        em.estep()
+        assert rel_err(em.doc_likelihood(), ref["doc_lik"], 1e-9) < 1e-10, vmi
+        assert rel_err(em.gamma(), ref["gamma"], 1e-9) < 1e-9, vmi
+        lik, _, _ = em.mstep()
+        lb_ref = np.zeros_like(lb)
+        oracle.lib().oracle_lda_mle(lb.shape[0], V, ref["class_word"], ref["class_total"], lb_ref)
+        assert rel_err(em.model().log_beta, lb_ref, 1e-6) < 1e-8, vmi
+        em.close()
+
+
+def test_sharded_em_matches_single(oni, corpusgen):
+    """Two shards on one device + the packed-statistics sum == one shard (the N>1 data path)."""
+    g = corpusgen.generate(3000, 40, 800, 20, seed=8, hub_tokens=3000)
+    c = oni.Corpus.from_csr(g.offsets, g.words, g.counts)
+    m = oni.Model.new(20, c.num_terms)
+    m.init_random(4)
+    m.alpha = 2.5
+    st = oni.Settings(20, 1e-6, 3, 1e-6, 1)
+    one = oni.EM(c, m, st)
+    a, b = oni.EM(c, m, st, doc_begin=0, doc_end=1300), oni.EM(c, m, st, doc_begin=1300, doc_end=3000)
+    for _ in range(3):
+        l1, c1, k1 = one.iterate()
+        a.estep()
+        b.estep()
+        oni.allreduce_peer([a, b])
+        la, ca, ka = a.mstep()
+        lb_, cb, kb = b.mstep()
+        assert la == lb_ and ka == kb
+        assert abs(la - l1) / abs(l1) < 1e-12
+    assert rel_err(a.model().log_beta, one.model().log_beta, 1e-6) < 1e-9
+    assert rel_err(np.vstack([a.gamma(), b.gamma()]), one.gamma(), 1e-9) < 1e-9
+    for e in (one, a, b):
+        e.close()
+
+
+# ------------------------------------------------------------------ scoring
+
+def test_theta_phi_against_reference_golden(oni, oracle):
+    """OniLDACWrapperTest.scala golden values through the device kernels."""
+    phi = oni.phi_from_log_beta(np.array([[1.0, 2.0, 3.0, 4.0, 5.0]]))
+    want = np.array([0.011656230956039607, 0.03168492079612427, 0.0861285444362687, 0.23412165725273662, 0.6364086465588308])
+    assert np.max(np.abs(phi[:, 0] - want) / want) < 1e-14
+    line = [0.0124531442] * 20
+    line[11], line[18] = 23983.5532262138, 22999.4716800747
+    th = oni.theta_from_gamma(np.array([line, [0.0, 0.0, 1.0, -1.0] + [0.0] * 16]))
+    assert th[0][11] == 0.5104702996191969 and th[0][18] == 0.48952492939114034 and th[0][0] == 2.6505498126219955E-7
+    assert np.all(th[1] == 0.0)
+    for case in CASES:
+        lb = read_matrix(GOLD / case / "final.beta")
+        ga = read_matrix(GOLD / case / "final.gamma")
+        assert np.array_equal(oni.theta_from_gamma(ga), oracle.theta_from_gamma(ga))
+        p, pr = oni.phi_from_log_beta(lb), oracle.phi_from_logbeta(lb)
+        assert np.max(np.abs(p - pr) / np.maximum(pr, 1e-300)) < 1e-13
+
+
+@pytest.mark.parametrize("K", [20, 5, 50, 7])
+def test_scores_bit_exact(oni, oracle, K):
+    rng = np.random.default_rng(K)
+    D, V, n = 3000, 700, 100003
+    theta = rng.dirichlet(np.full(K, 0.1), D)
+    phi = rng.dirichlet(np.full(V, 0.05), K).T.copy()
+    ids = [rng.integers(-1, hi, n).astype(np.int32) for hi in (D, V, D, V)]
+    ids[0][:5] = [D, D + 7, -1, 0, D - 1]          # out-of-table ids take the uniform row
+    ids[1][:5] = [V, -5, 3, V - 1, 0]
+    sc = oni.Scorer(theta, phi)
+    assert np.array_equal(sc.score(ids[0], ids[1]), oracle.score(ids[0], ids[1], theta, phi))
+    got = sc.score_flow_min(*ids)
+    want = oracle.score_flow_min(*ids, theta, phi)
+    assert np.array_equal(got, want)
+    assert sc.score(np.zeros(0, np.int32), np.zeros(0, np.int32)).shape == (0,)
+    sc.close()
+
+
+def test_topk_matches_oracle_with_ties(oni, oracle):
+    rng = np.random.default_rng(1)
+    n = 200000
+    base = rng.random(2000) * 1e-3
+    score = base[rng.integers(0, 2000, n)]           # heavy ties, as events sharing (ip, word) produce
+    sc = oni.Scorer(np.ones((1, 2)) / 2, np.ones((1, 2)) / 2)
+    for thr, k in [(1.0, 1000), (1e-4, 1000), (1e-4, -1), (0.0, 10), (5e-4, 1), (1.0, 300000), (base.min(), 50)]:
+        idx, s = sc.topk(score, thr, k)
+        ridx, rs = oracle.topk(score, thr, k)
+        assert np.array_equal(idx, ridx) and np.array_equal(s, rs), (thr, k)
+    idx, s = sc.topk(np.zeros(0), 1.0, 5)
+    assert len(idx) == 0
+    sc.close()
+
+
+def test_top1000_overlap_after_em(oni, oracle, corpusgen):
+    """End of the path: EM on the GPU vs the oracle, then score flow events and compare the 1000 most suspicious."""
+    g = corpusgen.generate(1500, 60, 1200, 20, seed=77, hub_tokens=3000)
+    c = oni.Corpus.from_csr(g.offsets, g.words, g.counts)
+    m = oni.Model.new(20, c.num_terms)
+    m.init_random(7)
+    m.alpha = 2.5
+    ref = oracle.run_em(g.offsets, g.words, g.counts, c.num_terms, 2.5, m.log_beta.copy(), oracle.settings(20, 1e-6, 4, 1e-6, 1))
+    em = oni.EM(c, m, oni.Settings(20, 1e-6, 4, 1e-6, 1))
+    keep = True
+    while keep:
+        _, _, keep = em.iterate()
+    theta, phi = oni.theta_from_gamma(em.gamma()), oni.phi_from_log_beta(em.model().log_beta)
+    theta_r, phi_r = oracle.theta_from_gamma(ref["gamma"]), oracle.phi_from_logbeta(ref["log_beta"])
+    ev = corpusgen.generate_flow_events(300000, theta_r, phi_r, seed=3)
+    sc = oni.Scorer(theta, phi)
+    mine = sc.score_flow_min(*ev)
+    want = oracle.score_flow_min(*ev, theta_r, phi_r)
+    assert np.max(np.abs(mine - want) / np.maximum(want, 1e-12)) < 1e-4
+    idx, s = sc.topk(mine, 1.0, 1000)
+    ridx, rs = oracle.topk(want, 1.0, 1000)
+    # tie-aware overlap: compare the multisets of (rounded) scores and the index sets
+    overlap = len(set(idx.tolist()) & set(ridx.tolist())) / 1000.0
+    assert overlap >= 0.99, overlap
+    sc.close()
+    em.close()
