@@ -210,6 +210,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD)
     ap.add_argument("--scale", type=float, default=1.0, help="development only: shrink the number of documents")
+    ap.add_argument("--hub-frac", type=float, default=None, help="development only: fraction of hub documents")
+    ap.add_argument("--no-e2e", action="store_true", help="development only")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-scoring", action="store_true")
     args = ap.parse_args()
@@ -228,6 +230,8 @@ def main():
     cfg = dict(WORKLOADS[args.workload])
     cfg["num_docs"] = max(1000, int(cfg["num_docs"] * args.scale))
     K, V = cfg["num_topics"], cfg["num_terms"]
+    if args.hub_frac is not None:
+        cfg["hub_frac"] = args.hub_frac
 
     if not torch.cuda.is_available() or oni.device_count() < 1:
         raise SystemExit("bench.py needs a CUDA device: libonilda has no CPU path")
@@ -352,15 +356,17 @@ def main():
         return out
 
     # the EM loop state must follow the iterations, not restart: reload() resets it, so carry it here
-    e2e_liks = []
-    for _ in range(args.warmup):
-        e2e_liks.append(e2e_step()[0])
-    barrier()
-    t_begin = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_liks.append(e2e_step()[0])
-    barrier()
-    e2e_elapsed = time.perf_counter() - t_begin
+    e2e_liks = [float("nan")]
+    e2e_elapsed = float("nan")
+    if not args.no_e2e:
+        for _ in range(args.warmup):
+            e2e_liks.append(e2e_step()[0])
+        barrier()
+        t_begin = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_liks.append(e2e_step()[0])
+        barrier()
+        e2e_elapsed = time.perf_counter() - t_begin
     if dist is not None:
         t = torch.tensor([e2e_elapsed], device=device, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

@@ -165,6 +165,9 @@ int onilda_em_get_model(onilda_em* em, onilda_model* out);
 int onilda_em_get_gamma(onilda_em* em, double* gamma_out);
 /* Per-document likelihood bound from the last estep ([doc_end-doc_begin]). */
 int onilda_em_get_doc_likelihood(onilda_em* em, double* out);
+/* Variational sweeps each document took in the last estep (lda_inference's var_iter,
+ * lda-inference.c:48): [doc_end-doc_begin]. */
+int onilda_em_get_doc_sweeps(onilda_em* em, int32_t* out);
 /* Counters of the last estep: kernel time in ms (CUDA events on the handle's
  * stream), number of kernel launches issued by the last estep+mstep pair, and
  * total variational sweeps summed over documents. */

@@ -104,6 +104,7 @@ def lib():
     L.onilda_em_get_model.argtypes = [_vp, _vp]
     L.onilda_em_get_gamma.argtypes = [_vp, _f64p]
     L.onilda_em_get_doc_likelihood.argtypes = [_vp, _f64p]
+    L.onilda_em_get_doc_sweeps.argtypes = [_vp, _i32p]
     L.onilda_em_stats.argtypes = [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int64),
                                   C.POINTER(C.c_int64)]
     L.onilda_em_stream.argtypes = [_vp]
@@ -237,10 +238,13 @@ class Model:
     @property
     def log_beta(self):
         """Writable numpy view [K][V] of the model's own storage."""
-        p = lib().onilda_model_log_beta(self._h)
-        if self.num_topics * self.num_terms == 0:
+        n = self.num_topics * self.num_terms
+        if n == 0:
             return np.zeros((self.num_topics, self.num_terms))
-        return np.ctypeslib.as_array(p, (self.num_topics, self.num_terms))
+        p = lib().onilda_model_log_beta(self._h)
+        buf = (C.c_double * n).from_address(C.addressof(p.contents))
+        buf._owner = self          # the view keeps the model (and its storage) alive
+        return np.frombuffer(buf, dtype=np.float64).reshape(self.num_topics, self.num_terms)
 
     def init_random(self, seed):
         _check(lib().onilda_model_init_random(self._h, seed))
@@ -310,6 +314,11 @@ class EM:
     def doc_likelihood(self):
         out = np.zeros(self.doc_end - self.doc_begin)
         _check(lib().onilda_em_get_doc_likelihood(self._h, out))
+        return out
+
+    def doc_sweeps(self):
+        out = np.zeros(self.doc_end - self.doc_begin, np.int32)
+        _check(lib().onilda_em_get_doc_sweeps(self._h, out))
         return out
 
     def stats(self, with_sweeps=False):

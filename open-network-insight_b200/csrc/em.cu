@@ -16,7 +16,10 @@ struct onilda_em {
     int device;
     int sm_count;
     cudaStream_t stream;
-    cudaEvent_t ev0, ev1, ev2, ev3;
+    cudaStream_t long_stream;   // long documents run beside the bulk launch
+    cudaEvent_t ev0, ev1, ev2, ev3, ev_fork, ev_join;
+    int64_t num_long;           // documents of at least long_len entries: prefix of d_order
+    int long_len, long_group;
     // shard
     int64_t doc_begin, doc_end, num_docs, nnz;
     int K, V;
@@ -38,7 +41,7 @@ struct onilda_em {
     double* d_phi;              // [nnz][kpad]
     double *d_gamma, *d_doc_lik, *d_doc_ass;
     int32_t* d_doc_sweeps;
-    unsigned long long* d_queue;
+    unsigned long long* d_queue;   // [2]: bulk, long
     int* d_error;
     double* d_kv;               // [K][V] staging for import / export
     // stats
@@ -143,6 +146,9 @@ extern "C" void onilda_em_destroy(onilda_em* em)
     if (em->ev1) cudaEventDestroy(em->ev1);
     if (em->ev2) cudaEventDestroy(em->ev2);
     if (em->ev3) cudaEventDestroy(em->ev3);
+    if (em->ev_fork) cudaEventDestroy(em->ev_fork);
+    if (em->ev_join) cudaEventDestroy(em->ev_join);
+    if (em->long_stream) cudaStreamDestroy(em->long_stream);
     if (em->stream) cudaStreamDestroy(em->stream);
     free(em);
 }
@@ -192,6 +198,9 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
     TRYCUDA(cudaEventCreate(&em->ev1));
     TRYCUDA(cudaEventCreate(&em->ev2));
     TRYCUDA(cudaEventCreate(&em->ev3));
+    TRYCUDA(cudaStreamCreateWithFlags(&em->long_stream, cudaStreamNonBlocking));
+    TRYCUDA(cudaEventCreateWithFlags(&em->ev_fork, cudaEventDisableTiming));
+    TRYCUDA(cudaEventCreateWithFlags(&em->ev_join, cudaEventDisableTiming));
 
     const int64_t D = em->num_docs, N = em->nnz;
     const size_t table = (size_t)em->V * lay.kpad;
@@ -211,7 +220,7 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
     TRY(dev_alloc(&em->d_doc_lik, (size_t)D));
     TRY(dev_alloc(&em->d_doc_ass, (size_t)D));
     TRY(dev_alloc(&em->d_doc_sweeps, (size_t)D));
-    TRY(dev_alloc(&em->d_queue, 1));
+    TRY(dev_alloc(&em->d_queue, 2));
     TRY(dev_alloc(&em->d_error, 1));
     TRY(dev_alloc(&em->d_kv, (size_t)em->K * em->V));
 
@@ -227,6 +236,18 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
         }
         std::vector<int32_t> order;
         order_by_length(off.data(), D, max_len, order);
+        // Long documents (a prefix of the order) get more lanes each and their own launch: the
+        // word-by-word chain of one document cannot be split, so the longest document bounds the
+        // E-step; fewer topics per lane makes each of its steps shorter.
+        const char* env_len = getenv("ONILDA_LONG_LEN");
+        const char* env_grp = getenv("ONILDA_LONG_GROUP");
+        em->long_len = env_len ? atoi(env_len) : 1024;
+        em->long_group = env_grp ? atoi(env_grp) : (lay.group * 2 <= 32 ? lay.group * 2 : 32);
+        if (em->long_group < lay.group || (em->long_group & (em->long_group - 1)) || em->long_group > 32) em->long_group = lay.group;
+        if ((em->K + em->long_group - 1) / em->long_group > 8) em->long_group = lay.group;
+        em->num_long = 0;
+        if (em->long_len > 0 && em->long_group != lay.group)
+            while (em->num_long < D && off[(size_t)order[(size_t)em->num_long] + 1] - off[(size_t)order[(size_t)em->num_long]] >= em->long_len) em->num_long++;
         TRYCUDA(cudaMemcpyAsync(em->d_offsets, off.data(), sizeof(int64_t) * (size_t)(D + 1), cudaMemcpyHostToDevice, em->stream));
         if (D > 0) {
             TRYCUDA(cudaMemcpyAsync(em->d_totals, c->totals + doc_begin, sizeof(int32_t) * (size_t)D, cudaMemcpyHostToDevice, em->stream));
@@ -283,8 +304,8 @@ static int run_estep(onilda_em* em, bool accumulate)
     }
     EStepArgs a;
     a.offsets = em->d_offsets; a.words = em->d_words; a.counts = em->d_counts; a.totals = em->d_totals;
-    a.order = em->d_order; a.num_docs = em->num_docs;
-    a.beta_scaled = em->d_beta_scaled; a.lbmax = em->d_lbmax; a.num_topics = em->K;
+    a.order = em->d_order;
+    a.beta_scaled = em->d_beta_scaled; a.lbmax = em->d_lbmax; a.num_topics = em->K; a.kstride = em->lay.kpad;
     a.alpha = em->alpha;
     a.lik_const = lgamma(em->alpha * em->K) - em->K * lgamma(em->alpha);
     a.var_max_iter = em->var_max_iter;
@@ -292,9 +313,24 @@ static int run_estep(onilda_em* em, bool accumulate)
     a.phi = em->d_phi; a.gamma = em->d_gamma; a.doc_lik = em->d_doc_lik; a.doc_alpha_ss = em->d_doc_ass;
     a.doc_sweeps = em->d_doc_sweeps;
     a.class_word = accumulate ? em->d_ss : nullptr;
-    a.queue = em->d_queue; a.error_flag = em->d_error;
-    int rc = launch_estep(em->lay, a, em->sm_count, em->stream, &l);
+    a.error_flag = em->d_error;
+    ONILDA_CUDA(cudaMemsetAsync(em->d_queue, 0, 2 * sizeof(unsigned long long), em->stream));
+    int rc;
+    if (em->num_long > 0) {
+        // fork: long documents first, on their own stream, one warp per block so that the block
+        // scheduler spreads them over the SMs; the bulk launch fills the rest of the machine
+        ONILDA_CUDA(cudaEventRecord(em->ev_fork, em->stream));
+        ONILDA_CUDA(cudaStreamWaitEvent(em->long_stream, em->ev_fork, 0));
+        EStepArgs b = a;
+        b.order_begin = 0; b.order_count = em->num_long; b.queue = em->d_queue + 1;
+        rc = launch_estep(em->long_group, b, em->sm_count, 32, em->long_stream, &l);
+        if (rc != ONILDA_OK) return rc;
+        ONILDA_CUDA(cudaEventRecord(em->ev_join, em->long_stream));
+    }
+    a.order_begin = em->num_long; a.order_count = em->num_docs - em->num_long; a.queue = em->d_queue;
+    rc = launch_estep(em->lay.group, a, em->sm_count, 128, em->stream, &l);
     if (rc != ONILDA_OK) return rc;
+    if (em->num_long > 0) ONILDA_CUDA(cudaStreamWaitEvent(em->stream, em->ev_join, 0));
     rc = launch_reduce_doc_stats(em->d_doc_lik, em->d_doc_ass, em->num_docs, em->d_partial, em->d_ss + table, em->stream, &l);
     if (rc != ONILDA_OK) return rc;
     ONILDA_CUDA(cudaEventRecord(em->ev1, em->stream));
@@ -401,6 +437,16 @@ extern "C" int onilda_em_get_doc_likelihood(onilda_em* em, double* out)
     DeviceGuard g(em->device);
     if (em->num_docs > 0)
         ONILDA_CUDA(cudaMemcpyAsync(out, em->d_doc_lik, sizeof(double) * (size_t)em->num_docs, cudaMemcpyDeviceToHost, em->stream));
+    ONILDA_CUDA(cudaStreamSynchronize(em->stream));
+    return ONILDA_OK;
+}
+
+extern "C" int onilda_em_get_doc_sweeps(onilda_em* em, int32_t* out)
+{
+    if (!em || (!out && em->num_docs > 0)) return onilda_fail(ONILDA_EINVAL, "em_get_doc_sweeps: null argument");
+    DeviceGuard g(em->device);
+    if (em->num_docs > 0)
+        ONILDA_CUDA(cudaMemcpyAsync(out, em->d_doc_sweeps, sizeof(int32_t) * (size_t)em->num_docs, cudaMemcpyDeviceToHost, em->stream));
     ONILDA_CUDA(cudaStreamSynchronize(em->stream));
     return ONILDA_OK;
 }

@@ -21,7 +21,8 @@
 // beta'[w][k] = exp(log_beta[k][w] - lbmax[w]) built once per EM iteration,
 //     phi_nk = E_k beta'_kw / s_n,   s_n = sum_j E_j beta'_jw
 // which is the reference's exp(psi_k + log_beta_kw - log_sum) without a
-// log_sum/exp per (word, topic): one log per WORD (log s_n) remains.  shift is
+// log_sum/exp per (word, topic): one log per WORD (log s_n) remains.  Per (word,
+// topic) the update costs one reciprocal, one exp and one log (device_math.cuh).  shift is
 // psi(alpha + total/K), the value every topic starts from, so E starts at 1 and
 // s_n can neither overflow nor vanish in practice; if it ever leaves
 // [1e-290, 1e290] that word is redone in log space (the reference's own form).
@@ -36,25 +37,28 @@
 
 namespace onilda {
 
+// Sum / max over the G lanes of a group.  Always executed by the whole warp with the full
+// mask (the kernel keeps its warps converged in the hot loop; partial-mask shuffles cost a
+// MATCH/VOTE/branch sequence each).
 template <int G>
-__device__ __forceinline__ double group_sum(double v, unsigned mask)
+__device__ __forceinline__ double group_sum(double v)
 {
 #pragma unroll
-    for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(mask, v, o);
+    for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
 }
 
 template <int G>
-__device__ __forceinline__ double group_max(double v, unsigned mask)
+__device__ __forceinline__ double group_max(double v)
 {
 #pragma unroll
-    for (int o = G / 2; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(mask, v, o));
+    for (int o = G / 2; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
 }
 
 template <int TPL>
 struct WordItem {
-    int word;
+    int word;            // -1: this group idles at this word
     double count;
     double lbmax;
     double beta[TPL];
@@ -65,16 +69,18 @@ template <int G, int TPL>
 __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long long num_bundles)
 {
     constexpr int DPW = 32 / G;      // documents per warp
-    constexpr int KPAD = G * TPL;
     const int lane = threadIdx.x & 31;
     const int grp = lane / G;
     const int j = lane % G;
-    const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (grp * G));
     const int K = a.num_topics;
+    const int KS = a.kstride;
     const double inv_K = 1.0 / K;
     bool valid[TPL];
 #pragma unroll
     for (int t = 0; t < TPL; t++) valid[t] = (t * G + j) < K;
+
+    const double* __restrict__ beta_scaled = a.beta_scaled;
+    double* __restrict__ phi = a.phi;
 
     for (;;) {
         unsigned long long bundle = 0;
@@ -83,8 +89,8 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
         if (bundle >= num_bundles) break;
 
         const int64_t slot = (int64_t)bundle * DPW + grp;
-        const bool has_doc = slot < a.num_docs;
-        const int64_t d = has_doc ? a.order[slot] : 0;
+        const bool has_doc = slot < a.order_count;
+        const int64_t d = has_doc ? a.order[a.order_begin + slot] : 0;
         const int64_t beg = has_doc ? a.offsets[d] : 0;
         const int len = has_doc ? (int)(a.offsets[d + 1] - beg) : 0;
         const int total = has_doc ? a.totals[d] : 0;
@@ -107,9 +113,6 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
         int sweeps = 0;
         bool active = has_doc && (converged > a.var_converged) && ((0 < a.var_max_iter) || (a.var_max_iter == -1));
 
-        const double* __restrict__ beta_scaled = a.beta_scaled;
-        double* __restrict__ phi = a.phi;
-
         while (__any_sync(0xffffffffu, active)) {
             if (active) sweeps++;
             const bool first = (sweeps == 1);   // same for every active group of the warp
@@ -118,91 +121,110 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
 #pragma unroll
             for (int t = 0; t < TPL; t++) acc_psi[t] = 0.0;
 
-            auto load_item = [&](int n, WordItem<TPL>& it) {
+            // Two-stage software pipeline over the words: ids (word, count) are fetched two words
+            // ahead, the rows they select (beta', old phi, lbmax) one word ahead, so neither load
+            // latency nor the id -> address dependency sits on the serial update chain.
+            // A group that is idle at word n (document shorter than the bundle's longest, or already
+            // converged) still runs the arithmetic, on count = 0 and beta' = 1: every update is then
+            // multiplied by zero and nothing of it is stored.  That keeps the warp converged.
+            auto load_ids = [&](int n, int& w, int& c) {
                 const bool on = active && n < len;
-                const int64_t e = beg + n;
-                it.word = on ? a.words[e] : 0;
-                it.count = on ? (double)a.counts[e] : 0.0;
-                it.lbmax = on ? a.lbmax[it.word] : 0.0;
-                const double* brow = beta_scaled + (int64_t)it.word * KPAD + j;
-                const double* prow = phi + e * KPAD + j;
+                w = on ? a.words[beg + n] : -1;
+                c = on ? a.counts[beg + n] : 0;
+            };
+            auto load_rows = [&](int n, int w, int c, WordItem<TPL>& it) {
+                const bool on = w >= 0;
+                it.word = w;
+                it.count = (double)c;
+                it.lbmax = on ? a.lbmax[w] : 0.0;
+                const double* brow = beta_scaled + (int64_t)w * KS + j;
+                const double* prow = phi + (beg + n) * KS + j;
 #pragma unroll
                 for (int t = 0; t < TPL; t++) {
-                    it.beta[t] = on ? __ldg(brow + t * G) : 0.0;
-                    it.old_phi[t] = first ? (valid[t] ? inv_K : 0.0) : (on ? prow[t * G] : 0.0);
+                    it.beta[t] = (on && valid[t]) ? __ldg(brow + t * G) : (valid[t] ? 1.0 : 0.0);
+                    it.old_phi[t] = (first || !on || !valid[t]) ? (valid[t] ? inv_K : 0.0) : prow[t * G];
                 }
             };
 
+            int w1, c1, w2 = -1, c2 = 0;
             WordItem<TPL> cur, nxt;
-            load_item(0, nxt);
+            load_ids(0, w1, c1);
+            load_rows(0, w1, c1, nxt);
+            load_ids(1, w1, c1);
             for (int n = 0; n < max_len; n++) {
                 cur = nxt;
-                if (n + 1 < max_len) load_item(n + 1, nxt);
-                if (active && n < len) {
-                    double x[TPL], part = 0.0;
-#pragma unroll
-                    for (int t = 0; t < TPL; t++) {
-                        x[t] = E[t] * cur.beta[t];
-                        part += x[t];
-                    }
-                    double s = group_sum<G>(part, gmask);
-                    double lse;   // log sum_k exp(psi_k + log_beta_kw) minus shift
-                    if (s > 1e-290 && s < 1e290) {
-                        const double inv = 1.0 / s;
-#pragma unroll
-                        for (int t = 0; t < TPL; t++) x[t] *= inv;
-                        lse = cur.lbmax + log(s);
-                    } else {
-                        // rare: redo this word in log space, as the reference does (lda-inference.c:52-68)
-                        double av[TPL], m = -INFINITY;
-#pragma unroll
-                        for (int t = 0; t < TPL; t++) {
-                            av[t] = (valid[t] && cur.beta[t] > 0.0) ? (psi[t] - shift) + log(cur.beta[t]) : -INFINITY;
-                            m = fmax(m, av[t]);
-                        }
-                        m = group_max<G>(m, gmask);
-                        double ps = 0.0;
-#pragma unroll
-                        for (int t = 0; t < TPL; t++) {
-                            x[t] = (av[t] > -INFINITY) ? exp(av[t] - m) : 0.0;
-                            ps += x[t];
-                        }
-                        ps = group_sum<G>(ps, gmask);
-                        const double inv = 1.0 / ps;
-#pragma unroll
-                        for (int t = 0; t < TPL; t++) x[t] *= inv;
-                        lse = cur.lbmax + m + log(ps);
-                    }
-                    double* prow = phi + (beg + n) * KPAD + j;
-#pragma unroll
-                    for (int t = 0; t < TPL; t++) {
-                        const double p = x[t];
-                        prow[t * G] = p;
-                        acc_psi[t] = fma(cur.count * p, psi[t], acc_psi[t]);
-                        gam[t] = gam[t] + cur.count * (p - cur.old_phi[t]);
-                        const DigammaParts dp = digamma_rational(gam[t]);
-                        psi[t] = dp.rational + log(dp.y);
-                        E[t] = valid[t] ? exp(psi[t] - shift) : 0.0;
-                    }
-                    acc_lse = fma(cur.count, lse, acc_lse);
-                    count_sum += cur.count;
-                }
-            }
+                load_ids(n + 2, w2, c2);
+                load_rows(n + 1, w1, c1, nxt);
+                w1 = w2;
+                c1 = c2;
+                const bool on = cur.word >= 0;
 
-            if (active) {
-                // likelihood bound of this sweep (lda-inference.c:93-127, see header)
-                double gs = 0.0, lg = 0.0, ap = 0.0;
+                double x[TPL], part = 0.0;
 #pragma unroll
                 for (int t = 0; t < TPL; t++) {
-                    if (valid[t]) {
-                        gs += gam[t];
-                        lg += lgamma(gam[t]);
-                    }
-                    ap += acc_psi[t];
+                    x[t] = E[t] * cur.beta[t];
+                    part += x[t];
                 }
-                gs = group_sum<G>(gs, gmask);
-                lg = group_sum<G>(lg, gmask);
-                ap = group_sum<G>(ap, gmask);
+                const double s = group_sum<G>(part);
+                const bool bad = !(s > 1e-290 && s < 1e290);
+                double inv = fast_rcp(s);
+                double lse = cur.lbmax + fast_log(s);    // log sum_k exp(psi_k + log_beta_kw), minus shift
+                if (__any_sync(0xffffffffu, bad)) {
+                    // rare: redo this word in log space, as the reference does (lda-inference.c:52-68)
+                    double av[TPL], m = -INFINITY;
+#pragma unroll
+                    for (int t = 0; t < TPL; t++) {
+                        av[t] = (valid[t] && cur.beta[t] > 0.0) ? (psi[t] - shift) + log(cur.beta[t]) : -INFINITY;
+                        m = fmax(m, av[t]);
+                    }
+                    m = group_max<G>(m);
+                    double y[TPL], ps = 0.0;
+#pragma unroll
+                    for (int t = 0; t < TPL; t++) {
+                        y[t] = (av[t] > -INFINITY) ? exp(av[t] - m) : 0.0;
+                        ps += y[t];
+                    }
+                    ps = group_sum<G>(ps);
+                    if (bad) {
+#pragma unroll
+                        for (int t = 0; t < TPL; t++) x[t] = y[t];
+                        inv = 1.0 / ps;
+                        lse = cur.lbmax + m + log(ps);
+                    }
+                }
+                double* prow = phi + (beg + n) * KS + j;
+#pragma unroll
+                for (int t = 0; t < TPL; t++) {
+                    const double p = x[t] * inv;
+                    if (on && valid[t]) prow[t * G] = p;
+                    const double cp = cur.count * p;
+                    acc_psi[t] = fma(cp, psi[t], acc_psi[t]);
+                    gam[t] = gam[t] + cur.count * (p - cur.old_phi[t]);
+                    const DigammaParts dp = digamma_rational(gam[t]);
+                    // E = exp(psi - shift) = y * exp(rational - shift): the logarithm stays off the
+                    // E -> s -> phi -> gamma -> E recurrence; psi itself is only needed by acc_psi
+                    E[t] = valid[t] ? dp.y * fast_exp(dp.rational - shift) : 0.0;
+                    psi[t] = dp.rational + fast_log(dp.y);
+                }
+                acc_lse = fma(cur.count, lse, acc_lse);
+                count_sum += cur.count;
+            }
+
+            // likelihood bound of this sweep (lda-inference.c:93-127, see header); computed by every
+            // group, used by the active ones
+            double gs = 0.0, lg = 0.0, ap = 0.0;
+#pragma unroll
+            for (int t = 0; t < TPL; t++) {
+                if (valid[t]) {
+                    gs += gam[t];
+                    lg += lgamma(gam[t]);
+                }
+                ap += acc_psi[t];
+            }
+            gs = group_sum<G>(gs);
+            lg = group_sum<G>(lg);
+            ap = group_sum<G>(ap);
+            if (active) {
                 lik = a.lik_const - lgamma(gs) + lg - ap + (acc_lse + shift * count_sum);
                 if (isnan(lik)) *a.error_flag = 1;   // the reference asserts here (lda-inference.c:78)
                 converged = (lik_old - lik) / lik_old;
@@ -211,38 +233,36 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
             }
         }
 
-        if (has_doc) {
-            // doc_e_step (lda-estimate.c:40-46): alpha_suffstats += sum_k psi(gamma_k) - K psi(sum gamma)
-            double gs = 0.0, ps = 0.0;
+        // doc_e_step (lda-estimate.c:40-46): alpha_suffstats += sum_k psi(gamma_k) - K psi(sum gamma)
+        double gs = 0.0, ps = 0.0;
 #pragma unroll
-            for (int t = 0; t < TPL; t++) {
-                if (valid[t]) {
-                    gs += gam[t];
-                    ps += psi[t];
-                    a.gamma[d * K + t * G + j] = gam[t];
-                }
+        for (int t = 0; t < TPL; t++) {
+            if (valid[t]) {
+                gs += gam[t];
+                ps += psi[t];
+                if (has_doc) a.gamma[d * K + t * G + j] = gam[t];
             }
-            gs = group_sum<G>(gs, gmask);
-            ps = group_sum<G>(ps, gmask);
-            if (j == 0) {
-                a.doc_lik[d] = lik;
-                a.doc_alpha_ss[d] = ps - K * digamma(gs);
-                a.doc_sweeps[d] = sweeps;
-            }
-            // class_word[k][w] += c_n phi_nk (lda-estimate.c:48-55); class_total is the column sum (mstep.cu)
-            if (a.class_word != nullptr) {
-                for (int n = 0; n < len; n++) {
-                    const int64_t e = beg + n;
-                    const int w = a.words[e];
-                    const double c = (double)a.counts[e];
-                    const double* prow = phi + e * KPAD + j;
-                    double* crow = a.class_word + (int64_t)w * KPAD + j;
+        }
+        gs = group_sum<G>(gs);
+        ps = group_sum<G>(ps);
+        if (has_doc && j == 0) {
+            a.doc_lik[d] = lik;
+            a.doc_alpha_ss[d] = ps - K * digamma(gs);
+            a.doc_sweeps[d] = sweeps;
+        }
+        // class_word[k][w] += c_n phi_nk (lda-estimate.c:48-55); class_total is the column sum (mstep.cu)
+        if (a.class_word != nullptr) {
+            for (int n = 0; n < len; n++) {
+                const int64_t e = beg + n;
+                const int w = a.words[e];
+                const double c = (double)a.counts[e];
+                const double* prow = phi + e * KS + j;
+                double* crow = a.class_word + (int64_t)w * KS + j;
 #pragma unroll
-                    for (int t = 0; t < TPL; t++) {
-                        if (valid[t]) {
-                            const double p = (sweeps == 0) ? inv_K : prow[t * G];
-                            atomicAdd(crow + t * G, c * p);
-                        }
+                for (int t = 0; t < TPL; t++) {
+                    if (valid[t]) {
+                        const double p = (sweeps == 0) ? inv_K : prow[t * G];
+                        atomicAdd(crow + t * G, c * p);
                     }
                 }
             }
@@ -250,51 +270,58 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
     }
 }
 
+// Grid for `num_bundles` bundles of one (G, TPL) instantiation: persistent, at most the resident
+// capacity of `sm_count` SMs (or `max_blocks` when the launch shares the device with another).
 template <int G, int TPL>
-static int launch_one(const EStepArgs& args, int sm_count, cudaStream_t stream)
+static int launch_one(const EStepArgs& args, int sm_count, int block_threads, cudaStream_t stream)
 {
     constexpr int DPW = 32 / G;
-    const unsigned long long num_bundles = (unsigned long long)((args.num_docs + DPW - 1) / DPW);
+    const unsigned long long num_bundles = (unsigned long long)((args.order_count + DPW - 1) / DPW);
     if (num_bundles == 0) return ONILDA_OK;
     int per_sm = 0;
-    ONILDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_kernel<G, TPL>, 128, 0));
+    ONILDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_kernel<G, TPL>, block_threads, 0));
     if (per_sm < 1) per_sm = 1;
-    unsigned long long want = (num_bundles + 3) / 4;   // 4 warps per block
+    const unsigned long long wpb = (unsigned long long)(block_threads / 32);
+    unsigned long long want = (num_bundles + wpb - 1) / wpb;
     unsigned long long grid = (unsigned long long)sm_count * per_sm;
     if (grid > want) grid = want;
-    estep_kernel<G, TPL><<<(unsigned)grid, 128, 0, stream>>>(args, num_bundles);
+    estep_kernel<G, TPL><<<(unsigned)grid, block_threads, 0, stream>>>(args, num_bundles);
     ONILDA_CUDA(cudaGetLastError());
     return ONILDA_OK;
 }
 
 template <int G>
-static int launch_group(int tpl, const EStepArgs& args, int sm_count, cudaStream_t stream)
+static int launch_group(int tpl, const EStepArgs& args, int sm_count, int block_threads, cudaStream_t stream)
 {
     switch (tpl) {
-        case 1: return launch_one<G, 1>(args, sm_count, stream);
-        case 2: return launch_one<G, 2>(args, sm_count, stream);
-        case 3: return launch_one<G, 3>(args, sm_count, stream);
-        case 4: return launch_one<G, 4>(args, sm_count, stream);
-        case 5: return launch_one<G, 5>(args, sm_count, stream);
-        case 6: return launch_one<G, 6>(args, sm_count, stream);
-        case 7: return launch_one<G, 7>(args, sm_count, stream);
-        case 8: return launch_one<G, 8>(args, sm_count, stream);
+        case 1: return launch_one<G, 1>(args, sm_count, block_threads, stream);
+        case 2: return launch_one<G, 2>(args, sm_count, block_threads, stream);
+        case 3: return launch_one<G, 3>(args, sm_count, block_threads, stream);
+        case 4: return launch_one<G, 4>(args, sm_count, block_threads, stream);
+        case 5: return launch_one<G, 5>(args, sm_count, block_threads, stream);
+        case 6: return launch_one<G, 6>(args, sm_count, block_threads, stream);
+        case 7: return launch_one<G, 7>(args, sm_count, block_threads, stream);
+        case 8: return launch_one<G, 8>(args, sm_count, block_threads, stream);
     }
     return onilda_fail(ONILDA_EINVAL, "unsupported topics-per-lane %d", tpl);
 }
 
-int launch_estep(const TopicLayout& lay, const EStepArgs& args, int sm_count, cudaStream_t stream, int* launches)
+// One launch over documents order[order_begin, order_begin + order_count) with `group` lanes per
+// document and `block_threads` (32..128) threads per block.  args.queue must be zero (the caller
+// clears it on the same stream).
+int launch_estep(int group, const EStepArgs& args, int sm_count, int block_threads, cudaStream_t stream, int* launches)
 {
-    ONILDA_CUDA(cudaMemsetAsync(args.queue, 0, sizeof(unsigned long long), stream));
+    if (args.order_count <= 0) return ONILDA_OK;
+    const int tpl = (args.num_topics + group - 1) / group;
     int rc;
-    switch (lay.group) {
-        case 4: rc = launch_group<4>(lay.tpl, args, sm_count, stream); break;
-        case 8: rc = launch_group<8>(lay.tpl, args, sm_count, stream); break;
-        case 16: rc = launch_group<16>(lay.tpl, args, sm_count, stream); break;
-        case 32: rc = launch_group<32>(lay.tpl, args, sm_count, stream); break;
-        default: return onilda_fail(ONILDA_EINVAL, "unsupported lane group %d", lay.group);
+    switch (group) {
+        case 4: rc = launch_group<4>(tpl, args, sm_count, block_threads, stream); break;
+        case 8: rc = launch_group<8>(tpl, args, sm_count, block_threads, stream); break;
+        case 16: rc = launch_group<16>(tpl, args, sm_count, block_threads, stream); break;
+        case 32: rc = launch_group<32>(tpl, args, sm_count, block_threads, stream); break;
+        default: return onilda_fail(ONILDA_EINVAL, "unsupported lane group %d", group);
     }
-    if (rc == ONILDA_OK && launches && args.num_docs > 0) *launches += 1;
+    if (rc == ONILDA_OK && launches) *launches += 1;
     return rc;
 }
 

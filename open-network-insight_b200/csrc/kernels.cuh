@@ -47,17 +47,19 @@ struct EStepArgs {
     const int32_t* counts;
     const int32_t* totals;
     const int32_t* order;       // documents by decreasing length
-    int64_t num_docs;
+    int64_t order_begin;        // this launch works on order[order_begin, order_begin + order_count)
+    int64_t order_count;
     // model tables, word-major [V][kpad]
     const double* beta_scaled;  // exp(log_beta[w][k] - lbmax[w]); 0 in padding
     const double* lbmax;        // [V] max_k log_beta[w][k]
     int num_topics;
+    int kstride;                // row stride of the tables and of phi, in doubles (TopicLayout::kpad)
     double alpha;
     double lik_const;           // lgamma(alpha*K) - K*lgamma(alpha)
     int var_max_iter;
     double var_converged;       // the reference's float threshold, widened
     // scratch and outputs
-    double* phi;                // [nnz][kpad]
+    double* phi;                // [nnz][kstride]
     double* gamma;              // [D][K]
     double* doc_lik;            // [D]
     double* doc_alpha_ss;       // [D]
@@ -67,7 +69,7 @@ struct EStepArgs {
     int* error_flag;            // set to 1 on a NaN likelihood
 };
 
-int launch_estep(const TopicLayout& lay, const EStepArgs& args, int sm_count, cudaStream_t stream, int* launches);
+int launch_estep(int group, const EStepArgs& args, int sm_count, int block_threads, cudaStream_t stream, int* launches);
 
 // M-step and table kernels (mstep.cu)
 int launch_tables_from_log_beta(const double* log_beta_kv, int K, int V, const TopicLayout& lay, double* log_beta_wk,

@@ -491,6 +491,24 @@ int oracle_run_em(int64_t D, const int64_t* offsets, const int32_t* words, const
     return 0;
 }
 
+/* Sweeps (var_iter, lda-inference.c:48) each document takes with a fixed model; test aid. */
+int oracle_doc_sweeps(int64_t D, const int64_t* offsets, const int32_t* words, const int32_t* counts,
+                      const int32_t* totals, int K, int V, double alpha, const double* log_beta,
+                      int var_max_iter, float var_converged, int32_t* sweeps_out)
+{
+    double* gamma = malloc(sizeof(double) * (size_t)K);
+    for (int64_t d = 0; d < D; d++) {
+        int len = (int)(offsets[d + 1] - offsets[d]), it = 0;
+        double* phi = malloc(sizeof(double) * (size_t)(len > 0 ? len : 1) * K);
+        oracle_lda_inference(len, words + offsets[d], counts + offsets[d], totals[d], K, V, alpha, log_beta,
+                             var_max_iter, var_converged, gamma, phi, &it);
+        sweeps_out[d] = it;
+        free(phi);
+    }
+    free(gamma);
+    return 0;
+}
+
 /* infer (lda-estimate.c:358-388) */
 int oracle_infer(int64_t D, const int64_t* offsets, const int32_t* words, const int32_t* counts,
                  const int32_t* totals, int K, int V, double alpha, const double* log_beta,

@@ -93,6 +93,10 @@ int oracle_run_em(int64_t D, const int64_t* offsets, const int32_t* words, const
                   const oracle_settings* settings, int nproc, double* gamma,
                   double* lik, double* conv, int* n_iter);
 
+int oracle_doc_sweeps(int64_t D, const int64_t* offsets, const int32_t* words, const int32_t* counts,
+                      const int32_t* totals, int K, int V, double alpha, const double* log_beta,
+                      int var_max_iter, float var_converged, int32_t* sweeps_out);
+
 /* infer (lda-estimate.c:358-388): per-document likelihood + gamma with a fixed model. */
 int oracle_infer(int64_t D, const int64_t* offsets, const int32_t* words, const int32_t* counts,
                  const int32_t* totals, int K, int V, double alpha, const double* log_beta,

@@ -78,6 +78,8 @@ def lib():
                                 _f64p, C.POINTER(Settings), C.c_int, _f64p, _f64p, _f64p, C.POINTER(C.c_int)]
     L.oracle_infer.argtypes = [C.c_int64, _i64p, _i32p, _i32p, _i32p, C.c_int, C.c_int, C.c_double, _f64p,
                                C.POINTER(Settings), _f64p, _f64p]
+    L.oracle_doc_sweeps.argtypes = [C.c_int64, _i64p, _i32p, _i32p, _i32p, C.c_int, C.c_int, C.c_double, _f64p,
+                                    C.c_int, C.c_float, _i32p]
     L.oracle_set_threads.argtypes = [C.c_int]
     L.oracle_theta_from_gamma.argtypes = [C.c_int64, C.c_int, _f64p, _f64p]
     L.oracle_phi_from_logbeta.argtypes = [C.c_int, C.c_int, _f64p, _f64p]
@@ -175,6 +177,14 @@ def e_step(offsets, words, counts, V, alpha, log_beta, var_max_iter, var_converg
                           doc_lik.ctypes.data_as(C.c_void_p))
     return dict(gamma=gamma, class_word=cw, class_total=ct, alpha_ss=a_ss.value, num_docs=nd.value,
                 lik=lik, doc_lik=doc_lik)
+
+
+def doc_sweeps(offsets, words, counts, V, alpha, log_beta, var_max_iter, var_converged):
+    D = len(offsets) - 1
+    out = np.zeros(D, np.int32)
+    lib().oracle_doc_sweeps(D, offsets, words, counts, totals_of(offsets, counts), log_beta.shape[0], V, alpha,
+                            np.ascontiguousarray(log_beta), var_max_iter, var_converged, out)
+    return out
 
 
 def infer(offsets, words, counts, V, alpha, log_beta, st: Settings):

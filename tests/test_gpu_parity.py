@@ -62,6 +62,42 @@ def test_single_estep_against_oracle(oni, oracle, case):
 
 
 @pytest.mark.parametrize("case", CASES)
+def test_sweep_counts_match_oracle(oni, oracle, case):
+    """Per-document convergence bookkeeping: the number of sweeps each document takes (lda-inference.c:46-48)."""
+    d, c, m, st = load_case(oni, case)
+    off, w, cn, tot, V = oracle.read_dat(d / "c.dat")
+    alpha, lb = oracle.load_model(d / "000")
+    want = oracle.doc_sweeps(off, w, cn, V, alpha, lb, st.var_max_iter, st.var_converged)
+    em = oni.EM(c, m, st)
+    em.estep()
+    got = em.doc_sweeps()
+    # a document whose last relative change lands within rounding of the 1e-6 threshold may differ by one sweep
+    assert np.mean(got != want) <= 0.01 and np.max(np.abs(got - want)) <= 1
+    em.close()
+
+
+@pytest.mark.parametrize("group", [8, 16, 32])
+def test_long_document_path(oni, oracle, group, monkeypatch):
+    """Every document through the long-document launch (more lanes per document, own stream)."""
+    monkeypatch.setenv("ONILDA_LONG_LEN", "1")
+    monkeypatch.setenv("ONILDA_LONG_GROUP", str(group))
+    d, c, m, st = load_case(oni, "k20")
+    off, w, cn, tot, V = oracle.read_dat(d / "c.dat")
+    alpha, lb = oracle.load_model(d / "000")
+    ref = oracle.e_step(off, w, cn, V, alpha, lb, st.var_max_iter, st.var_converged)
+    em = oni.EM(c, m, st)
+    em.estep()
+    assert rel_err(em.doc_likelihood(), ref["doc_lik"], 1e-9) < 1e-10
+    assert rel_err(em.gamma(), ref["gamma"], 1e-9) < 1e-9
+    lik, _, _ = em.mstep()
+    assert abs(lik - ref["lik"]) / abs(ref["lik"]) < 1e-12
+    lb_ref = np.zeros_like(lb)
+    oracle.lib().oracle_lda_mle(lb.shape[0], V, ref["class_word"], ref["class_total"], lb_ref)
+    assert rel_err(em.model().log_beta, lb_ref, 1e-6) < 1e-8
+    em.close()
+
+
+@pytest.mark.parametrize("case", CASES)
 def test_full_em_against_reference_files(oni, case, tmp_path):
     """The whole run from 000 against what the reference binary wrote (likelihood.dat, final.*)."""
     d, c, m, st = load_case(oni, case)
@@ -88,7 +124,7 @@ def test_full_em_against_reference_files(oni, case, tmp_path):
 
 
 @pytest.mark.parametrize("case", ["k5", "k20"])
-def test_lda_program_drop_in(oni, case, tmp_path):
+def test_lda_program_drop_in(oni, oracle, case, tmp_path):
     """`lda est` / `lda inf` with the reference's argv, files compared with the reference's."""
     d = GOLD / case
     K = int((d / "000.other").read_text().split()[1])
@@ -96,8 +132,11 @@ def test_lda_program_drop_in(oni, case, tmp_path):
     r = subprocess.run([str(oni.LDA_BIN), "est", "2.5", str(K), str(d / "settings.txt"), "1", str(d / "c.dat"),
                         str(d / "000"), str(out)], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
-    assert (out / "000.beta").read_bytes() == (d / "000.beta").read_bytes()     # float-parsed model re-serialises identically
-    assert (out / "000.other").read_bytes() == (d / "000.other").read_bytes()
+    # 000.* is the float-parsed start model written back (lda-estimate.c:163-170)
+    a0, lb0 = oracle.load_model(d / "000")
+    oracle.save_model(tmp_path / "o000", a0, lb0)
+    assert (out / "000.beta").read_bytes() == (tmp_path / "o000.beta").read_bytes()
+    assert (out / "000.other").read_bytes() == (tmp_path / "o000.other").read_bytes()
     mine, ref = np.loadtxt(out / "likelihood.dat", ndmin=2), np.loadtxt(d / "likelihood.dat", ndmin=2)
     assert mine.shape == ref.shape
     assert np.max(np.abs(mine[:, 0] - ref[:, 0]) / np.abs(ref[:, 0])) < LIK_RTOL
