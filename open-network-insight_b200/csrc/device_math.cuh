@@ -133,13 +133,13 @@ ONILDA_HD double fast_log(double x)
     return fma(ed, kLn2[0], r);
 }
 
-// exp(x) for x <= ~700 (any finite x below that; very negative x gives a tiny positive value or 0).
+// exp(x) for x <= ~700.  Very negative x gives a tiny positive value (about 2^-1021), never NaN:
+// the binary exponent is clamped as an integer, which keeps the clamp off the FP64 dependency chain.
 ONILDA_HD double fast_exp(double x)
 {
-    x = fmax(x, -707.0);
     const double magic = 6755399441055744.0;            // 1.5 * 2^52: round-to-nearest-integer trick
     const double t = fma(x, kLn2[2], magic);
-    const int k = double_lo(t);
+    int k = double_lo(t);
     const double kd = t - magic;
     double r = fma(kd, -kLn2[0], x);
     r = fma(kd, -kLn2[1], r);
@@ -156,7 +156,10 @@ ONILDA_HD double fast_exp(double x)
     const double q4567 = fma(q67, r2, q45);
     const double q89ab = fma(qab, r2, q89);
     const double r8 = r4 * r4;
-    const double q = fma(q89ab, r8, fma(q4567, r4, q0123));
+    double q = fma(q89ab, r8, fma(q4567, r4, q0123));
+    // x below about -1e15 would make r meaningless; such x only ever mean "zero"
+    q = (x > -1.0e9) ? q : 1.0;
+    k = k > -1021 ? k : -1021;
     // scale by 2^k through the exponent field (q in [0.7, 1.42], k in [-1021, 1011])
     return hilo_to_double(double_hi(q) + (k << 20), double_lo(q));
 }
@@ -168,6 +171,10 @@ struct DigammaParts {
 };
 
 // psi(x) - log(x+6): everything except the logarithm.  x > 0.
+// Two independent reciprocals (of y and of the recurrence denominator) instead of one shared
+// one: four more instructions, but the asymptotic series then runs beside the denominator chain
+// and only "multiply, subtract" follow the second reciprocal (the update of one word is a
+// serial chain; see estep.cu).
 ONILDA_HD DigammaParts digamma_rational(double x)
 {
     const double y = x + 6.0;
@@ -177,17 +184,16 @@ ONILDA_HD DigammaParts digamma_rational(double x)
     const double u = xr * (xr + 5.0);
     const double den = (u * (u + 4.0)) * (u + 6.0);          // xr(xr+1)...(xr+5)
     const double num = fma(fma(3.0, u, 20.0), u, 24.0);
-    const double t = fma(2.0, xr, 5.0);
-    const double inv = fast_rcp(y * den);
-    const double inv_y = den * inv;
-    const double rec = (t * num) * (y * inv);                // sum_{j=0..5} 1/(x+j)
+    const double tn = fma(2.0, xr, 5.0) * num;
+    const double inv_y = fast_rcp(y);
     const double z = inv_y * inv_y;
     const double z2 = z * z;
     const double s01 = fma(kPsiSeries[1], z, kPsiSeries[0]);
     const double s23 = fma(kPsiSeries[3], z, kPsiSeries[2]);
-    const double series = fma(s23, z2, s01) * z;
+    const double head = fma(-0.5, inv_y, fma(s23, z2, s01) * z);
+    const double inv_den = fast_rcp(den);
     DigammaParts out;
-    out.rational = fma(-0.5, inv_y, series) - rec;
+    out.rational = fma(-tn, inv_den, head);                  // head - sum_{j=0..5} 1/(xr+j)
     out.y = y;
     out.inv_y = inv_y;
     return out;

@@ -242,7 +242,7 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
         const char* env_len = getenv("ONILDA_LONG_LEN");
         const char* env_grp = getenv("ONILDA_LONG_GROUP");
         em->long_len = env_len ? atoi(env_len) : 1024;
-        em->long_group = env_grp ? atoi(env_grp) : (lay.group * 2 <= 32 ? lay.group * 2 : 32);
+        em->long_group = env_grp ? atoi(env_grp) : 32;     // one topic per lane where K <= 32: shortest step
         if (em->long_group < lay.group || (em->long_group & (em->long_group - 1)) || em->long_group > 32) em->long_group = lay.group;
         if ((em->K + em->long_group - 1) / em->long_group > 8) em->long_group = lay.group;
         em->num_long = 0;

@@ -83,9 +83,13 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
     double* __restrict__ phi = a.phi;
 
     for (;;) {
-        unsigned long long bundle = 0;
-        if (lane == 0) bundle = atomicAdd(a.queue, 1ull);
-        bundle = __shfl_sync(0xffffffffu, bundle, 0);
+        // Warp-uniform values are produced with redux/vote (their results live in uniform
+        // registers), so the compiler can prove the warp converged at every shuffle below and
+        // emits them without a divergence branch (BRA.DIV), which would otherwise fence its
+        // instruction scheduling around each one.
+        unsigned int claimed = 0;
+        if (lane == 0) claimed = (unsigned int)atomicAdd(a.queue, 1ull);
+        const unsigned long long bundle = __reduce_max_sync(0xffffffffu, claimed);
         if (bundle >= num_bundles) break;
 
         const int64_t slot = (int64_t)bundle * DPW + grp;
@@ -94,19 +98,21 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
         const int64_t beg = has_doc ? a.offsets[d] : 0;
         const int len = has_doc ? (int)(a.offsets[d + 1] - beg) : 0;
         const int total = has_doc ? a.totals[d] : 0;
-        int max_len = len;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) max_len = max(max_len, __shfl_xor_sync(0xffffffffu, max_len, o));
+        const int max_len = __reduce_max_sync(0xffffffffu, len);
 
         // posterior Dirichlet start (lda-inference.c:37-43)
         const double gamma0 = a.alpha + (total / ((double)K));
-        const double shift = digamma(gamma0);
-        double gam[TPL], psi[TPL], E[TPL];
+        const DigammaParts d0 = digamma_rational(gamma0);
+        const double shift = d0.rational + fast_log(d0.y);
+        // per topic: gamma, E = exp(psi(gamma) - shift), and psi(gamma) kept as its two parts
+        // (rational part, y = gamma + 6) so that the logarithm can be taken one word later
+        double gam[TPL], E[TPL], rat[TPL], yy[TPL];
 #pragma unroll
         for (int t = 0; t < TPL; t++) {
             gam[t] = valid[t] ? gamma0 : 1.0;
-            psi[t] = valid[t] ? shift : 0.0;
-            E[t] = valid[t] ? 1.0 : 0.0;
+            E[t] = 1.0;
+            rat[t] = d0.rational;
+            yy[t] = d0.y;
         }
 
         double lik = 0.0, lik_old = 0.0, converged = 1.0;
@@ -151,6 +157,8 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
             load_ids(0, w1, c1);
             load_rows(0, w1, c1, nxt);
             load_ids(1, w1, c1);
+            // word n's log(s_n) is also taken one word later (s_prev, with its weight and lbmax)
+            double s_prev = 1.0, c_prev = 0.0, lb_prev = 0.0;
             for (int n = 0; n < max_len; n++) {
                 cur = nxt;
                 load_ids(n + 2, w2, c2);
@@ -159,6 +167,7 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
                 c1 = c2;
                 const bool on = cur.word >= 0;
 
+                // The recurrence E -> s -> phi -> gamma -> E (lda-inference.c:52-73) starts here ...
                 double x[TPL], part = 0.0;
 #pragma unroll
                 for (int t = 0; t < TPL; t++) {
@@ -166,9 +175,19 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
                     part += x[t];
                 }
                 const double s = group_sum<G>(part);
+
+                // ... and, off the recurrence, the two logarithms left over from the previous word.
+                // They depend only on values carried into this iteration, so they fill the latency
+                // gaps of the serial chain (the shuffles above, the reciprocals below).
+                double psi[TPL];
+#pragma unroll
+                for (int t = 0; t < TPL; t++) psi[t] = rat[t] + fast_log(yy[t]);
+                acc_lse = fma(c_prev, lb_prev + fast_log(s_prev), acc_lse);
                 const bool bad = !(s > 1e-290 && s < 1e290);
                 double inv = fast_rcp(s);
-                double lse = cur.lbmax + fast_log(s);    // log sum_k exp(psi_k + log_beta_kw), minus shift
+                s_prev = s;
+                c_prev = cur.count;
+                lb_prev = cur.lbmax;
                 if (__any_sync(0xffffffffu, bad)) {
                     // rare: redo this word in log space, as the reference does (lda-inference.c:52-68)
                     double av[TPL], m = -INFINITY;
@@ -189,7 +208,9 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
 #pragma unroll
                         for (int t = 0; t < TPL; t++) x[t] = y[t];
                         inv = 1.0 / ps;
-                        lse = cur.lbmax + m + log(ps);
+                        acc_lse = fma(cur.count, cur.lbmax + m + log(ps), acc_lse);
+                        c_prev = 0.0;      // this word's log-sum is already in
+                        s_prev = 1.0;
                     }
                 }
                 double* prow = phi + (beg + n) * KS + j;
@@ -197,18 +218,18 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
                 for (int t = 0; t < TPL; t++) {
                     const double p = x[t] * inv;
                     if (on && valid[t]) prow[t * G] = p;
-                    const double cp = cur.count * p;
-                    acc_psi[t] = fma(cp, psi[t], acc_psi[t]);
+                    acc_psi[t] = fma(cur.count * p, psi[t], acc_psi[t]);
                     gam[t] = gam[t] + cur.count * (p - cur.old_phi[t]);
                     const DigammaParts dp = digamma_rational(gam[t]);
-                    // E = exp(psi - shift) = y * exp(rational - shift): the logarithm stays off the
-                    // E -> s -> phi -> gamma -> E recurrence; psi itself is only needed by acc_psi
-                    E[t] = valid[t] ? dp.y * fast_exp(dp.rational - shift) : 0.0;
-                    psi[t] = dp.rational + fast_log(dp.y);
+                    // E = exp(psi - shift) = y * exp(rational - shift): no logarithm on the chain.
+                    // Padding topics need no mask here: their beta' is 0, so their E never counts.
+                    E[t] = dp.y * fast_exp(dp.rational - shift);
+                    rat[t] = dp.rational;
+                    yy[t] = dp.y;
                 }
-                acc_lse = fma(cur.count, lse, acc_lse);
                 count_sum += cur.count;
             }
+            acc_lse = fma(c_prev, lb_prev + fast_log(s_prev), acc_lse);
 
             // likelihood bound of this sweep (lda-inference.c:93-127, see header); computed by every
             // group, used by the active ones
@@ -239,7 +260,7 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
         for (int t = 0; t < TPL; t++) {
             if (valid[t]) {
                 gs += gam[t];
-                ps += psi[t];
+                ps += rat[t] + fast_log(yy[t]);
                 if (has_doc) a.gamma[d * K + t * G + j] = gam[t];
             }
         }
