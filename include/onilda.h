@@ -229,6 +229,34 @@ int onilda_score_flow_topk_device(onilda_scorer* s, const int32_t* sdoc_dev, con
                                   int64_t* n_out, double* score_dev_out /* may be NULL */);
 int onilda_scorer_stats(onilda_scorer* s, double* kernel_ms, int64_t* launches);
 
+/* Top-k for callers that cannot allocate.  (No counterpart in the reference: it exists because
+ * of where this library runs, not because of anything lda-c or oni-ml does.)
+ *
+ * Who that is: code running inside a process that has already given all of the GPU's memory to
+ * a pooling allocator - a Spark executor with a GPU memory pool, which is where ONI's post-LDA
+ * scoring lives - so that a cudaMalloc made by this library would fail; and latency-bound
+ * streaming scorers, because cudaMalloc / cudaFree stall the whole device and cannot be issued
+ * while a stream is being captured.  onilda_topk and onilda_score_flow_topk_device both allocate.
+ *
+ * This one makes no cudaMalloc / cudaFree / host-heap call.  Same result as onilda_topk (the k
+ * smallest scores that are <= threshold, ascending, ties by event index), with
+ *   - score_dev: DEVICE pointer to n scores on the current device (n < 2^44); idx_out,
+ *     score_out: HOST arrays with room for k entries; *n_out receives the number written;
+ *   - 0 <= k <= ONILDA_NOALLOC_MAX_K; a larger k, or -1, is refused with ONILDA_EINVAL and a
+ *     message naming the limit;
+ *   - its scratch (histogram, counter, the selected rows: 82 KB) is a fixed device array inside
+ *     the library, one per GPU, kept until the process exits.  Every call on a GPU shares it and
+ *     finds the previous call's contents there; the entry point clears what has to start at
+ *     zero itself.  Two calls that overlap on the same GPU (two host threads, or one thread and
+ *     work of its own still running that reads the results) race on that array: serialise them.
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress);
+ *     make that first call before starting any stream capture.
+ *   - work is issued to the legacy default stream and the call returns when the rows are in
+ *     the host arrays. */
+#define ONILDA_NOALLOC_MAX_K 4096
+int onilda_topk_device_noalloc(const double* score_dev, int64_t n, double threshold, int64_t k,
+                               int64_t* idx_out, double* score_out, int64_t* n_out);
+
 #ifdef __cplusplus
 }
 #endif

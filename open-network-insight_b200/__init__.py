@@ -124,6 +124,7 @@ def lib():
     L.onilda_score_flow_topk_device.argtypes = [_vp, _vp, _vp, _vp, _vp, C.c_int64, C.c_double, C.c_int64, _i64p,
                                                 _f64p, C.POINTER(C.c_int64), _vp]
     L.onilda_scorer_stats.argtypes = [_vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
+    L.onilda_topk_device_noalloc.argtypes = [_vp, C.c_int64, C.c_double, C.c_int64, _i64p, _f64p, C.POINTER(C.c_int64)]
     _lib = L
     return L
 
@@ -431,3 +432,15 @@ class Scorer:
             self._h = None
 
     __del__ = close
+
+
+NOALLOC_MAX_K = 4096
+
+
+def topk_device_noalloc(score_dev_ptr, n, threshold, k):
+    """onilda_topk_device_noalloc: scores already on the current device (pointer as int); the
+    call allocates nothing in the library (the two small result arrays here are the caller's)."""
+    cap = max(min(k, n), 1) if k >= 0 else 1
+    idx, sc, m = np.zeros(cap, np.int64), np.zeros(cap), C.c_int64()
+    _check(lib().onilda_topk_device_noalloc(score_dev_ptr, n, threshold, k, idx, sc, C.byref(m)))
+    return idx[:m.value].copy(), sc[:m.value].copy()

@@ -569,3 +569,138 @@ extern "C" int onilda_phi_from_log_beta(const double* log_beta, int num_topics, 
     if (e != cudaSuccess) return onilda_fail(ONILDA_ECUDA, "phi_from_log_beta: %s", cudaGetErrorString(e));
     return ONILDA_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Top-k without any allocation.
+//
+// Some callers of the scorer may not allocate device memory at the moment they need a result:
+//   * a Spark executor (the reference's post-LDA scoring runs inside one) whose GPU memory has
+//     been handed in full to a pooling allocator at start-up - a cudaMalloc from this library
+//     then fails with out-of-memory although the pool still has room;
+//   * a streaming scorer that ranks every micro-batch and must not stall the device -
+//     cudaMalloc and cudaFree synchronise the whole GPU, and they are illegal while a stream
+//     is being captured.
+// onilda_topk / onilda_score_flow_topk_device allocate (a device copy of the scores, candidate
+// buffers that grow on demand, a scorer handle with its own streams).  The entry point below
+// allocates nothing, on the device or on the host heap: the radix-select histogram, the
+// candidate counter and the at most ONILDA_NOALLOC_MAX_K selected rows live in the file-scope
+// array g_topk_scratch (82 KB, held by every GPU that loads the library until the process
+// exits); host temporaries are on the stack; all work goes to the legacy default stream.
+//
+// In host code the name g_topk_scratch is only a stand-in, not a device address: the address the
+// kernels need is asked for once per device with cudaGetSymbolAddress (with that device
+// current) and handed to them as an ordinary pointer argument.
+namespace {
+
+constexpr int64_t kNoAllocMaxK = 4096;     // ONILDA_NOALLOC_MAX_K in onilda.h
+
+struct TopkScratch {
+    unsigned long long hist[kBins];        // one radix digit's histogram
+    unsigned long long counter[32];        // collect-pass row counter (padded to 256 B)
+    int64_t idx[kNoAllocMaxK];             // selected rows, unordered
+    double score[kNoAllocMaxK];
+};
+
+static __device__ __align__(256) unsigned char g_topk_scratch[sizeof(TopkScratch)];
+
+constexpr int kMaxDevices = 64;
+TopkScratch* g_topk_scratch_addr[kMaxDevices];   // per device; filled on the first call on that device
+
+struct ScoredRow {
+    double s;
+    int64_t i;
+};
+
+}  // namespace
+
+extern "C" int onilda_topk_device_noalloc(const double* score_dev, int64_t n, double threshold, int64_t k,
+                                          int64_t* idx_out, double* score_out, int64_t* n_out)
+{
+    if (n < 0 || (n > 0 && !score_dev) || !n_out || (k > 0 && (!idx_out || !score_out)))
+        return onilda_fail(ONILDA_EINVAL, "topk_device_noalloc: bad argument");
+    if (k < 0 || k > kNoAllocMaxK)
+        return onilda_fail(ONILDA_EINVAL,
+                           "topk_device_noalloc: k = %lld is outside 0..%lld, the most rows the fixed scratch holds "
+                           "(use onilda_topk for more, or for k = -1)", (long long)k, (long long)kNoAllocMaxK);
+    if (n >= ((int64_t)1 << 44))
+        return onilda_fail(ONILDA_EINVAL, "topk_device_noalloc: more than 2^44 events");
+    int dev = 0, sms = 0;
+    ONILDA_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return onilda_fail(ONILDA_EINVAL, "topk_device_noalloc: device index %d unsupported", dev);
+    if (!g_topk_scratch_addr[dev]) {
+        // first call on this device: resolve the device address of the scratch symbol
+        void* p = nullptr;
+        ONILDA_CUDA(cudaGetSymbolAddress(&p, g_topk_scratch));
+        g_topk_scratch_addr[dev] = static_cast<TopkScratch*>(p);
+    }
+    TopkScratch* sc = g_topk_scratch_addr[dev];
+    ONILDA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int blocks = sms * 4;
+    const unsigned long long max_key = isnan(threshold) ? 0ull : host_order_key(threshold);
+    unsigned long long hist[kBins];          // 16 KB on the stack
+    *n_out = 0;
+    if (n == 0 || k == 0) return ONILDA_OK;
+
+    // one histogram pass: the scratch keeps the previous call's numbers, so it is cleared first
+    auto run_hist = [&](unsigned long long kp, unsigned long long km, int on_idx, unsigned long long ip,
+                        unsigned long long im, int shift, int bits) -> int {
+        ONILDA_CUDA(cudaMemsetAsync(sc->hist, 0, sizeof sc->hist, 0));
+        select_hist_kernel<<<blocks, 256, 0, 0>>>(score_dev, n, max_key, kp, km, on_idx, ip, im, shift,
+                                                  (1u << bits) - 1u, sc->hist);
+        ONILDA_CUDA(cudaGetLastError());
+        ONILDA_CUDA(cudaMemcpy(hist, sc->hist, sizeof hist, cudaMemcpyDeviceToHost));
+        return ONILDA_OK;
+    };
+    auto pick = [&](unsigned long long& remaining) -> unsigned long long {
+        unsigned long long acc = 0;
+        int b = 0;
+        for (; b < kBins - 1; b++) { if (acc + hist[b] >= remaining) break; acc += hist[b]; }
+        remaining -= acc;
+        return (unsigned long long)b;
+    };
+    static const int key_pass[6][2] = { {53, 11}, {42, 11}, {31, 11}, {20, 11}, {9, 11}, {0, 9} };
+    static const int idx_pass[4][2] = { {33, 11}, {22, 11}, {11, 11}, {0, 11} };
+
+    int rc = run_hist(0, 0, 0, 0, 0, key_pass[0][0], key_pass[0][1]);
+    if (rc != ONILDA_OK) return rc;
+    unsigned long long under = 0;
+    for (int b = 0; b < kBins; b++) under += hist[b];
+    const int64_t take = (unsigned long long)k > under ? (int64_t)under : k;
+    unsigned long long cut_key = max_key, cut_idx = ~0ull;
+    if (take > 0 && (unsigned long long)take < under) {
+        unsigned long long remaining = (unsigned long long)take, kp = 0, km = 0;
+        for (int p = 0; p < 6; p++) {
+            const int shift = key_pass[p][0], bits = key_pass[p][1];
+            if (p > 0) { rc = run_hist(kp, km, 0, 0, 0, shift, bits); if (rc != ONILDA_OK) return rc; }
+            kp |= pick(remaining) << shift;
+            km |= ((1ull << bits) - 1ull) << shift;
+        }
+        cut_key = kp;
+        unsigned long long ip = 0, im = 0;
+        for (int p = 0; p < 4; p++) {
+            const int shift = idx_pass[p][0], bits = idx_pass[p][1];
+            rc = run_hist(cut_key, ~0ull, 1, ip, im, shift, bits);
+            if (rc != ONILDA_OK) return rc;
+            ip |= pick(remaining) << shift;
+            im |= ((1ull << bits) - 1ull) << shift;
+        }
+        cut_idx = ip;
+    }
+    if (take == 0) return ONILDA_OK;
+    ONILDA_CUDA(cudaMemsetAsync(sc->counter, 0, sizeof sc->counter, 0));
+    select_collect_kernel<<<blocks, 256, 0, 0>>>(score_dev, n, max_key, cut_key, cut_idx, take, sc->counter, sc->idx, sc->score);
+    ONILDA_CUDA(cudaGetLastError());
+    unsigned long long got = 0;
+    ONILDA_CUDA(cudaMemcpy(&got, sc->counter, sizeof got, cudaMemcpyDeviceToHost));
+    if ((int64_t)got != take)
+        return onilda_fail(ONILDA_ECUDA, "topk_device_noalloc: collected %llu rows, expected %lld", got, (long long)take);
+    ONILDA_CUDA(cudaMemcpy(idx_out, sc->idx, sizeof(int64_t) * (size_t)take, cudaMemcpyDeviceToHost));
+    ONILDA_CUDA(cudaMemcpy(score_out, sc->score, sizeof(double) * (size_t)take, cudaMemcpyDeviceToHost));
+    // ascending by (score, index), in place, no heap: at most 4096 rows (64 KB) on the stack
+    ScoredRow rows[kNoAllocMaxK];
+    for (int64_t i = 0; i < take; i++) { rows[i].s = score_out[i]; rows[i].i = idx_out[i]; }
+    std::sort(rows, rows + take, [](const ScoredRow& a, const ScoredRow& b) { return a.s != b.s ? a.s < b.s : a.i < b.i; });
+    for (int64_t i = 0; i < take; i++) { score_out[i] = rows[i].s; idx_out[i] = rows[i].i; }
+    *n_out = take;
+    return ONILDA_OK;
+}
