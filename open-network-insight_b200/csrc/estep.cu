@@ -152,26 +152,18 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
                 }
             };
 
-            int w1, c1, w2 = -1, c2 = 0;
-            WordItem<TPL> cur, nxt;
-            load_ids(0, w1, c1);
-            load_rows(0, w1, c1, nxt);
-            load_ids(1, w1, c1);
             // word n's log(s_n) is also taken one word later (s_prev, with its weight and lbmax)
             double s_prev = 1.0, c_prev = 0.0, lb_prev = 0.0;
-            for (int n = 0; n < max_len; n++) {
-                cur = nxt;
-                load_ids(n + 2, w2, c2);
-                load_rows(n + 1, w1, c1, nxt);
-                w1 = w2;
-                c1 = c2;
-                const bool on = cur.word >= 0;
+
+            // one word of one sweep for every group of the warp
+            auto step = [&](const WordItem<TPL>& it, int n) {
+                const bool on = it.word >= 0;
 
                 // The recurrence E -> s -> phi -> gamma -> E (lda-inference.c:52-73) starts here ...
                 double x[TPL], part = 0.0;
 #pragma unroll
                 for (int t = 0; t < TPL; t++) {
-                    x[t] = E[t] * cur.beta[t];
+                    x[t] = E[t] * it.beta[t];
                     part += x[t];
                 }
                 const double s = group_sum<G>(part);
@@ -186,14 +178,14 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
                 const bool bad = !(s > 1e-290 && s < 1e290);
                 double inv = fast_rcp(s);
                 s_prev = s;
-                c_prev = cur.count;
-                lb_prev = cur.lbmax;
+                c_prev = it.count;
+                lb_prev = it.lbmax;
                 if (__any_sync(0xffffffffu, bad)) {
                     // rare: redo this word in log space, as the reference does (lda-inference.c:52-68)
                     double av[TPL], m = -INFINITY;
 #pragma unroll
                     for (int t = 0; t < TPL; t++) {
-                        av[t] = (valid[t] && cur.beta[t] > 0.0) ? (psi[t] - shift) + log(cur.beta[t]) : -INFINITY;
+                        av[t] = (valid[t] && it.beta[t] > 0.0) ? (psi[t] - shift) + log(it.beta[t]) : -INFINITY;
                         m = fmax(m, av[t]);
                     }
                     m = group_max<G>(m);
@@ -208,7 +200,7 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
 #pragma unroll
                         for (int t = 0; t < TPL; t++) x[t] = y[t];
                         inv = 1.0 / ps;
-                        acc_lse = fma(cur.count, cur.lbmax + m + log(ps), acc_lse);
+                        acc_lse = fma(it.count, it.lbmax + m + log(ps), acc_lse);
                         c_prev = 0.0;      // this word's log-sum is already in
                         s_prev = 1.0;
                     }
@@ -218,8 +210,8 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
                 for (int t = 0; t < TPL; t++) {
                     const double p = x[t] * inv;
                     if (on && valid[t]) prow[t * G] = p;
-                    acc_psi[t] = fma(cur.count * p, psi[t], acc_psi[t]);
-                    gam[t] = gam[t] + cur.count * (p - cur.old_phi[t]);
+                    acc_psi[t] = fma(it.count * p, psi[t], acc_psi[t]);
+                    gam[t] = gam[t] + it.count * (p - it.old_phi[t]);
                     const DigammaParts dp = digamma_rational(gam[t]);
                     // E = exp(psi - shift) = y * exp(rational - shift): no logarithm on the chain.
                     // Padding topics need no mask here: their beta' is 0, so their E never counts.
@@ -227,7 +219,37 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
                     rat[t] = dp.rational;
                     yy[t] = dp.y;
                 }
-                count_sum += cur.count;
+                count_sum += it.count;
+            };
+
+            // The loop is unrolled by two over a pair of row buffers (A, B) so that prefetched rows
+            // are never copied: a register move of a value still in flight would wait for the load.
+            // Rows for word n+1 are requested before word n is worked on and first touched a whole
+            // step later; ids run one word further ahead.
+            // (The one-document-per-warp instantiation keeps a single-step loop: it is bound by the
+            // latency of its own instruction stream, and doubling the loop body costs it more in
+            // instruction fetch than the copies do.)
+            int wa, ca, wb, cb;
+            WordItem<TPL> A, B;
+            load_ids(0, wa, ca);
+            load_ids(1, wb, cb);
+            load_rows(0, wa, ca, A);
+            if constexpr (G < 32) {
+                for (int n = 0; n < max_len; n += 2) {
+                    load_rows(n + 1, wb, cb, B);
+                    load_ids(n + 2, wa, ca);
+                    step(A, n);
+                    load_rows(n + 2, wa, ca, A);
+                    load_ids(n + 3, wb, cb);
+                    step(B, n + 1);
+                }
+            } else {
+                for (int n = 0; n < max_len; n++) {   // wb, cb hold the ids of word n + 1
+                    load_rows(n + 1, wb, cb, B);
+                    load_ids(n + 2, wb, cb);
+                    step(A, n);
+                    A = B;
+                }
             }
             acc_lse = fma(c_prev, lb_prev + fast_log(s_prev), acc_lse);
 
@@ -273,17 +295,30 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
         }
         // class_word[k][w] += c_n phi_nk (lda-estimate.c:48-55); class_total is the column sum (mstep.cu)
         if (a.class_word != nullptr) {
-            for (int n = 0; n < len; n++) {
-                const int64_t e = beg + n;
-                const int w = a.words[e];
-                const double c = (double)a.counts[e];
-                const double* prow = phi + e * KS + j;
-                double* crow = a.class_word + (int64_t)w * KS + j;
+            // four words per trip, all loads issued before the first atomic: the pass is pure
+            // memory latency otherwise (phi rows come back from L2/HBM)
+            constexpr int U = 4;
+            for (int n0 = 0; n0 < len; n0 += U) {
+                int w[U];
+                double c[U], p[U][TPL];
 #pragma unroll
-                for (int t = 0; t < TPL; t++) {
-                    if (valid[t]) {
-                        const double p = (sweeps == 0) ? inv_K : prow[t * G];
-                        atomicAdd(crow + t * G, c * p);
+                for (int u = 0; u < U; u++) {
+                    const bool in = n0 + u < len;
+                    const int64_t e = beg + n0 + u;
+                    w[u] = in ? a.words[e] : -1;
+                    c[u] = in ? (double)a.counts[e] : 0.0;
+                    const double* prow = phi + e * KS + j;
+#pragma unroll
+                    for (int t = 0; t < TPL; t++)
+                        p[u][t] = (in && valid[t] && sweeps != 0) ? prow[t * G] : inv_K;
+                }
+#pragma unroll
+                for (int u = 0; u < U; u++) {
+                    if (w[u] >= 0) {
+                        double* crow = a.class_word + (int64_t)w[u] * KS + j;
+#pragma unroll
+                        for (int t = 0; t < TPL; t++)
+                            if (valid[t]) atomicAdd(crow + t * G, c[u] * p[u][t]);
                     }
                 }
             }
