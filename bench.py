@@ -195,6 +195,105 @@ def reference_sample_docs(corpus_offsets, cores, target_seconds=8.0, nnz_per_cor
     return max(min(n, len(corpus_offsets) - 1), 1)
 
 
+# ----------------------------------------------------------------- scoring leg (BASELINE.json configs[4])
+
+def gen_flow_events_torch(n, theta_t, phi_cdf_flat, D, V, K, device, chunk=1 << 24, unknown_frac=0.001):
+    """Flow events (src_doc, src_word, dst_doc, dst_word) int32 on the device: documents Zipf(1.1)
+    over D, words drawn from the document's theta^T phi, a few unknown (-1) ids."""
+    import torch
+    rank = torch.arange(1, D + 1, device=device, dtype=torch.float64) ** -1.1
+    doc_cdf = torch.cumsum(rank, 0)
+    doc_cdf = doc_cdf / doc_cdf[-1]
+    theta_cdf = torch.cumsum(theta_t, 1)
+    theta_cdf = (theta_cdf / theta_cdf[:, -1:].clamp_min(1e-300)).float()
+    out = [torch.empty(n, dtype=torch.int32, device=device) for _ in range(4)]
+    for side in range(2):
+        for lo in range(0, n, chunk):
+            m = min(chunk, n - lo)
+            doc = torch.searchsorted(doc_cdf, torch.rand(m, device=device, dtype=torch.float64)).clamp_(0, D - 1)
+            z = (torch.rand(m, 1, device=device) > theta_cdf[doc]).sum(1).clamp_(0, K - 1)
+            w = torch.searchsorted(phi_cdf_flat, torch.rand(m, device=device, dtype=torch.float64) + z.double(), right=True)
+            w = (w - z * V).clamp_(0, V - 1)
+            doc = doc.to(torch.int32)
+            w = w.to(torch.int32)
+            doc[torch.rand(m, device=device) < unknown_frac] = -1
+            w[torch.rand(m, device=device) < unknown_frac] = -1
+            out[2 * side][lo:lo + m] = doc
+            out[2 * side + 1][lo:lo + m] = w
+            del doc, z, w
+    return out
+
+
+def scoring_leg(oni, torch, device, gamma, log_beta, n_events, n_e2e, steps, peak, cpu_cores=0):
+    """Events scored per second: device-resident (score kernel + top-1000 select) and end to end
+    from pinned host buffers through onilda_score_flow_min."""
+    D, K = gamma.shape
+    V = log_beta.shape[1]
+    theta = oni.theta_from_gamma(gamma)
+    phi = oni.phi_from_log_beta(log_beta)
+    theta_t = torch.from_numpy(theta).to(device)
+    phi_t = torch.from_numpy(phi).to(device)                      # [V][K]
+    pc = torch.cumsum(phi_t.t().contiguous(), 1)
+    pc = pc / pc[:, -1:]
+    phi_cdf_flat = (pc + torch.arange(K, device=device, dtype=torch.float64)[:, None]).reshape(-1)
+    ev = gen_flow_events_torch(n_events, theta_t, phi_cdf_flat, D, V, K, device)
+    del theta_t, phi_t, pc, phi_cdf_flat
+    torch.cuda.empty_cache()
+    sc = oni.Scorer(theta, phi)
+    scores = torch.empty(n_events, dtype=torch.float64, device=device)
+    torch.cuda.synchronize()
+    kms, tot = [], []
+    for it in range(3 + steps):
+        t0 = time.perf_counter()
+        idx, val = sc.score_flow_topk_device(ev[0].data_ptr(), ev[1].data_ptr(), ev[2].data_ptr(), ev[3].data_ptr(),
+                                             n_events, 1.0, 1000, scores.data_ptr())
+        dt = time.perf_counter() - t0
+        if it >= 3:
+            kms.append(sc.stats()["kernel_ms"])
+            tot.append(dt)
+    kernel_s = float(np.mean(kms)) * 1e-3
+    b_alg = n_events * 2 * (16 + 16 * K)
+    res = {"events": n_events, "events_per_sec": n_events / float(np.mean(tot)), "unit": "flow events/s",
+           "score_kernel_ms": 1e3 * kernel_s, "score_plus_top1000_ms": 1e3 * float(np.mean(tot)),
+           "most_suspicious_score": float(val[0]) if len(val) else None,
+           "roofline": {"bound": "hbm", "kernel": "score_kernel<true>", "achieved": b_alg / kernel_s / 1e9, "peak": peak,
+                        "unit": "GB/s", "frac": b_alg / kernel_s / 1e9 / peak, "algorithmic_bytes_per_launch": b_alg,
+                        "traffic": None}}
+    # end to end from pinned host memory
+    n2 = min(n_e2e, n_events)
+    host = [torch.empty(n2, dtype=torch.int32, pin_memory=True) for _ in range(4)]
+    for h, d in zip(host, ev):
+        h.copy_(d[:n2])
+    out = torch.empty(n2, dtype=torch.float64, pin_memory=True)
+    torch.cuda.synchronize()
+    ts = []
+    for it in range(3 + steps):
+        t0 = time.perf_counter()
+        sc.score_raw(host[0].data_ptr(), host[1].data_ptr(), host[2].data_ptr(), host[3].data_ptr(), n2, out.data_ptr())
+        if it >= 3:
+            ts.append(time.perf_counter() - t0)
+    check = bool(torch.equal(out.to(device), scores[:n2]))
+    res["e2e"] = {"value": n2 / float(np.mean(ts)), "unit": "flow events/s", "events": n2,
+                  "h2d_bytes_per_step": 16 * n2, "d2h_bytes_per_step": 8 * n2, "matches_device_leg": check}
+    res["gpu_launches"] = sc.stats()["launches"]
+    sc.close()
+    if cpu_cores > 0:
+        # CPU baseline: the C restatement of SuspiciousConnectsScoreFunction + flow min (oracle/score_oracle.c;
+        # the Scala/Spark original cannot run here: no JVM), all host threads, on a bounded sample
+        sys.path.insert(0, str(ROOT / "oracle"))
+        import oracle_py
+        m = min(n2, 1 << 25)
+        ids = [h.numpy()[:m] for h in host]
+        oracle_py.score_flow_min(*[x[:1 << 16] for x in ids], theta, phi, threads=cpu_cores)      # warm
+        t0 = time.perf_counter()
+        ref = oracle_py.score_flow_min(*ids, theta, phi, threads=cpu_cores)
+        dt = time.perf_counter() - t0
+        res["cpu_baseline"] = {"value": m / dt, "unit": "flow events/s", "cores": cpu_cores, "kind": "port",
+                               "sample": f"first {m} events, oracle/score_oracle.c with {cpu_cores} pthreads",
+                               "bit_identical_to_gpu": bool(np.array_equal(ref, out.numpy()[:m]))}
+    return res
+
+
 # ----------------------------------------------------------------- main
 
 def algorithmic_bytes(nnz, num_docs, K):
@@ -214,6 +313,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true", help="development only")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-scoring", action="store_true")
+    ap.add_argument("--events", type=int, default=1_000_000_000, help="flow events of the scoring leg (configs[4])")
     args = ap.parse_args()
     if args.warmup < 3:
         log("warm-up raised to 3 (timing rules)")
@@ -239,6 +339,7 @@ def main():
     device = torch.device("cuda", local_rank)
     dist = None
     if world > 1 and args.impl == "ours":
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")    # stdout carries the one JSON line only
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=device)
 
@@ -402,6 +503,18 @@ def main():
                 "kernel_ms": float(np.mean(estep_ms)), "peak_source": peak_src,
                 "note": "fp64-transcendental bound, not HBM bound: see DESIGN.md"}
 
+    # ------------------------------------------------------------ scoring leg (rank 0, one GPU)
+    scoring = None
+    if not args.no_scoring:
+        gamma = em.gamma()
+        log_beta = np.array(em.model().log_beta)
+        em.close()
+        torch.cuda.empty_cache()
+        n_events = max(1_000_000, int(args.events * args.scale))
+        scoring = scoring_leg(oni, torch, device, gamma, log_beta, n_events, 1 << 28, 5, peak,
+                              cpu_cores=0 if args.no_cpu_baseline else host_cores())
+        del gamma, log_beta
+
     # ------------------------------------------------------------ CPU baseline (reference lda-c on this box)
     cpu_baseline = None
     if not args.no_cpu_baseline:
@@ -430,7 +543,7 @@ def main():
                        "parallelism": f"dp{world} over documents", "scale": args.scale},
             "nnz_per_sec": N_all / (elapsed / args.steps),
             "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
-            "cpu_baseline": cpu_baseline,
+            "cpu_baseline": cpu_baseline, "scoring": scoring,
             "em": {"estep_ms": [round(x, 3) for x in estep_ms], "mstep_ms_mean": float(np.mean(mstep_ms)),
                    "likelihood_first": liks[0], "likelihood_last": liks[-1], "sweeps_last_iter": int(sweeps),
                    "e2e_likelihood_last": e2e_liks[-1]}}

@@ -336,3 +336,25 @@ def test_top1000_overlap_after_em(oni, oracle, corpusgen):
     assert overlap >= 0.99, overlap
     sc.close()
     em.close()
+
+
+def test_two_gpu_lda_est_matches_one_gpu(oni, tmp_path):
+    """`lda est ... 2 ...`: documents sharded over two devices, statistics summed over NVLink peer memory
+    (replaces the MPI_Allreduce calls of lda-estimate.c:211-252); results must not depend on the GPU count."""
+    if oni.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    d = GOLD / "k20"
+    outs = []
+    for ndev in (1, 2):
+        out = tmp_path / f"out{ndev}"
+        r = subprocess.run([str(oni.LDA_BIN), "est", "2.5", "20", str(d / "settings.txt"), str(ndev), str(d / "c.dat"),
+                            str(d / "000"), str(out)], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        outs.append(out)
+    l1, l2 = np.loadtxt(outs[0] / "likelihood.dat", ndmin=2), np.loadtxt(outs[1] / "likelihood.dat", ndmin=2)
+    ref = np.loadtxt(d / "likelihood.dat", ndmin=2)
+    assert l1.shape == l2.shape == ref.shape
+    assert np.max(np.abs(l2[:, 0] - ref[:, 0]) / np.abs(ref[:, 0])) < LIK_RTOL
+    assert np.max(np.abs(l2[:, 0] - l1[:, 0]) / np.abs(l1[:, 0])) < 1e-12
+    assert rel_err(read_matrix(outs[1] / "final.beta"), read_matrix(d / "final.beta"), 1e-2) < MODEL_RTOL
+    assert rel_err(read_matrix(outs[1] / "final.gamma"), read_matrix(d / "final.gamma"), 1e-3) < MODEL_RTOL
