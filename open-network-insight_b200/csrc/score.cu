@@ -127,6 +127,77 @@ __global__ void __launch_bounds__(kScoreThreads) score_kernel(const double* __re
     }
 }
 
+// Even K (the usual case: ONI uses K = 20): rows are whole numbers of 16-byte pairs, and only the
+// PRODUCTS need staging.  Lanes fetch pair c*32+lane of the 32 theta rows and the matching pair of
+// the 32 phi rows (two coalesced 128-bit gathers), multiply (each product is rounded on its own, so
+// doing them in parallel changes nothing), store the pair of products, and the owning lane then
+// adds its row's K products left to right - the order of Scala's sum.  Half the shared-memory
+// traffic of staging both tables, no shuffles, 128-bit accesses throughout.
+__device__ __forceinline__ double2 ldg_pair(const double* p)
+{
+    return __ldg(reinterpret_cast<const double2*>(p));
+}
+
+template <bool FLOW>
+__global__ void __launch_bounds__(kScoreThreads) score_pairs_kernel(const double* __restrict__ theta, int64_t D,
+                                                                    const double* __restrict__ phi, int32_t V, int K,
+                                                                    const int32_t* __restrict__ sdoc,
+                                                                    const int32_t* __restrict__ sword,
+                                                                    const int32_t* __restrict__ ddoc,
+                                                                    const int32_t* __restrict__ dword, int64_t n,
+                                                                    double* __restrict__ out)
+{
+    extern __shared__ double smem[];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int C = K >> 1;                 // pairs per row
+    const int stride = K + 2;             // C + 1 pairs: odd pair stride -> conflict-free 128-bit rows
+    double* tile = smem + (size_t)warp * (32 * stride + 64);
+    int* rows_t = reinterpret_cast<int*>(tile + 32 * stride);
+    int* rows_p = rows_t + 32;
+    // (row, pair) walked by this lane: element e = c*32 + lane, row = e / C, pair = e % C
+    const int r0 = lane / C, q0 = lane % C, dr = 32 / C, dq = 32 % C;
+    const int64_t tiles = (n + 31) / 32;
+    const int64_t warps_total = (int64_t)gridDim.x * kScoreWarps;
+    for (int64_t tile_id = (int64_t)blockIdx.x * kScoreWarps + warp; tile_id < tiles; tile_id += warps_total) {
+        const int64_t i = tile_id * 32 + lane;
+        const bool live = i < n;
+        double result = 0.0;
+#pragma unroll
+        for (int side = 0; side < (FLOW ? 2 : 1); side++) {
+            const int32_t d0 = live ? (side ? ddoc[i] : sdoc[i]) : -1;
+            const int32_t w0 = live ? (side ? dword[i] : sword[i]) : -1;
+            // ids outside the tables (e.g. -1) take the uniform row (SuspiciousConnectsScoreFunction.scala:13-18)
+            rows_t[lane] = (d0 >= 0 && d0 < D) ? d0 : (int)D;
+            rows_p[lane] = (w0 >= 0 && w0 < V) ? w0 : (int)V;
+            __syncwarp();
+            int r = r0, q = q0;
+            for (int c = 0; c < C; c++) {
+                const double2 t2 = ldg_pair(theta + (int64_t)rows_t[r] * K + 2 * q);
+                const double2 p2 = ldg_pair(phi + (int64_t)rows_p[r] * K + 2 * q);
+                double2 pr;
+                pr.x = __dmul_rn(t2.x, p2.x);
+                pr.y = __dmul_rn(t2.y, p2.y);
+                *reinterpret_cast<double2*>(tile + r * stride + 2 * q) = pr;
+                r += dr;
+                q += dq;
+                if (q >= C) { q -= C; r++; }
+            }
+            __syncwarp();
+            double s = 0.0;
+            const double* mine = tile + lane * stride;
+            for (int c = 0; c < C; c++) {
+                const double2 v = *reinterpret_cast<const double2*>(mine + 2 * c);
+                s = __dadd_rn(s, v.x);      // no fma, fixed order: bit-identical to the sequential sum
+                s = __dadd_rn(s, v.y);
+            }
+            __syncwarp();
+            result = (side == 0) ? s : ((result <= s) ? result : s);   // scala.math.min (FlowPostLDA.scala:117-119)
+        }
+        if (live) out[i] = result;
+    }
+}
+
 // theta row = gamma / sum (left-to-right sum), zeros when sum <= 0 (OniLDACWrapper.scala:132-144)
 __global__ void theta_kernel(const double* __restrict__ gamma, int64_t D, int K, double* __restrict__ theta)
 {
@@ -340,16 +411,26 @@ int select_topk_device(onilda_scorer* s, const double* score_dev, int64_t n, dou
 }
 
 size_t score_smem_bytes(int K) { return sizeof(double) * (size_t)kScoreWarps * 2 * 32 * (size_t)(K | 1); }
+size_t score_pairs_smem_bytes(int K) { return sizeof(double) * (size_t)kScoreWarps * (32 * (size_t)(K + 2) + 64); }
+bool use_pairs_kernel(const onilda_scorer* s) { return (s->K % 2) == 0 && s->K >= 2 && s->K <= 64 && s->D < 0x7fffffff; }
 
 int launch_score(onilda_scorer* s, cudaStream_t st, const int32_t* sdoc, const int32_t* sword, const int32_t* ddoc,
                  const int32_t* dword, int64_t n, double* out)
 {
     if (n <= 0) return ONILDA_OK;
-    const size_t shmem = score_smem_bytes(s->K);
     int64_t tiles = (n + 31) / 32;
     int64_t blocks = (tiles + kScoreWarps - 1) / kScoreWarps;
     const int64_t cap = (int64_t)s->sm_count * 8;
     if (blocks > cap) blocks = cap;
+    if (use_pairs_kernel(s)) {
+        const size_t sh = score_pairs_smem_bytes(s->K);
+        if (ddoc) score_pairs_kernel<true><<<(unsigned)blocks, kScoreThreads, sh, st>>>(s->d_theta, s->D, s->d_phi, s->V, s->K, sdoc, sword, ddoc, dword, n, out);
+        else score_pairs_kernel<false><<<(unsigned)blocks, kScoreThreads, sh, st>>>(s->d_theta, s->D, s->d_phi, s->V, s->K, sdoc, sword, nullptr, nullptr, n, out);
+        ONILDA_CUDA(cudaGetLastError());
+        s->launches++;
+        return ONILDA_OK;
+    }
+    const size_t shmem = score_smem_bytes(s->K);
     if (ddoc) score_kernel<true><<<(unsigned)blocks, kScoreThreads, shmem, st>>>(s->d_theta, s->D, s->d_phi, s->V, s->K, sdoc, sword, ddoc, dword, n, out);
     else score_kernel<false><<<(unsigned)blocks, kScoreThreads, shmem, st>>>(s->d_theta, s->D, s->d_phi, s->V, s->K, sdoc, sword, nullptr, nullptr, n, out);
     ONILDA_CUDA(cudaGetLastError());
@@ -405,6 +486,8 @@ extern "C" int onilda_scorer_create(const double* theta, int64_t num_docs, const
     const size_t shmem = score_smem_bytes(K);
     STEP(cudaFuncSetAttribute(score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
     STEP(cudaFuncSetAttribute(score_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
+    STEP(cudaFuncSetAttribute(score_pairs_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_pairs_smem_bytes(K)));
+    STEP(cudaFuncSetAttribute(score_pairs_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_pairs_smem_bytes(K)));
     STEP(cudaStreamSynchronize(s->stream[0]));
 #undef STEP
     if (e != cudaSuccess) {
