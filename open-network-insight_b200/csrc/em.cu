@@ -19,7 +19,7 @@ struct onilda_em {
     cudaStream_t long_stream;   // long documents run beside the bulk launch
     cudaEvent_t ev0, ev1, ev2, ev3, ev_fork, ev_join;
     int64_t num_long;           // documents of at least long_len entries: prefix of d_order
-    int long_len, long_group, long_smem, bulk_group;
+    int long_len, long_group, long_smem, bulk_group, bulk_per_sm;
     // shard
     int64_t doc_begin, doc_end, num_docs, nnz;
     int K, V;
@@ -198,7 +198,12 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
     TRYCUDA(cudaEventCreate(&em->ev1));
     TRYCUDA(cudaEventCreate(&em->ev2));
     TRYCUDA(cudaEventCreate(&em->ev3));
-    TRYCUDA(cudaStreamCreateWithFlags(&em->long_stream, cudaStreamNonBlocking));
+    {
+        // highest priority: when both launches are ready the block scheduler takes the long documents first
+        int prio_lo = 0, prio_hi = 0;
+        TRYCUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+        TRYCUDA(cudaStreamCreateWithPriority(&em->long_stream, cudaStreamNonBlocking, prio_hi));
+    }
     TRYCUDA(cudaEventCreateWithFlags(&em->ev_fork, cudaEventDisableTiming));
     TRYCUDA(cudaEventCreateWithFlags(&em->ev_join, cudaEventDisableTiming));
 
@@ -248,6 +253,8 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
         const char* env_bulk = getenv("ONILDA_BULK_GROUP");
         em->bulk_group = env_bulk ? atoi(env_bulk) : lay.group;
         if (em->bulk_group < lay.group || (em->bulk_group & (em->bulk_group - 1)) || em->bulk_group > 32) em->bulk_group = lay.group;
+        const char* env_bps = getenv("ONILDA_BULK_PER_SM");
+        em->bulk_per_sm = env_bps ? atoi(env_bps) : 0;
         const char* env_smem = getenv("ONILDA_LONG_SMEM");
         em->long_smem = env_smem ? atoi(env_smem) : 0;
         em->num_long = 0;
@@ -328,12 +335,12 @@ static int run_estep(onilda_em* em, bool accumulate)
         ONILDA_CUDA(cudaStreamWaitEvent(em->long_stream, em->ev_fork, 0));
         EStepArgs b = a;
         b.order_begin = 0; b.order_count = em->num_long; b.queue = em->d_queue + 1;
-        rc = launch_estep(em->long_group, b, em->sm_count, 32, em->long_smem, em->long_stream, &l);
+        rc = launch_estep(em->long_group, b, em->sm_count, 32, em->long_smem, 0, em->long_stream, &l);
         if (rc != ONILDA_OK) return rc;
         ONILDA_CUDA(cudaEventRecord(em->ev_join, em->long_stream));
     }
     a.order_begin = em->num_long; a.order_count = em->num_docs - em->num_long; a.queue = em->d_queue;
-    rc = launch_estep(em->bulk_group, a, em->sm_count, 128, 0, em->stream, &l);
+    rc = launch_estep(em->bulk_group, a, em->sm_count, 128, 0, em->num_long > 0 ? em->bulk_per_sm : 0, em->stream, &l);
     if (rc != ONILDA_OK) return rc;
     if (em->num_long > 0) ONILDA_CUDA(cudaStreamWaitEvent(em->stream, em->ev_join, 0));
     rc = launch_reduce_doc_stats(em->d_doc_lik, em->d_doc_ass, em->num_docs, em->d_partial, em->d_ss + table, em->stream, &l);

@@ -329,7 +329,8 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
 // Grid for `num_bundles` bundles of one (G, TPL) instantiation: persistent, at most the resident
 // capacity of `sm_count` SMs (or `max_blocks` when the launch shares the device with another).
 template <int G, int TPL>
-static int launch_one(const EStepArgs& args, int sm_count, int block_threads, int reserve_smem, cudaStream_t stream)
+static int launch_one(const EStepArgs& args, int sm_count, int block_threads, int reserve_smem, int max_per_sm,
+                      cudaStream_t stream)
 {
     constexpr int DPW = 32 / G;
     const unsigned long long num_bundles = (unsigned long long)((args.order_count + DPW - 1) / DPW);
@@ -341,6 +342,7 @@ static int launch_one(const EStepArgs& args, int sm_count, int block_threads, in
     int per_sm = 0;
     ONILDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_kernel<G, TPL>, block_threads, (size_t)reserve_smem));
     if (per_sm < 1) per_sm = 1;
+    if (max_per_sm > 0 && per_sm > max_per_sm) per_sm = max_per_sm;
     const unsigned long long wpb = (unsigned long long)(block_threads / 32);
     unsigned long long want = (num_bundles + wpb - 1) / wpb;
     unsigned long long grid = (unsigned long long)sm_count * per_sm;
@@ -351,17 +353,18 @@ static int launch_one(const EStepArgs& args, int sm_count, int block_threads, in
 }
 
 template <int G>
-static int launch_group(int tpl, const EStepArgs& args, int sm_count, int block_threads, int reserve_smem, cudaStream_t stream)
+static int launch_group(int tpl, const EStepArgs& args, int sm_count, int block_threads, int reserve_smem, int max_per_sm,
+                        cudaStream_t stream)
 {
     switch (tpl) {
-        case 1: return launch_one<G, 1>(args, sm_count, block_threads, reserve_smem, stream);
-        case 2: return launch_one<G, 2>(args, sm_count, block_threads, reserve_smem, stream);
-        case 3: return launch_one<G, 3>(args, sm_count, block_threads, reserve_smem, stream);
-        case 4: return launch_one<G, 4>(args, sm_count, block_threads, reserve_smem, stream);
-        case 5: return launch_one<G, 5>(args, sm_count, block_threads, reserve_smem, stream);
-        case 6: return launch_one<G, 6>(args, sm_count, block_threads, reserve_smem, stream);
-        case 7: return launch_one<G, 7>(args, sm_count, block_threads, reserve_smem, stream);
-        case 8: return launch_one<G, 8>(args, sm_count, block_threads, reserve_smem, stream);
+        case 1: return launch_one<G, 1>(args, sm_count, block_threads, reserve_smem, max_per_sm, stream);
+        case 2: return launch_one<G, 2>(args, sm_count, block_threads, reserve_smem, max_per_sm, stream);
+        case 3: return launch_one<G, 3>(args, sm_count, block_threads, reserve_smem, max_per_sm, stream);
+        case 4: return launch_one<G, 4>(args, sm_count, block_threads, reserve_smem, max_per_sm, stream);
+        case 5: return launch_one<G, 5>(args, sm_count, block_threads, reserve_smem, max_per_sm, stream);
+        case 6: return launch_one<G, 6>(args, sm_count, block_threads, reserve_smem, max_per_sm, stream);
+        case 7: return launch_one<G, 7>(args, sm_count, block_threads, reserve_smem, max_per_sm, stream);
+        case 8: return launch_one<G, 8>(args, sm_count, block_threads, reserve_smem, max_per_sm, stream);
     }
     return onilda_fail(ONILDA_EINVAL, "unsupported topics-per-lane %d", tpl);
 }
@@ -369,17 +372,17 @@ static int launch_group(int tpl, const EStepArgs& args, int sm_count, int block_
 // One launch over documents order[order_begin, order_begin + order_count) with `group` lanes per
 // document and `block_threads` (32..128) threads per block.  args.queue must be zero (the caller
 // clears it on the same stream).
-int launch_estep(int group, const EStepArgs& args, int sm_count, int block_threads, int reserve_smem, cudaStream_t stream,
-                 int* launches)
+int launch_estep(int group, const EStepArgs& args, int sm_count, int block_threads, int reserve_smem, int max_per_sm,
+                 cudaStream_t stream, int* launches)
 {
     if (args.order_count <= 0) return ONILDA_OK;
     const int tpl = (args.num_topics + group - 1) / group;
     int rc;
     switch (group) {
-        case 4: rc = launch_group<4>(tpl, args, sm_count, block_threads, reserve_smem, stream); break;
-        case 8: rc = launch_group<8>(tpl, args, sm_count, block_threads, reserve_smem, stream); break;
-        case 16: rc = launch_group<16>(tpl, args, sm_count, block_threads, reserve_smem, stream); break;
-        case 32: rc = launch_group<32>(tpl, args, sm_count, block_threads, reserve_smem, stream); break;
+        case 4: rc = launch_group<4>(tpl, args, sm_count, block_threads, reserve_smem, max_per_sm, stream); break;
+        case 8: rc = launch_group<8>(tpl, args, sm_count, block_threads, reserve_smem, max_per_sm, stream); break;
+        case 16: rc = launch_group<16>(tpl, args, sm_count, block_threads, reserve_smem, max_per_sm, stream); break;
+        case 32: rc = launch_group<32>(tpl, args, sm_count, block_threads, reserve_smem, max_per_sm, stream); break;
         default: return onilda_fail(ONILDA_EINVAL, "unsupported lane group %d", group);
     }
     if (rc == ONILDA_OK && launches) *launches += 1;

@@ -69,8 +69,8 @@ struct EStepArgs {
     int* error_flag;            // set to 1 on a NaN likelihood
 };
 
-int launch_estep(int group, const EStepArgs& args, int sm_count, int block_threads, int reserve_smem, cudaStream_t stream,
-                 int* launches);
+int launch_estep(int group, const EStepArgs& args, int sm_count, int block_threads, int reserve_smem, int max_per_sm,
+                 cudaStream_t stream, int* launches);
 
 // M-step and table kernels (mstep.cu)
 int launch_tables_from_log_beta(const double* log_beta_kv, int K, int V, const TopicLayout& lay, double* log_beta_wk,
