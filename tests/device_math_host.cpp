@@ -6,5 +6,6 @@ extern "C" {
 void dm_rcp(const double* x, double* y, long n) { for (long i = 0; i < n; i++) y[i] = onilda::fast_rcp(x[i]); }
 void dm_log(const double* x, double* y, long n) { for (long i = 0; i < n; i++) y[i] = onilda::fast_log(x[i]); }
 void dm_exp(const double* x, double* y, long n) { for (long i = 0; i < n; i++) y[i] = onilda::fast_exp(x[i]); }
+void dm_log_tab(const double* x, double* y, long n) { for (long i = 0; i < n; i++) y[i] = onilda::fast_log_tab(x[i], onilda::kLogTab); }
 void dm_digamma(const double* x, double* y, long n) { for (long i = 0; i < n; i++) y[i] = onilda::digamma(x[i]); }
 }

@@ -20,7 +20,7 @@ def dm(tmp_path_factory):
                     "-I", str(ROOT / "open-network-insight_b200" / "csrc"),
                     str(ROOT / "tests" / "device_math_host.cpp"), "-o", str(out)], check=True)
     L = C.CDLL(str(out))
-    for f in (L.dm_rcp, L.dm_log, L.dm_exp, L.dm_digamma):
+    for f in (L.dm_rcp, L.dm_log, L.dm_log_tab, L.dm_exp, L.dm_digamma):
         f.argtypes = [_f64p, _f64p, C.c_long]
 
     def call(fn, x):
@@ -50,6 +50,16 @@ def test_log(dm):
     err = np.abs(got - want)
     assert np.all(err <= 2.5 * np.spacing(np.abs(want)) + 2.3e-16)       # <= 2 ulp, or ~1 ulp of 1 near log = 0
     assert dm.call(dm.dm_log, np.array([1.0]))[0] == 0.0
+
+
+def test_log_by_table(dm):
+    rng = np.random.default_rng(4)
+    x = np.concatenate([np.exp(rng.uniform(-700, 700, 200000)), rng.uniform(0.5, 2.0, 200000),
+                        6 + np.exp(rng.uniform(-30, 15, 200000)), 1 + np.arange(129) / 128.0,
+                        np.nextafter(1 + np.arange(1, 129) / 128.0, 0), [1.0, 2.0, 0.5, 6.0, 1e-300, 1e300]])
+    got, want = dm.call(dm.dm_log_tab, x), np.log(x)
+    err = np.abs(got - want)
+    assert np.all(err <= 2.5 * np.spacing(np.abs(want)) + 4.5e-16)       # <= 2 ulp, or ~2 ulp of 1 near log = 0
 
 
 def test_exp(dm):
