@@ -358,3 +358,44 @@ def test_two_gpu_lda_est_matches_one_gpu(oni, tmp_path):
     assert np.max(np.abs(l2[:, 0] - l1[:, 0]) / np.abs(l1[:, 0])) < 1e-12
     assert rel_err(read_matrix(outs[1] / "final.beta"), read_matrix(d / "final.beta"), 1e-2) < MODEL_RTOL
     assert rel_err(read_matrix(outs[1] / "final.gamma"), read_matrix(d / "final.gamma"), 1e-3) < MODEL_RTOL
+
+
+def test_degenerate_shapes(oni, oracle):
+    """Empty shard, a one-document corpus, empty documents only, vocabulary wider than the data."""
+    d = GOLD / "k5"
+    c, m = oni.Corpus.from_dat(d / "c.dat"), oni.Model.load(d / "000")
+    st = oni.Settings(20, 1e-6, 2, 1e-6, 1)
+    # an empty shard contributes nothing and must not fault
+    e0 = oni.EM(c, m, st, doc_begin=7, doc_end=7)
+    e0.estep()
+    assert e0.gamma().shape == (0, 5) and e0.doc_likelihood().shape == (0,)
+    e0.close()
+    # one document
+    off, w, cn, tot, V = oracle.read_dat(d / "c.dat")
+    alpha, lb = oracle.load_model(d / "000")
+    one = oni.Corpus.from_csr(off[:2], w[:off[1]], cn[:off[1]], num_terms=V)
+    e1 = oni.EM(one, m, st)
+    e1.estep()
+    ref = oracle.e_step(off[:2].copy(), w[:off[1]].copy(), cn[:off[1]].copy(), V, alpha, lb, 20, 1e-6)
+    assert rel_err(e1.doc_likelihood(), ref["doc_lik"], 1e-9) < 1e-10
+    e1.close()
+    # only empty documents: gamma stays at alpha, bound is the Dirichlet terms (lda-inference.c:37-43, 106-116)
+    empty = oni.Corpus.from_csr(np.zeros(4, np.int64), np.zeros(0, np.int32), np.zeros(0, np.int32), num_terms=V)
+    e2 = oni.EM(empty, m, st)
+    e2.estep()
+    refe = oracle.e_step(np.zeros(4, np.int64), np.zeros(0, np.int32), np.zeros(0, np.int32), V, alpha, lb, 20, 1e-6)
+    assert np.allclose(e2.gamma(), alpha) and rel_err(e2.doc_likelihood(), refe["doc_lik"], 1e-12) < 1e-9
+    e2.close()
+    # a model with more terms than the corpus uses: unseen words get the -100 sentinel after the M-step
+    wide = oni.Model.new(5, V + 9)
+    wide.log_beta[:, :V] = m.log_beta
+    wide.log_beta[:, V:] = -100.0
+    wide.alpha = m.alpha
+    e3 = oni.EM(c, wide, st)
+    e3.iterate()
+    assert np.all(e3.model().log_beta[:, V:] == -100.0)
+    e3.close()
+    with pytest.raises(oni.OnildaError):
+        oni.EM(c, oni.Model.new(5, V - 1), st)                 # corpus has more terms than the model
+    with pytest.raises(oni.OnildaError):
+        oni.EM(c, oni.Model.new(300, V), st)                   # more topics than the kernels support
