@@ -40,6 +40,11 @@ WORKLOADS = {
     # BASELINE.json configs[1]
     "netflow-1M-docs-100M-tokens-V100k-K20": dict(num_docs=1_000_000, mean_tokens=100, num_terms=100_000,
                                                   num_topics=20, seed=20161102),
+    # BASELINE.json configs[2] and [3]: parity/scale cases, not the headline line (run with --workload, usually --scale < 1)
+    "dns-2M-docs-200M-tokens-V50k-K20": dict(num_docs=2_000_000, mean_tokens=100, num_terms=50_000,
+                                             num_topics=20, seed=20161103),
+    "proxy-5M-docs-1B-tokens-V500k-K50": dict(num_docs=5_000_000, mean_tokens=200, num_terms=500_000,
+                                              num_topics=50, seed=20161104),
 }
 DEFAULT_WORKLOAD = "netflow-1M-docs-100M-tokens-V100k-K20"
 ALPHA0 = 2.5                     # OniLDACWrapper.scala:83
@@ -311,7 +316,7 @@ def main():
     ap.add_argument("--steps", type=int, default=18)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=DEFAULT_WORKLOAD)
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--scale", type=float, default=1.0, help="development only: shrink the number of documents")
     ap.add_argument("--hub-frac", type=float, default=None, help="development only: fraction of hub documents")
     ap.add_argument("--no-e2e", action="store_true", help="development only")
