@@ -256,7 +256,14 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
         const char* env_bps = getenv("ONILDA_BULK_PER_SM");
         em->bulk_per_sm = env_bps ? atoi(env_bps) : 0;
         const char* env_smem = getenv("ONILDA_LONG_SMEM");
-        em->long_smem = env_smem ? atoi(env_smem) : 0;
+        // Default: eight one-warp blocks per SM, i.e. two long documents per SM sub-partition.  With
+        // every long document resident at once (9-10 per SM at cfg 2) some sub-partitions carry three and
+        // their documents finish last; the cap is enforced by asking for an eighth of the SM's shared
+        // memory per block, which the kernel never touches (measured at cfg 2: 155-160 -> 145 ms).
+        int smem_sm = 0;
+        if (cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, device) != cudaSuccess) smem_sm = 0;
+        cudaGetLastError();
+        em->long_smem = env_smem ? atoi(env_smem) : (smem_sm >= 65536 ? smem_sm / 8 - 1184 : 0);
         em->num_long = 0;
         if (em->long_len > 0 && em->long_group != lay.group)
             while (em->num_long < D && off[(size_t)order[(size_t)em->num_long] + 1] - off[(size_t)order[(size_t)em->num_long]] >= em->long_len) em->num_long++;

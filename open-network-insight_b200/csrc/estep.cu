@@ -352,7 +352,7 @@ static int launch_one(const EStepArgs& args, int sm_count, int block_threads, in
     const unsigned long long num_bundles = (unsigned long long)((args.order_count + DPW - 1) / DPW);
     if (num_bundles == 0) return ONILDA_OK;
     // reserve_smem: dynamic shared memory the kernel never touches, asked for only to cap how many
-    // of these blocks an SM takes (a tuning knob, 0 by default; see em.cu)
+    // of these blocks an SM takes (em.cu sets it for the long-document launch: two warps per sub-partition)
     if (reserve_smem > 0)
         ONILDA_CUDA(cudaFuncSetAttribute(estep_kernel<G, TPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, reserve_smem));
     int per_sm = 0;
