@@ -43,6 +43,9 @@ struct onilda_scorer {
     int64_t* d_sel_idx;
     double* d_sel_score;
     int64_t sel_cap;
+    int64_t* d_cand_idx;          // candidates still in question after two radix digits
+    double* d_cand_score;
+    int64_t cand_cap;
     double kernel_ms;
     int64_t launches;
 };
@@ -252,7 +255,9 @@ constexpr int kBins = 1 << kDigitBits;
 
 // Histogram of one digit.  Items considered: key <= max_key, (key & key_mask) == key_prefix and,
 // when on_index, key == key_prefix exactly and (idx & idx_mask) == idx_prefix.
-__global__ void __launch_bounds__(256) select_hist_kernel(const double* __restrict__ score, int64_t n,
+// idx_map: event index of element i when the array is a compacted candidate list (nullptr: i itself).
+__global__ void __launch_bounds__(256) select_hist_kernel(const double* __restrict__ score,
+                                                          const int64_t* __restrict__ idx_map, int64_t n,
                                                           unsigned long long max_key, unsigned long long key_prefix,
                                                           unsigned long long key_mask, int on_index,
                                                           unsigned long long idx_prefix, unsigned long long idx_mask,
@@ -268,8 +273,9 @@ __global__ void __launch_bounds__(256) select_hist_kernel(const double* __restri
         if (key > max_key || (key & key_mask) != key_prefix) continue;
         unsigned long long digit_src = key;
         if (on_index) {
-            if (((unsigned long long)i & idx_mask) != idx_prefix) continue;
-            digit_src = (unsigned long long)i;
+            const unsigned long long ev = idx_map ? (unsigned long long)idx_map[i] : (unsigned long long)i;
+            if ((ev & idx_mask) != idx_prefix) continue;
+            digit_src = ev;
         }
         atomicAdd(&sh[(unsigned int)(digit_src >> shift) & digit_mask], 1u);
     }
@@ -279,7 +285,8 @@ __global__ void __launch_bounds__(256) select_hist_kernel(const double* __restri
 }
 
 // Collect every item with (key, idx) <= (cut_key, cut_idx) and key <= max_key (unordered).
-__global__ void __launch_bounds__(256) select_collect_kernel(const double* __restrict__ score, int64_t n,
+__global__ void __launch_bounds__(256) select_collect_kernel(const double* __restrict__ score,
+                                                             const int64_t* __restrict__ idx_map, int64_t n,
                                                              unsigned long long max_key, unsigned long long cut_key,
                                                              unsigned long long cut_idx, int64_t cap,
                                                              unsigned long long* __restrict__ counter,
@@ -290,9 +297,37 @@ __global__ void __launch_bounds__(256) select_collect_kernel(const double* __res
         const double s = score[i];
         const unsigned long long key = order_key(s);
         if (key > max_key) continue;
-        if (key < cut_key || (key == cut_key && (unsigned long long)i <= cut_idx)) {
+        const int64_t ev = idx_map ? idx_map[i] : i;
+        if (key < cut_key || (key == cut_key && (unsigned long long)ev <= cut_idx)) {
             const unsigned long long slot = atomicAdd(counter, 1ull);
-            if ((int64_t)slot < cap) { idx_out[slot] = i; score_out[slot] = s; }
+            if ((int64_t)slot < cap) { idx_out[slot] = ev; score_out[slot] = s; }
+        }
+    }
+}
+
+// After two digits of the radix select: events whose key prefix is BELOW the cut prefix are selected
+// for certain (written straight to the output, counter[0]); those EQUAL to it are the only ones still
+// in question and are compacted (score + event index, counter[1]) so that the remaining passes read
+// that short list instead of all n scores.
+__global__ void __launch_bounds__(256) select_split_kernel(const double* __restrict__ score, int64_t n,
+                                                           unsigned long long max_key, unsigned long long prefix,
+                                                           unsigned long long mask, int64_t sel_cap, int64_t cand_cap,
+                                                           unsigned long long* __restrict__ counter,
+                                                           int64_t* __restrict__ sel_idx, double* __restrict__ sel_score,
+                                                           int64_t* __restrict__ cand_idx, double* __restrict__ cand_score)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const double s = score[i];
+        const unsigned long long key = order_key(s);
+        if (key > max_key) continue;
+        const unsigned long long pre = key & mask;
+        if (pre < prefix) {
+            const unsigned long long slot = atomicAdd(&counter[0], 1ull);
+            if ((int64_t)slot < sel_cap) { sel_idx[slot] = i; sel_score[slot] = s; }
+        } else if (pre == prefix) {
+            const unsigned long long slot = atomicAdd(&counter[1], 1ull);
+            if ((int64_t)slot < cand_cap) { cand_idx[slot] = i; cand_score[slot] = s; }
         }
     }
 }
@@ -318,9 +353,25 @@ int ensure_sel(onilda_scorer* s, int64_t cap)
     return ONILDA_OK;
 }
 
+int ensure_cand(onilda_scorer* s, int64_t cap)
+{
+    if (cap <= s->cand_cap) return ONILDA_OK;
+    cudaFree(s->d_cand_idx); cudaFree(s->d_cand_score);
+    s->d_cand_idx = nullptr; s->d_cand_score = nullptr; s->cand_cap = 0;
+    if (cudaMalloc((void**)&s->d_cand_idx, sizeof(int64_t) * (size_t)cap) != cudaSuccess ||
+        cudaMalloc((void**)&s->d_cand_score, sizeof(double) * (size_t)cap) != cudaSuccess) {
+        cudaGetLastError();
+        return onilda_fail(ONILDA_ENOMEM, "top-k: cannot allocate room for %lld candidates on the device", (long long)cap);
+    }
+    s->cand_cap = cap;
+    return ONILDA_OK;
+}
+
 // k smallest of score_dev[0..n) (device) under `threshold`; ties by index.  Host outputs.
-// Radix select, most significant digit first, on the composite (order_key(score), index):
-// each pass is one histogram kernel over the scores plus an 16 KB read-back.
+// Radix select, most significant digit first, on the composite (order_key(score), index): each
+// pass is one histogram kernel plus a 16 KB read-back.  After two digits the events still in
+// question are normally a sliver of n; they are compacted once (select_split_kernel) and the
+// remaining eight passes read that list, so all n scores are read three times, not eleven.
 int select_topk_device(onilda_scorer* s, const double* score_dev, int64_t n, double threshold, int64_t k,
                        int64_t* idx_out, double* score_out, int64_t* n_out)
 {
@@ -328,10 +379,14 @@ int select_topk_device(onilda_scorer* s, const double* score_dev, int64_t n, dou
     const unsigned long long max_key = isnan(threshold) ? 0ull : host_order_key(threshold);
     const int blocks = s->sm_count * 4;
     std::vector<unsigned long long> hist(kBins);
+    // the array the digit passes read: all n scores at first, the compacted candidates later
+    const double* cur_score = score_dev;
+    const int64_t* cur_map = nullptr;
+    int64_t cur_n = n;
     auto run_hist = [&](unsigned long long kp, unsigned long long km, int on_idx, unsigned long long ip,
                         unsigned long long im, int shift, int bits) -> int {
         ONILDA_CUDA(cudaMemsetAsync(s->d_hist, 0, sizeof(unsigned long long) * kBins, st));
-        select_hist_kernel<<<blocks, 256, 0, st>>>(score_dev, n, max_key, kp, km, on_idx, ip, im, shift,
+        select_hist_kernel<<<blocks, 256, 0, st>>>(cur_score, cur_map, cur_n, max_key, kp, km, on_idx, ip, im, shift,
                                                    (1u << bits) - 1u, s->d_hist);
         ONILDA_CUDA(cudaGetLastError());
         ONILDA_CUDA(cudaMemcpyAsync(hist.data(), s->d_hist, sizeof(unsigned long long) * kBins, cudaMemcpyDeviceToHost, st));
@@ -349,24 +404,48 @@ int select_topk_device(onilda_scorer* s, const double* score_dev, int64_t n, dou
     };
     static const int key_pass[6][2] = { {53, 11}, {42, 11}, {31, 11}, {20, 11}, {9, 11}, {0, 9} };
     static const int idx_pass[4][2] = { {33, 11}, {22, 11}, {11, 11}, {0, 11} };   // indices < 2^44
+    constexpr int64_t kMaxCandidates = (int64_t)1 << 26;
 
     unsigned long long cut_key = max_key, cut_idx = ~0ull;
-    int64_t take = 0;
+    int64_t take = 0, already = 0;       // already: rows written to d_sel by the split pass
+    int rc;
     if (n > 0) {
         // the first key pass also yields the number of events under the threshold
-        int rc = run_hist(0, 0, 0, 0, 0, key_pass[0][0], key_pass[0][1]);
+        rc = run_hist(0, 0, 0, 0, 0, key_pass[0][0], key_pass[0][1]);
         if (rc != ONILDA_OK) return rc;
         unsigned long long under = 0;
         for (unsigned long long h : hist) under += h;
         take = (k == -1 || (unsigned long long)k > under) ? (int64_t)under : k;
+        if (take > 0) { rc = ensure_sel(s, take); if (rc != ONILDA_OK) return rc; }
         if (take > 0 && (unsigned long long)take < under) {
             unsigned long long remaining = (unsigned long long)take, kp = 0, km = 0;
             for (int p = 0; p < 6; p++) {
                 const int shift = key_pass[p][0], bits = key_pass[p][1];
                 if (p > 0) { rc = run_hist(kp, km, 0, 0, 0, shift, bits); if (rc != ONILDA_OK) return rc; }
                 const unsigned long long b = pick(remaining);
+                const unsigned long long in_bin = hist[(size_t)b];
                 kp |= b << shift;
                 km |= ((1ull << bits) - 1ull) << shift;
+                // two digits fixed and the undecided set is small next to n: split once, then work on the short list
+                if (p == 1 && cur_map == nullptr && (int64_t)in_bin <= kMaxCandidates && (int64_t)in_bin * 4 <= n) {
+                    rc = ensure_cand(s, (int64_t)in_bin);
+                    if (rc != ONILDA_OK) return rc;
+                    ONILDA_CUDA(cudaMemsetAsync(s->d_hist, 0, 2 * sizeof(unsigned long long), st));
+                    select_split_kernel<<<blocks, 256, 0, st>>>(score_dev, n, max_key, kp, km, take, (int64_t)in_bin, s->d_hist,
+                                                                s->d_sel_idx, s->d_sel_score, s->d_cand_idx, s->d_cand_score);
+                    ONILDA_CUDA(cudaGetLastError());
+                    s->launches++;
+                    unsigned long long cnt[2] = {0, 0};
+                    ONILDA_CUDA(cudaMemcpyAsync(cnt, s->d_hist, sizeof cnt, cudaMemcpyDeviceToHost, st));
+                    ONILDA_CUDA(cudaStreamSynchronize(st));
+                    if (cnt[1] != in_bin || cnt[0] != (unsigned long long)take - remaining)
+                        return onilda_fail(ONILDA_ECUDA, "top-k split pass: %llu below / %llu candidates, expected %llu / %llu",
+                                           cnt[0], cnt[1], (unsigned long long)take - remaining, in_bin);
+                    already = (int64_t)cnt[0];
+                    cur_score = s->d_cand_score;
+                    cur_map = s->d_cand_idx;
+                    cur_n = (int64_t)in_bin;
+                }
             }
             cut_key = kp;
             // among events whose score equals the cut, keep the `remaining` smallest indices
@@ -384,10 +463,11 @@ int select_topk_device(onilda_scorer* s, const double* score_dev, int64_t n, dou
     }
     *n_out = take;
     if (take == 0) return ONILDA_OK;
-    int rc = ensure_sel(s, take);
-    if (rc != ONILDA_OK) return rc;
-    ONILDA_CUDA(cudaMemsetAsync(s->d_hist, 0, sizeof(unsigned long long), st));
-    select_collect_kernel<<<blocks, 256, 0, st>>>(score_dev, n, max_key, cut_key, cut_idx, take, s->d_hist, s->d_sel_idx, s->d_sel_score);
+    // collect: from the candidate list (appending to what the split pass already wrote) or from all scores
+    unsigned long long start = (unsigned long long)already;
+    ONILDA_CUDA(cudaMemcpyAsync(s->d_hist, &start, sizeof start, cudaMemcpyHostToDevice, st));
+    select_collect_kernel<<<blocks, 256, 0, st>>>(cur_score, cur_map, cur_n, max_key, cut_key, cut_idx, take, s->d_hist,
+                                                  s->d_sel_idx, s->d_sel_score);
     ONILDA_CUDA(cudaGetLastError());
     s->launches++;
     std::vector<int64_t> idx((size_t)take);
@@ -446,7 +526,7 @@ extern "C" void onilda_scorer_destroy(onilda_scorer* s)
     DeviceGuard g(s->device);
     cudaFree(s->d_theta); cudaFree(s->d_phi);
     for (int i = 0; i < 2; i++) { cudaFree(s->d_ids[i]); cudaFree(s->d_out[i]); if (s->stream[i]) cudaStreamDestroy(s->stream[i]); }
-    cudaFree(s->d_hist); cudaFree(s->d_sel_idx); cudaFree(s->d_sel_score);
+    cudaFree(s->d_hist); cudaFree(s->d_sel_idx); cudaFree(s->d_sel_score); cudaFree(s->d_cand_idx); cudaFree(s->d_cand_score);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     free(s);
@@ -728,7 +808,7 @@ extern "C" int onilda_topk_device_noalloc(const double* score_dev, int64_t n, do
     auto run_hist = [&](unsigned long long kp, unsigned long long km, int on_idx, unsigned long long ip,
                         unsigned long long im, int shift, int bits) -> int {
         ONILDA_CUDA(cudaMemsetAsync(sc->hist, 0, sizeof sc->hist, 0));
-        select_hist_kernel<<<blocks, 256, 0, 0>>>(score_dev, n, max_key, kp, km, on_idx, ip, im, shift,
+        select_hist_kernel<<<blocks, 256, 0, 0>>>(score_dev, nullptr, n, max_key, kp, km, on_idx, ip, im, shift,
                                                   (1u << bits) - 1u, sc->hist);
         ONILDA_CUDA(cudaGetLastError());
         ONILDA_CUDA(cudaMemcpy(hist, sc->hist, sizeof hist, cudaMemcpyDeviceToHost));
@@ -771,7 +851,7 @@ extern "C" int onilda_topk_device_noalloc(const double* score_dev, int64_t n, do
     }
     if (take == 0) return ONILDA_OK;
     ONILDA_CUDA(cudaMemsetAsync(sc->counter, 0, sizeof sc->counter, 0));
-    select_collect_kernel<<<blocks, 256, 0, 0>>>(score_dev, n, max_key, cut_key, cut_idx, take, sc->counter, sc->idx, sc->score);
+    select_collect_kernel<<<blocks, 256, 0, 0>>>(score_dev, nullptr, n, max_key, cut_key, cut_idx, take, sc->counter, sc->idx, sc->score);
     ONILDA_CUDA(cudaGetLastError());
     unsigned long long got = 0;
     ONILDA_CUDA(cudaMemcpy(&got, sc->counter, sizeof got, cudaMemcpyDeviceToHost));

@@ -307,6 +307,13 @@ def test_topk_matches_oracle_with_ties(oni, oracle):
         assert np.array_equal(idx, ridx) and np.array_equal(s, rs), (thr, k)
     idx, s = sc.topk(np.zeros(0), 1.0, 5)
     assert len(idx) == 0
+    # few ties: after two radix digits the undecided events are a sliver and get compacted (split pass)
+    wide = rng.random(3_000_000) ** 3
+    wide[rng.integers(0, len(wide), 5000)] = wide[7]          # plus a tie group that straddles the cut
+    for thr, k in [(1.0, 1000), (1.0, 1), (0.5, 4000), (float(wide[7]), 3000), (1e-12, 10)]:
+        idx, s = sc.topk(wide, thr, k)
+        ridx, rs = oracle.topk(wide, thr, k)
+        assert np.array_equal(idx, ridx) and np.array_equal(s, rs), (thr, k)
     sc.close()
 
 
