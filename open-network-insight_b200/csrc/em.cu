@@ -18,6 +18,8 @@ struct onilda_em {
     cudaStream_t stream;
     cudaStream_t long_stream;   // long documents run beside the bulk launch
     cudaEvent_t ev0, ev1, ev2, ev3, ev_fork, ev_join;
+    cudaEvent_t ev_long_end, ev_bulk_end;   // ONILDA_TIMING=1: when each of the two concurrent launches ended
+    int timing;
     int64_t num_long;           // documents of at least long_len entries: prefix of d_order
     int long_len, long_group, long_smem, bulk_group, bulk_per_sm;
     // shard
@@ -148,6 +150,8 @@ extern "C" void onilda_em_destroy(onilda_em* em)
     if (em->ev3) cudaEventDestroy(em->ev3);
     if (em->ev_fork) cudaEventDestroy(em->ev_fork);
     if (em->ev_join) cudaEventDestroy(em->ev_join);
+    if (em->ev_long_end) cudaEventDestroy(em->ev_long_end);
+    if (em->ev_bulk_end) cudaEventDestroy(em->ev_bulk_end);
     if (em->long_stream) cudaStreamDestroy(em->long_stream);
     if (em->stream) cudaStreamDestroy(em->stream);
     free(em);
@@ -206,6 +210,9 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
     }
     TRYCUDA(cudaEventCreateWithFlags(&em->ev_fork, cudaEventDisableTiming));
     TRYCUDA(cudaEventCreateWithFlags(&em->ev_join, cudaEventDisableTiming));
+    TRYCUDA(cudaEventCreate(&em->ev_long_end));
+    TRYCUDA(cudaEventCreate(&em->ev_bulk_end));
+    em->timing = getenv("ONILDA_TIMING") != nullptr;
 
     const int64_t D = em->num_docs, N = em->nnz;
     const size_t table = (size_t)em->V * lay.kpad;
@@ -344,11 +351,13 @@ static int run_estep(onilda_em* em, bool accumulate)
         b.order_begin = 0; b.order_count = em->num_long; b.queue = em->d_queue + 1;
         rc = launch_estep(em->long_group, b, em->sm_count, 32, em->long_smem, 0, em->long_stream, &l);
         if (rc != ONILDA_OK) return rc;
+        if (em->timing) ONILDA_CUDA(cudaEventRecord(em->ev_long_end, em->long_stream));
         ONILDA_CUDA(cudaEventRecord(em->ev_join, em->long_stream));
     }
     a.order_begin = em->num_long; a.order_count = em->num_docs - em->num_long; a.queue = em->d_queue;
     rc = launch_estep(em->bulk_group, a, em->sm_count, 128, 0, em->num_long > 0 ? em->bulk_per_sm : 0, em->stream, &l);
     if (rc != ONILDA_OK) return rc;
+    if (em->timing) ONILDA_CUDA(cudaEventRecord(em->ev_bulk_end, em->stream));
     if (em->num_long > 0) ONILDA_CUDA(cudaStreamWaitEvent(em->stream, em->ev_join, 0));
     rc = launch_reduce_doc_stats(em->d_doc_lik, em->d_doc_ass, em->num_docs, em->d_partial, em->d_ss + table, em->stream, &l);
     if (rc != ONILDA_OK) return rc;
@@ -396,6 +405,13 @@ extern "C" int onilda_em_mstep(onilda_em* em, double* likelihood, double* conver
     em->estep_done = 0;
     float ms = 0;
     if (cudaEventElapsedTime(&ms, em->ev0, em->ev1) == cudaSuccess) em->estep_ms = ms;
+    if (em->timing) {
+        float tl = 0, tb = 0;
+        if (em->num_long > 0) cudaEventElapsedTime(&tl, em->ev0, em->ev_long_end);
+        cudaEventElapsedTime(&tb, em->ev0, em->ev_bulk_end);
+        fprintf(stderr, "[onilda] E-step %.2f ms: long-document launch ended at %.2f ms, bulk launch at %.2f ms\n",
+                em->estep_ms, tl, tb);
+    }
     if (cudaEventElapsedTime(&ms, em->ev2, em->ev3) == cudaSuccess) em->mstep_ms = ms;
     cudaGetLastError();
     if (err || isnan(tail[SS_LIK])) return onilda_fail(ONILDA_ENAN, "NaN likelihood in the E-step (the reference asserts at lda-inference.c:78)");
