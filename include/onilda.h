@@ -205,6 +205,11 @@ int onilda_phi_from_log_beta(const double* log_beta, int num_topics, int num_ter
  * (SuspiciousConnectsScoreFunction.scala:7-9): tables resident on one device. */
 int onilda_scorer_create(const double* theta, int64_t num_docs, const double* phi, int32_t num_terms,
                          int num_topics, int device, onilda_scorer** out);
+/* The same tables taken straight from an EM handle's device memory (the handle's shard: its gamma rows
+ * become theta rows 0..D-1, its current model becomes phi): what getDocumentResults +
+ * getWordToProbPerTopicMap compute after reading final.gamma / final.beta back
+ * (OniLDACWrapper.scala:88-144, 170-195), without the text files or a host round trip. */
+int onilda_scorer_create_from_em(onilda_em* em, onilda_scorer** out);
 void onilda_scorer_destroy(onilda_scorer* s);
 /* replaces SuspiciousConnectsScoreFunction.score (:11-23) for n (doc, word)
  * pairs: sum_k theta[doc][k] * phi[word][k], products rounded then summed left

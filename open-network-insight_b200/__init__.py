@@ -116,6 +116,7 @@ def lib():
     L.onilda_theta_from_gamma.argtypes = [_f64p, C.c_int64, C.c_int, C.c_int, _f64p]
     L.onilda_phi_from_log_beta.argtypes = [_f64p, C.c_int, C.c_int, C.c_int, _f64p]
     L.onilda_scorer_create.argtypes = [_vp, C.c_int64, _vp, C.c_int32, C.c_int, C.c_int, C.POINTER(_vp)]
+    L.onilda_scorer_create_from_em.argtypes = [_vp, C.POINTER(_vp)]
     L.onilda_scorer_destroy.argtypes = [_vp]
     L.onilda_scorer_destroy.restype = None
     L.onilda_score.argtypes = [_vp, _vp, _vp, C.c_int64, _vp]
@@ -384,6 +385,16 @@ class Scorer:
         _check(lib().onilda_scorer_create(_ptr(theta), theta.shape[0], _ptr(phi_wk), phi_wk.shape[0], self.K, device,
                                           C.byref(h)))
         self._h = h
+
+    @classmethod
+    def from_em(cls, em: "EM"):
+        """theta / phi straight from an EM handle's device memory (no text files, no host copies)."""
+        self = cls.__new__(cls)
+        self.K = em.num_topics
+        h = _vp()
+        _check(lib().onilda_scorer_create_from_em(em._h, C.byref(h)))
+        self._h = h
+        return self
 
     def score(self, doc, word, out=None):
         doc = np.ascontiguousarray(doc, np.int32)

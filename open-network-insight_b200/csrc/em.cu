@@ -476,6 +476,17 @@ extern "C" int onilda_em_get_doc_likelihood(onilda_em* em, double* out)
     return ONILDA_OK;
 }
 
+extern "C" int onilda_em_device_views(onilda_em* em, int* device, int64_t* num_docs, int* num_topics, int* num_terms, int* kpad,
+                                      const double** gamma_dev, const double** log_beta_wk_dev)
+{
+    if (!em) return onilda_fail(ONILDA_EINVAL, "em_device_views: null handle");
+    DeviceGuard g(em->device);
+    ONILDA_CUDA(cudaStreamSynchronize(em->stream));
+    *device = em->device; *num_docs = em->num_docs; *num_topics = em->K; *num_terms = em->V; *kpad = em->lay.kpad;
+    *gamma_dev = em->d_gamma; *log_beta_wk_dev = em->d_log_beta_wk;
+    return ONILDA_OK;
+}
+
 extern "C" int onilda_em_get_doc_sweeps(onilda_em* em, int32_t* out)
 {
     if (!em || (!out && em->num_docs > 0)) return onilda_fail(ONILDA_EINVAL, "em_get_doc_sweeps: null argument");

@@ -41,6 +41,9 @@ double onilda_opt_alpha(double ss, int D, int K);
 
 /* em.cu */
 void onilda_corpus_unpin(onilda_corpus* c);
+/* device views of a handle's results for the scorer hand-off (score.cu); waits for the handle's stream */
+int onilda_em_device_views(onilda_em* em, int* device, int64_t* num_docs, int* num_topics, int* num_terms, int* kpad,
+                           const double** gamma_dev, const double** log_beta_wk_dev);
 
 /* textio.c */
 /* formats v as printf("%5.10f") would; returns the number of chars written (no NUL). */

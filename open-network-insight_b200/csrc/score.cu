@@ -236,6 +236,49 @@ __global__ void phi_norm_kernel(const double* __restrict__ log_beta_kv, const do
     for (int k = 0; k < K; k++) phi_wk[w * K + k] = exp(log_beta_kv[(int64_t)k * V + w]) / sums[k];
 }
 
+// phi straight from the E-step's word-major table log_beta_wk [V][kpad] (no host round trip):
+// per-block partial sums of exp over a slice of the vocabulary, then a fixed-order final sum
+constexpr int kPhiBlocks = 296;
+__global__ void __launch_bounds__(256) phi_partial_wk_kernel(const double* __restrict__ lb_wk, int V, int K, int kpad,
+                                                             double* __restrict__ partial)
+{
+    extern __shared__ double sh[];                       // [rows][K]
+    const int rows = 256 / K, k = threadIdx.x % K, r = threadIdx.x / K;
+    const int64_t chunk = ((int64_t)V + gridDim.x - 1) / gridDim.x, lo = chunk * blockIdx.x;
+    int64_t hi = lo + chunk;
+    if (hi > V) hi = V;
+    if (r < rows) {
+        double acc = 0.0;
+        for (int64_t w = lo + r; w < hi; w += rows) acc += exp(lb_wk[w * kpad + k]);
+        sh[r * K + k] = acc;
+    }
+    __syncthreads();
+    if (r == 0) {
+        double tot = sh[k];
+        for (int i = 1; i < rows; i++) tot += sh[i * K + k];
+        partial[(int64_t)blockIdx.x * K + k] = tot;
+    }
+}
+
+__global__ void phi_final_wk_kernel(const double* __restrict__ partial, int nblocks, int K, double* __restrict__ sums)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= K) return;
+    double acc = 0.0;
+    for (int b = 0; b < nblocks; b++) acc += partial[(int64_t)b * K + k];
+    sums[k] = acc;
+}
+
+__global__ void phi_norm_wk_kernel(const double* __restrict__ lb_wk, const double* __restrict__ sums, int V, int K, int kpad,
+                                   double* __restrict__ phi_wk)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (int64_t)V * K) return;
+    const int64_t w = i / K;
+    const int k = (int)(i % K);
+    phi_wk[i] = exp(lb_wk[w * kpad + k]) / sums[k];
+}
+
 __global__ void fill_kernel(double* p, int n, double v)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -577,6 +620,55 @@ extern "C" int onilda_scorer_create(const double* theta, int64_t num_docs, const
         return rc;
     }
     *out = s;
+    return ONILDA_OK;
+}
+
+// theta / phi taken from an EM handle on the device: replaces writing final.gamma / final.beta, reading them
+// back and normalising on the host (OniLDACWrapper.scala:88-144, 170-195) when EM and scoring share a process
+extern "C" int onilda_scorer_create_from_em(onilda_em* em, onilda_scorer** out)
+{
+    if (!em || !out) return onilda_fail(ONILDA_EINVAL, "scorer_create_from_em: null argument");
+    int device = 0, K = 0, V = 0, kpad = 0;
+    int64_t D = 0;
+    const double *gamma_dev = nullptr, *lb_dev = nullptr;
+    int rc = onilda_em_device_views(em, &device, &D, &K, &V, &kpad, &gamma_dev, &lb_dev);
+    if (rc != ONILDA_OK) return rc;
+    if (K > 256) return onilda_fail(ONILDA_EINVAL, "scorer_create_from_em: %d topics unsupported", K);
+    // an empty scorer of the right shape (uniform rows, streams, scratch), then the tables are filled on the device
+    rc = onilda_scorer_create(nullptr, 0, nullptr, 0, K, device, out);
+    if (rc != ONILDA_OK) return rc;
+    onilda_scorer* s = *out;
+    DeviceGuard g(device);
+    cudaFree(s->d_theta); cudaFree(s->d_phi);
+    s->d_theta = nullptr; s->d_phi = nullptr;
+    s->D = D; s->V = V;
+    double *partial = nullptr, *sums = nullptr;
+    cudaError_t e = cudaMalloc((void**)&s->d_theta, sizeof(double) * (size_t)(D + 1) * K);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&s->d_phi, sizeof(double) * (size_t)(V + 1) * K);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&partial, sizeof(double) * (size_t)kPhiBlocks * K);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&sums, sizeof(double) * (size_t)K);
+    if (e == cudaSuccess) {
+        cudaStream_t st = s->stream[0];
+        if (D > 0) theta_kernel<<<(unsigned)((D + 255) / 256), 256, 0, st>>>(gamma_dev, D, K, s->d_theta);
+        if (V > 0) {
+            phi_partial_wk_kernel<<<kPhiBlocks, 256, sizeof(double) * (size_t)(256 / K) * K, st>>>(lb_dev, V, K, kpad, partial);
+            phi_final_wk_kernel<<<(K + 63) / 64, 64, 0, st>>>(partial, kPhiBlocks, K, sums);
+            phi_norm_wk_kernel<<<(unsigned)(((int64_t)V * K + 255) / 256), 256, 0, st>>>(lb_dev, sums, V, K, kpad, s->d_phi);
+        }
+        fill_kernel<<<(K + 63) / 64, 64, 0, st>>>(s->d_theta + (size_t)D * K, K, 1.0 / K);
+        fill_kernel<<<(K + 63) / 64, 64, 0, st>>>(s->d_phi + (size_t)V * K, K, 1.0 / K);
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        s->launches += 6;
+    }
+    cudaFree(partial); cudaFree(sums);
+    if (e != cudaSuccess) {
+        rc = onilda_fail(e == cudaErrorMemoryAllocation ? ONILDA_ENOMEM : ONILDA_ECUDA, "scorer_create_from_em: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+        onilda_scorer_destroy(s);
+        *out = nullptr;
+        return rc;
+    }
     return ONILDA_OK;
 }
 

@@ -24,6 +24,14 @@ def rel_err(a, b, floor):
     return np.max(np.abs(a - b) / np.maximum(np.abs(b), floor))
 
 
+def tie_aware_overlap(my_idx, ref_scores, ref_top_scores, rtol=1e-9):
+    """Share of my selected events that the REFERENCE's own scores also place at or below its cut.
+    Many events share (ip, word) and hence a score, and whole tie groups sit on the cut: an
+    index-set intersection would punish an arbitrary choice inside such a group, this does not."""
+    cut = ref_top_scores[-1] * (1 + rtol)
+    return float(np.mean(ref_scores[my_idx] <= cut))
+
+
 def read_matrix(path):
     return np.array([[float(x) for x in line.split()] for line in Path(path).read_text().splitlines()])
 
@@ -338,8 +346,7 @@ def test_top1000_overlap_after_em(oni, oracle, corpusgen):
     assert np.max(np.abs(mine - want) / np.maximum(want, 1e-12)) < 1e-4
     idx, s = sc.topk(mine, 1.0, 1000)
     ridx, rs = oracle.topk(want, 1.0, 1000)
-    # tie-aware overlap: compare the multisets of (rounded) scores and the index sets
-    overlap = len(set(idx.tolist()) & set(ridx.tolist())) / 1000.0
+    overlap = tie_aware_overlap(idx, want, rs)
     assert overlap >= 0.99, overlap
     sc.close()
     em.close()
@@ -406,3 +413,26 @@ def test_degenerate_shapes(oni, oracle):
         oni.EM(c, oni.Model.new(5, V - 1), st)                 # corpus has more terms than the model
     with pytest.raises(oni.OnildaError):
         oni.EM(c, oni.Model.new(300, V), st)                   # more topics than the kernels support
+
+
+@pytest.mark.parametrize("case", ["k20", "k50", "k5"])
+def test_scorer_from_em_matches_host_path(oni, oracle, case):
+    """theta/phi handed from the EM handle to the scorer on the device == the reference's route through
+    final.gamma / final.beta (OniLDACWrapper.scala:88-144, 170-195)."""
+    d, c, m, st = load_case(oni, case)
+    em = oni.EM(c, m, st)
+    em.iterate()
+    em.iterate()
+    gamma, lb = em.gamma(), np.array(em.model().log_beta)
+    theta, phi = oracle.theta_from_gamma(gamma), oracle.phi_from_logbeta(lb)
+    rng = np.random.default_rng(3)
+    n = 50_000
+    ids = [rng.integers(-1, hi, n).astype(np.int32) for hi in (theta.shape[0], phi.shape[0]) * 2]
+    dev = oni.Scorer.from_em(em)
+    host = oni.Scorer(theta, phi)
+    a, b = dev.score_flow_min(*ids), host.score_flow_min(*ids)
+    assert np.max(np.abs(a - b) / np.maximum(b, 1e-300)) < 1e-12          # phi sums are formed in another order
+    ia, sa = dev.topk(a, 1.0, 1000)
+    ib, sb = host.topk(b, 1.0, 1000)
+    assert tie_aware_overlap(ia, b, sb) >= 0.99 and np.max(np.abs(sa - sb) / sb) < 1e-12
+    dev.close(); host.close(); em.close()
