@@ -5,7 +5,8 @@
 
 Each case directory holds: c.dat, settings.txt, 000.{beta,other} (the start model the
 reference wrote with a fixed RNG seed), and the reference's outputs from that start:
-final.{beta,other,gamma}, likelihood.dat, plus `lda inf` outputs inf-gamma.dat and
+final.{beta,other,gamma}, likelihood.dat, random.{likelihood.dat,final.gamma,final.other} (what the
+`random` run with that seed wrote itself), plus `lda inf` outputs inf-gamma.dat and
 inf-lda-lhood.dat (model = final, settings = inf-settings.txt).
 The parity protocol is SURVEY.md section 8(c): both sides start from 000.
 """
@@ -63,6 +64,9 @@ def main():
                 shutil.copy(td / f, out / f)
             for f in ("000.beta", "000.other"):
                 shutil.copy(td / "boot" / f, out / f)
+            # the `random` run itself (double-precision start, no float round trip through 000.*)
+            for f in ("likelihood.dat", "final.gamma", "final.other"):
+                shutil.copy(td / "boot" / f, out / ("random." + f))
             for f in ("final.beta", "final.other", "final.gamma", "likelihood.dat"):
                 shutil.copy(td / "ref" / f, out / f)
             for f in ("inf-gamma.dat", "inf-lda-lhood.dat"):

@@ -436,3 +436,52 @@ def test_scorer_from_em_matches_host_path(oni, oracle, case):
     ib, sb = host.topk(b, 1.0, 1000)
     assert tie_aware_overlap(ia, b, sb) >= 0.99 and np.max(np.abs(sa - sb) / sb) < 1e-12
     dev.close(); host.close(); em.close()
+
+
+SEEDS = {"k5": (1001, 2.5), "k20": (2002, 2.5), "k20_fixed": (3003, 0.1), "k50": (4004, 2.5)}
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_random_start_against_reference_files(oni, case, tmp_path):
+    """`lda est ... random` end to end through the program, seed fixed with ONILDA_SEED: the reference's own
+    `random` run with the same seed wrote random.likelihood.dat / random.final.* (no float round trip)."""
+    d = GOLD / case
+    seed, alpha0 = SEEDS[case]
+    K = int((d / "000.other").read_text().split()[1])
+    out = tmp_path / "out"
+    import os
+    r = subprocess.run([str(oni.LDA_BIN), "est", str(alpha0), str(K), str(d / "settings.txt"), "1", str(d / "c.dat"),
+                        "random", str(out)], capture_output=True, text=True, env=dict(os.environ, ONILDA_SEED=str(seed)))
+    assert r.returncode == 0, r.stderr
+    assert (out / "000.beta").read_bytes() == (d / "000.beta").read_bytes()          # same MT19937 stream
+    assert (out / "000.other").read_bytes() == (d / "000.other").read_bytes()
+    mine, ref = np.loadtxt(out / "likelihood.dat", ndmin=2), np.loadtxt(d / "random.likelihood.dat", ndmin=2)
+    assert mine.shape == ref.shape
+    assert np.max(np.abs(mine[:, 0] - ref[:, 0]) / np.abs(ref[:, 0])) < LIK_RTOL
+    assert rel_err(read_matrix(out / "final.gamma"), read_matrix(d / "random.final.gamma"), 1e-3) < MODEL_RTOL
+    a_ref = float((d / "random.final.other").read_text().split()[-1])
+    a_mine = float((out / "final.other").read_text().split()[-1])
+    assert abs(a_mine - a_ref) <= MODEL_RTOL * a_ref + 1e-10
+
+
+def test_full_default_run_against_oracle(oni, oracle, corpusgen):
+    """All 21 EM iterations of lda-c's default settings (em max iter 20 runs 21, lda-estimate.c:186) on a
+    cfg-1-shaped corpus scaled to what the oracle does in about twenty seconds."""
+    g = corpusgen.generate(1200, 100, 5000, 20, seed=20161101, hub_tokens=6000)
+    c = oni.Corpus.from_csr(g.offsets, g.words, g.counts)
+    m = oni.Model.new(20, c.num_terms)
+    m.init_random(424242)
+    m.alpha = 2.5
+    ref = oracle.run_em(g.offsets, g.words, g.counts, c.num_terms, 2.5, m.log_beta.copy(), oracle.settings())
+    em = oni.EM(c, m, oni.Settings.default())
+    liks, keep = [], True
+    while keep:
+        lik, conv, keep = em.iterate()
+        liks.append(lik)
+    assert len(liks) == len(ref["lik"]) == 21
+    assert np.max(np.abs(np.array(liks) - ref["lik"]) / np.abs(ref["lik"])) < LIK_RTOL
+    final = em.model()
+    assert rel_err(final.log_beta, ref["log_beta"], 1e-2) < MODEL_RTOL
+    assert rel_err(em.gamma(), ref["gamma"], 1e-3) < MODEL_RTOL
+    assert abs(final.alpha - ref["alpha"]) / ref["alpha"] < MODEL_RTOL
+    em.close()

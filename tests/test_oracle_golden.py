@@ -47,6 +47,28 @@ def test_infer_reproduces_reference_files(oracle, case):
     assert "".join("%5.5f\n" % x for x in lik) == (d / "inf-lda-lhood.dat").read_text()
 
 
+SEEDS = {"k5": (1001, 2.5), "k20": (2002, 2.5), "k20_fixed": (3003, 0.1), "k50": (4004, 2.5)}
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_random_start_run_reproduces_reference_files(oracle, case):
+    """`lda est ... random` with the fixture's RNG seed: MT19937 init + the whole EM, no float round trip."""
+    d = GOLD / case
+    seed, alpha0 = SEEDS[case]
+    st = oracle.read_settings(d / "settings.txt")
+    off, w, cn, tot, V = oracle.read_dat(d / "c.dat")
+    K = int((d / "000.other").read_text().split()[1])
+    L = oracle.lib()
+    L.oracle_mt_seed(seed)
+    lb = np.zeros((K, V))
+    L.oracle_random_init(K, V, lb)
+    res = oracle.run_em(off, w, cn, V, float(np.float32(alpha0)), lb, st)
+    lik = "".join("%10.10f\t%5.5e\n" % (l, c) for l, c in zip(res["lik"], res["conv"]))
+    assert lik == (d / "random.likelihood.dat").read_text()
+    assert fmt_gamma(res["gamma"]) == (d / "random.final.gamma").read_text()
+    assert fmt_model(res["alpha"], res["log_beta"])[1] == (d / "random.final.other").read_text()
+
+
 def test_parser_edge_cases_in_k5(oracle):
     """empty doc, single entry, entries split over lines, zero count (appended by make_golden.py)."""
     off, w, cn, tot, V = oracle.read_dat(GOLD / "k5" / "c.dat")
