@@ -35,6 +35,10 @@
 #include "device_math.cuh"
 #include "kernels.cuh"
 
+#ifndef ONILDA_PHI_AHEAD
+#define ONILDA_PHI_AHEAD 8
+#endif
+
 namespace onilda {
 
 // Sum / max over the G lanes of a group.  Always executed by the whole warp with the full
@@ -149,6 +153,7 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
             // A group that is idle at word n (document shorter than the bundle's longest, or already
             // converged) still runs the arithmetic, on count = 0 and beta' = 1: every update is then
             // multiplied by zero and nothing of it is stored.  That keeps the warp converged.
+            constexpr int kPhiAhead = ONILDA_PHI_AHEAD;
             auto load_ids = [&](int n, int& w, int& c) {
                 const bool on = active && n < len;
                 w = on ? a.words[beg + n] : -1;
@@ -161,6 +166,10 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
                 it.lbmax = on ? a.lbmax[w] : 0.0;
                 const double* brow = beta_scaled + (int64_t)w * KS + j;
                 const double* prow = phi + (beg + n) * KS + j;
+                // phi is the one stream that comes from HBM (17 GB at cfg 2, re-read every sweep); ask L2 for
+                // the row kPhiAhead words ahead so that the load one word ahead finds it there
+                if (kPhiAhead > 0 && !first && active && n + kPhiAhead < len)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(prow + (int64_t)kPhiAhead * KS));
 #pragma unroll
                 for (int t = 0; t < TPL; t++) {
                     it.beta[t] = (on && valid[t]) ? __ldg(brow + t * G) : (valid[t] ? 1.0 : 0.0);
