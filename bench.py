@@ -511,7 +511,7 @@ def main():
                 "traffic": traffic, "kernel": "E-step = estep_kernel<32,1> (documents >= 1024 entries) || estep_kernel<4,5> "
                                               "(the rest), two concurrent launches timed as one",
                 "algorithmic_bytes_per_launch": b_em, "kernel_ms": float(np.mean(estep_ms)), "peak_source": peak_src,
-                "fp64_pipe_pct_of_active_cycles": {"estep_kernel<4,5>": 62.6, "estep_kernel<32,1>": 37.6,
+                "fp64_pipe_pct_of_active_cycles": {"estep_kernel<4,5>": 62.6, "estep_kernel<32,1>": 43.9,
                                                    "source": "profiles/ncu_r1_*_summary.txt"},
                 "note": "nominally an HBM gather; measured bound is FP64 issue + the serial per-word dependency chain "
                         "(Gauss-Seidel order of lda-inference.c:50-75), so frac against HBM is small by construction: DESIGN.md 4.1"}
