@@ -310,7 +310,22 @@ def algorithmic_bytes(nnz, num_docs, K):
     return nnz * (8 + 16 * K) + num_docs * (16 + 8 * K)
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The one JSON line goes to the process's real stdout."""
+    data = (json.dumps(line, default=float) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
 def main():
+    # Libraries (NCCL's version banner, for one) write to file descriptor 1.  stdout must carry exactly one
+    # JSON line, so fd 1 is pointed at stderr for the duration and the line is written to a saved copy.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=18)
@@ -373,7 +388,7 @@ def main():
         with tempfile.TemporaryDirectory() as td:
             secs = time_reference(oni, corpus, model0, n_docs, n_iters, cores, td)
         if secs is None:
-            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/lda missing or failed on this box"}))
+            emit({"impl": "reference", "unavailable": "oracle/_ref/lda missing or failed on this box"})
             return 0
         timed = secs[args.warmup:] if len(secs) > args.warmup else secs
         tok = int(np.asarray(corpus.csr()[2][:offsets[n_docs]], np.int64).sum())
@@ -387,7 +402,7 @@ def main():
                 "cpu_baseline": {"value": val, "unit": "tokens/s", "cores": cores, "kind": "reference", "sample": sample},
                 "e2e": {"value": val, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
-        print(json.dumps(line, default=float))
+        emit(line)
         return 0
 
     # ------------------------------------------------------------ our arm: resident-in-HBM leg
@@ -560,7 +575,7 @@ def main():
             "em": {"estep_ms": [round(x, 3) for x in estep_ms], "mstep_ms_mean": float(np.mean(mstep_ms)),
                    "likelihood_first": liks[0], "likelihood_last": liks[-1], "sweeps_last_iter": int(sweeps),
                    "e2e_likelihood_last": e2e_liks[-1]}}
-    print(json.dumps(line, default=float))
+    emit(line)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
