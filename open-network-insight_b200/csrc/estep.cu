@@ -1,12 +1,17 @@
 // E-step of variational-EM LDA on sm_100a: the per-document fixed point
 // (reference: oni-ml/oni-lda-c/lda-inference.c:27-85), its likelihood bound
 // (:93-127) and the sufficient-statistics update of doc_e_step
-// (lda-estimate.c:28-60), for every document of a shard in ONE launch.
+// (lda-estimate.c:28-60), for every document of a shard in two concurrent
+// launches of one kernel template (em.cu): the documents of at least 1024
+// entries with G = 32, all others with G = 4 (K <= 32).
 //
 // Mapping
-//   * a document is owned by a group of G lanes (G = 4 for K <= 32); lane j
-//     keeps topics k = t*G + j in registers (gamma, digamma(gamma), E).  A warp
-//     therefore advances 32/G documents at once.
+//   * a document is owned by a group of G lanes; lane j keeps topics
+//     k = t*G + j in registers (gamma, E, and psi(gamma) as two parts).  A warp
+//     therefore advances 32/G documents at once.  G = 4 is the efficient form
+//     (no idle lanes at K = 20, 72 instructions per document-word); G = 32, one
+//     topic per lane, is the low-latency form for long documents, whose serial
+//     word chain would otherwise bound the whole E-step.
 //   * words of a document are visited strictly in file order and gamma /
 //     digamma are refreshed after EVERY word (lda-inference.c:66-74): the
 //     Gauss-Seidel order of the reference is kept; parallelism is over topics
@@ -22,7 +27,7 @@
 //     phi_nk = E_k beta'_kw / s_n,   s_n = sum_j E_j beta'_jw
 // which is the reference's exp(psi_k + log_beta_kw - log_sum) without a
 // log_sum/exp per (word, topic): one log per WORD (log s_n) remains.  Per (word,
-// topic) the update costs one reciprocal, one exp and one log (device_math.cuh).  shift is
+// topic) the update costs two reciprocals, one exp and one log (device_math.cuh).  shift is
 // psi(alpha + total/K), the value every topic starts from, so E starts at 1 and
 // s_n can neither overflow nor vanish in practice; if it ever leaves
 // [1e-290, 1e290] that word is redone in log space (the reference's own form).
