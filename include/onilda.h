@@ -148,7 +148,7 @@ int onilda_em_mstep(onilda_em* em, double* likelihood, double* converged, int* k
 /* Re-sends the shard's CSR arrays (from the corpus given to onilda_em_create,
  * which must still be alive) and `m` (alpha + log_beta) host -> device, and
  * resets the EM loop state: the handle is then as freshly created, without
- * reallocating.  With it one call sequence reload -> iterate -> get_model /
+ * reallocating.  Returns once the copies are done (the caller may reuse `m`).  With it one call sequence reload -> iterate -> get_model /
  * get_gamma is a stateless EM step on HOST buffers. */
 int onilda_em_reload(onilda_em* em, const onilda_model* m);
 /* estep + mstep for a single shard. */

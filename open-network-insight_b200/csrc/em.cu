@@ -317,6 +317,8 @@ extern "C" int onilda_em_reload(onilda_em* em, const onilda_model* m)
     em->likelihood_old = 0;
     em->converged = 1;
     em->estep_done = 0;
+    // the host arrays belong to the caller: they may be reused as soon as this returns
+    ONILDA_CUDA(cudaStreamSynchronize(em->stream));
     return ONILDA_OK;
 }
 
