@@ -303,6 +303,75 @@ def scoring_leg(oni, torch, device, gamma, log_beta, n_events, n_e2e, steps, pea
     return res
 
 
+def grouping_leg(oni, torch, device, offsets, words, counts, steps, peak, cpu=True):
+    """(document, word, count) triples in arrival order -> CSR corpus
+    (OniLDACWrapper.createModel).  The workload's own nnz entries, shuffled."""
+    D, n = len(offsets) - 1, int(offsets[-1])
+    lens = torch.from_numpy(np.diff(offsets)).to(device)
+    doc = torch.repeat_interleave(torch.arange(D, device=device, dtype=torch.int32), lens)
+    perm = torch.randperm(n, device=device, generator=torch.Generator(device=device).manual_seed(7))
+    doc = doc[perm].contiguous()
+    word = torch.from_numpy(np.asarray(words[:n])).to(device)[perm].contiguous()
+    cnt = torch.from_numpy(np.asarray(counts[:n])).to(device)[perm].contiguous()
+    del perm, lens
+    off = torch.empty(D + 1, dtype=torch.int64, device=device)
+    wo, co = torch.empty_like(word), torch.empty_like(cnt)
+    tot = torch.empty(D, dtype=torch.int32, device=device)
+    ml = torch.empty(1, dtype=torch.int32, device=device)
+    st = torch.cuda.current_stream().cuda_stream
+    L = oni.lib()
+
+    def run():
+        oni._check(L.onilda_triples_group_device(doc.data_ptr(), word.data_ptr(), cnt.data_ptr(), n, D, off.data_ptr(),
+                                                 wo.data_ptr(), co.data_ptr(), tot.data_ptr(), ml.data_ptr(), st))
+    for _ in range(3):
+        run()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    torch.cuda.synchronize()
+    ev[0].record()
+    for _ in range(steps):
+        run()
+    ev[1].record()
+    torch.cuda.synchronize()
+    sec = ev[0].elapsed_time(ev[1]) * 1e-3 / steps
+    order = torch.sort(doc, stable=True).indices
+    ok = bool(torch.equal(wo, word[order]) and torch.equal(co, cnt[order]) and
+              torch.equal(off.cpu(), torch.from_numpy(np.asarray(offsets, np.int64))) and int(ml.item()) == int(np.diff(offsets).max()))
+    del order
+    b_alg = 20 * n + 12 * D
+    bits = max(1, int(D - 1).bit_length())
+    passes = (bits + 7) // 8
+    res = {"triples": n, "num_docs": D, "triples_per_sec": n / sec, "unit": "triples/s", "ms": 1e3 * sec,
+           "matches_torch_stable_sort": ok, "gpu_launches_per_call": 5 * passes + 2,
+           "roofline": {"bound": "hbm", "kernel": "radix_scatter_kernel (x%d passes) + histogram/scan/totals/offsets" % passes,
+                        "achieved": b_alg / sec / 1e9, "peak": peak, "unit": "GB/s", "frac": b_alg / sec / 1e9 / peak,
+                        "algorithmic_bytes_per_launch": b_alg, "pass_bytes": (28 * passes + 8) * n, "traffic": None,
+                        "note": "algorithmic = triples in (12 B) + word,count out (8 B) + offsets,totals; the LSD sort moves "
+                                "28 B per triple per pass (4 B histogram read, 12 B in, 12 B out), pass_bytes in total"}}
+    hd, hw, hc = doc.cpu().numpy(), word.cpu().numpy(), cnt.cpu().numpy()
+    del doc, word, cnt, wo, co
+    ts = []
+    for it in range(3):
+        t0 = time.perf_counter()
+        c = oni.Corpus.from_triples(hd, hw, hc, num_docs=D)
+        if it >= 1:
+            ts.append(time.perf_counter() - t0)
+    res["e2e"] = {"value": n / float(np.mean(ts)), "unit": "triples/s", "h2d_bytes_per_step": 12 * n,
+                  "d2h_bytes_per_step": 8 * n + 12 * D, "note": "pageable host arrays in, host corpus out (onilda_corpus_from_triples)"}
+    if cpu:
+        m = min(n, 20_000_000)
+        t0 = time.perf_counter()
+        o = np.argsort(hd[:m], kind="stable")
+        w2, c2 = hw[:m][o], hc[:m][o]
+        lens2 = np.bincount(hd[:m], minlength=D)
+        dt = time.perf_counter() - t0
+        res["cpu_baseline"] = {"value": m / dt, "unit": "triples/s", "cores": 1, "kind": "port",
+                               "sample": f"first {m} triples, numpy stable argsort + gathers + bincount (oracle_py.triples_to_csr's "
+                                         "steps; the Spark groupByKey original cannot run here: no JVM)"}
+        del o, w2, c2, lens2
+    return res
+
+
 # ----------------------------------------------------------------- main
 
 def algorithmic_bytes(nnz, num_docs, K):
@@ -337,6 +406,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true", help="development only")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-scoring", action="store_true")
+    ap.add_argument("--no-grouping", action="store_true")
     ap.add_argument("--events", type=int, default=1_000_000_000, help="flow events of the scoring leg (configs[4])")
     args = ap.parse_args()
     if args.warmup < 3:
@@ -543,6 +613,16 @@ def main():
                               cpu_cores=0 if args.no_cpu_baseline else host_cores())
         del gamma, log_beta
 
+    # ------------------------------------------------------------ grouping leg (rank 0, one GPU)
+    grouping = None
+    if not args.no_grouping:
+        if args.no_scoring:
+            em.close()
+        torch.cuda.empty_cache()
+        _, w_all, c_all, _ = corpus.csr()
+        grouping = grouping_leg(oni, torch, device, np.asarray(offsets), w_all, c_all, 5, peak,
+                                cpu=not args.no_cpu_baseline)
+
     # ------------------------------------------------------------ CPU baseline (reference lda-c on this box)
     cpu_baseline = None
     if not args.no_cpu_baseline:
@@ -571,7 +651,7 @@ def main():
                        "parallelism": f"dp{world} over documents", "scale": args.scale},
             "nnz_per_sec": N_all / (elapsed / args.steps),
             "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
-            "cpu_baseline": cpu_baseline, "scoring": scoring,
+            "cpu_baseline": cpu_baseline, "scoring": scoring, "grouping": grouping,
             "em": {"estep_ms": [round(x, 3) for x in estep_ms], "mstep_ms_mean": float(np.mean(mstep_ms)),
                    "likelihood_first": liks[0], "likelihood_last": liks[-1], "sweeps_last_iter": int(sweeps),
                    "e2e_likelihood_last": e2e_liks[-1]}}

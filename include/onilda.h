@@ -78,6 +78,24 @@ int onilda_corpus_from_dat(const char* path, onilda_corpus** out);
  * the data as read_data does; a larger value is kept (vocabulary with unseen ids). */
 int onilda_corpus_from_csr(const int64_t* offsets, const int32_t* words, const int32_t* counts,
                            int64_t num_docs, int32_t num_terms, onilda_corpus** out);
+/* SURVEY section 8(f) row N1.  Replaces the grouping half of OniLDACWrapper.createModel
+ * (OniLDACWrapper.scala:146-168) together with the model.dat round trip through read_data
+ * (lda-data.c:22-59): n (document id, word id, count) triples, in any order, become the CSR
+ * corpus.  Documents come out in id order (the order of `distinctDocument`), the entries of a
+ * document keep their input order (createModelTest: ("192.168.1.1",w0,8), ("10.10.98.123",w1,4),
+ * ("66.23.45.11",w2,2), ("192.168.1.1",w3,5) -> "2 0:8 3:5", "1 1:4", "1 2:2"), repeated words
+ * stay separate entries as read_data keeps them.  num_docs 0 = max id + 1; ids that never occur
+ * are empty documents.  The grouping is a stable radix sort on `device` (-1: current); the host
+ * arrays may be pageable.  n < 2^31. */
+int onilda_corpus_from_triples(const int32_t* doc, const int32_t* word, const int32_t* count, int64_t n,
+                               int64_t num_docs, int32_t num_terms, int device, onilda_corpus** out);
+/* The same grouping with everything in device memory, ordered on `stream` (a cudaStream_t), no
+ * synchronisation: offsets_out[num_docs + 1], words_out[n], counts_out[n]; totals_out[num_docs]
+ * (int sum of counts per document, lda.h:27) and max_len_out[1] may be null.  Ids must already be in
+ * range.  Scratch (about 16 bytes per triple) comes from the device's stream-ordered pool. */
+int onilda_triples_group_device(const int32_t* doc, const int32_t* word, const int32_t* count, int64_t n,
+                                int64_t num_docs, int64_t* offsets_out, int32_t* words_out, int32_t* counts_out,
+                                int32_t* totals_out, int32_t* max_len_out, void* stream);
 int onilda_corpus_dims(const onilda_corpus* c, int64_t* num_docs, int64_t* nnz, int32_t* num_terms,
                        int64_t* tokens, int32_t* max_len);
 /* Borrowed views of the CSR arrays (valid until onilda_corpus_free). */

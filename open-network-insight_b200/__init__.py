@@ -71,6 +71,8 @@ def lib():
     L.onilda_settings_read.argtypes = [C.c_char_p, C.POINTER(Settings)]
     L.onilda_corpus_from_dat.argtypes = [C.c_char_p, C.POINTER(_vp)]
     L.onilda_corpus_from_csr.argtypes = [_i64p, _vp, _vp, C.c_int64, C.c_int32, C.POINTER(_vp)]
+    L.onilda_corpus_from_triples.argtypes = [_vp, _vp, _vp, C.c_int64, C.c_int64, C.c_int32, C.c_int, C.POINTER(_vp)]
+    L.onilda_triples_group_device.argtypes = [_vp, _vp, _vp, C.c_int64, C.c_int64, _vp, _vp, _vp, _vp, _vp, _vp]
     L.onilda_corpus_dims.argtypes = [_vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int32),
                                      C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
     L.onilda_corpus_csr.argtypes = [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp)]
@@ -171,6 +173,20 @@ class Corpus:
         counts = np.ascontiguousarray(counts, np.int32)
         h = _vp()
         _check(lib().onilda_corpus_from_csr(offsets, _ptr(words), _ptr(counts), len(offsets) - 1, num_terms, C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def from_triples(cls, doc, word, count, num_docs=0, num_terms=0, device=-1):
+        """(document id, word id, count) triples -> corpus, grouped on the GPU
+        (OniLDACWrapper.createModel, OniLDACWrapper.scala:146-168)."""
+        doc = np.ascontiguousarray(doc, np.int32)
+        word = np.ascontiguousarray(word, np.int32)
+        count = np.ascontiguousarray(count, np.int32)
+        if not (len(doc) == len(word) == len(count)):
+            raise ValueError("doc, word and count must have the same length")
+        h = _vp()
+        _check(lib().onilda_corpus_from_triples(_ptr(doc), _ptr(word), _ptr(count), len(doc), num_docs, num_terms,
+                                                device, C.byref(h)))
         return cls(h)
 
     def save_dat(self, path, doc_begin=0, doc_end=None):

@@ -235,6 +235,28 @@ def topk(scores, threshold, k):
     return idx[:m].copy(), sc[:m].copy()
 
 
+def triples_to_csr(doc, word, count, num_docs=0):
+    """OniLDACWrapper.createModel (OniLDACWrapper.scala:146-168) followed by read_data
+    (lda-data.c:22-59), without the text in between: documents in id order (the position in
+    `distinctDocument`), entries of a document in input order, repeated words kept.
+    Returns (offsets, words, counts)."""
+    doc = np.asarray(doc, np.int64)
+    if num_docs == 0:
+        num_docs = int(doc.max()) + 1 if len(doc) else 0
+    order = np.argsort(doc, kind="stable")
+    lens = np.bincount(doc, minlength=num_docs) if len(doc) else np.zeros(num_docs, np.int64)
+    offsets = np.zeros(num_docs + 1, np.int64)
+    np.cumsum(lens, out=offsets[1:])
+    return offsets, np.asarray(word, np.int32)[order], np.asarray(count, np.int32)[order]
+
+
+def dat_lines(offsets, words, counts):
+    """The model.dat lines createModel returns for a CSR corpus."""
+    return [" ".join([str(int(offsets[d + 1] - offsets[d]))] +
+                     ["%d:%d" % (w, c) for w, c in zip(words[offsets[d]:offsets[d + 1]], counts[offsets[d]:offsets[d + 1]])])
+            for d in range(len(offsets) - 1)]
+
+
 def run_ref(args, cwd, seed=None, nproc=1, timeout=3600):
     """Run the unmodified reference binary (oracle/_ref/lda).  Returns CompletedProcess."""
     if not REF_BIN.exists():

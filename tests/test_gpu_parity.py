@@ -485,3 +485,66 @@ def test_full_default_run_against_oracle(oni, oracle, corpusgen):
     assert rel_err(em.gamma(), ref["gamma"], 1e-3) < MODEL_RTOL
     assert abs(final.alpha - ref["alpha"]) / ref["alpha"] < MODEL_RTOL
     em.close()
+
+
+# ---------------------------------------------------------------- N1: triples -> corpus (createModel)
+def csr_of(c):
+    off, w, cnt, _ = c.csr()
+    return np.array(off), np.array(w), np.array(cnt)
+
+
+def test_triples_create_model_golden(oni, oracle, tmp_path):
+    """OniLDACWrapperTest.scala:53-75: the model.dat lines of createModel, bit for bit."""
+    c = oni.Corpus.from_triples([0, 1, 2, 0], [0, 1, 2, 3], [8, 4, 2, 5])
+    c.save_dat(tmp_path / "model.dat")
+    assert (tmp_path / "model.dat").read_text().splitlines() == ["2 0:8 3:5", "1 1:4", "1 2:2"]
+    assert c.num_docs == 3 and c.num_terms == 4
+
+
+@pytest.mark.parametrize("n,num_docs,V", [(1, 1, 1), (255, 3, 7), (2049, 257, 50), (100_000, 70_000, 3000),
+                                          (3_000_000, 1_000_003, 25_000), (500_000, 2, 5)])
+def test_triples_match_oracle(oni, oracle, n, num_docs, V):
+    """Stable grouping by document id: index-exact against the numpy restatement, across one to three
+    radix passes, partial tiles, empty documents and repeated (doc, word) pairs."""
+    rng = np.random.default_rng(n + num_docs)
+    doc = (rng.zipf(1.3, n) % num_docs).astype(np.int32) if n > 1000 else rng.integers(0, num_docs, n).astype(np.int32)
+    word = rng.integers(0, V, n).astype(np.int32)
+    count = rng.integers(1, 1000, n).astype(np.int32)
+    c = oni.Corpus.from_triples(doc, word, count, num_docs=num_docs, num_terms=V)
+    off, w, cnt = csr_of(c)
+    roff, rw, rc = oracle.triples_to_csr(doc, word, count, num_docs)
+    assert np.array_equal(off, roff) and np.array_equal(w, rw) and np.array_equal(cnt, rc)
+    assert c.num_docs == num_docs and c.num_terms == V
+
+
+def test_triples_edge_cases(oni, oracle):
+    c = oni.Corpus.from_triples([], [], [], num_docs=4, num_terms=3)       # no triples: four empty documents
+    assert c.num_docs == 4 and c.nnz == 0
+    c = oni.Corpus.from_triples([], [], [])
+    assert c.num_docs == 0
+    with pytest.raises(oni.OnildaError):
+        oni.Corpus.from_triples([0, -1], [0, 0], [1, 1])
+    with pytest.raises(oni.OnildaError):
+        oni.Corpus.from_triples([0, 5], [0, 0], [1, 1], num_docs=5)
+    # already grouped input comes back unchanged; reversed input keeps per-document order
+    doc = np.repeat(np.arange(1000, dtype=np.int32), 3)
+    word = np.arange(3000, dtype=np.int32)
+    cnt = np.ones(3000, np.int32)
+    off, w, _ = csr_of(oni.Corpus.from_triples(doc, word, cnt))
+    assert np.array_equal(w, word) and np.array_equal(off, np.arange(0, 3001, 3))
+    off, w, _ = csr_of(oni.Corpus.from_triples(doc[::-1].copy(), word, cnt))
+    assert np.array_equal(w.reshape(1000, 3), word.reshape(1000, 3)[::-1])
+
+
+def test_triples_then_em_equals_dat_route(oni, oracle, corpusgen, tmp_path):
+    """The reference's route (createModel -> model.dat -> read_data) and the triple route give the same
+    corpus, hence the same E-step."""
+    g = corpusgen.generate(3000, 200, 4000, 20, seed=5)
+    docs = np.repeat(np.arange(len(g.offsets) - 1), np.diff(g.offsets)).astype(np.int32)
+    perm = np.random.default_rng(1).permutation(len(docs))
+    c1 = oni.Corpus.from_triples(docs[perm], g.words[perm], g.counts[perm])
+    off, w, cnt = csr_of(c1)
+    (tmp_path / "model.dat").write_text("\n".join(oracle.dat_lines(off, w, cnt)) + "\n")
+    c2 = oni.Corpus.from_dat(tmp_path / "model.dat")
+    for a, b in zip(csr_of(c1), csr_of(c2)):
+        assert np.array_equal(a, b)

@@ -178,3 +178,18 @@ def test_score_restatement_small(oracle):
     assert list(idx) == [1, 3, 4] and list(sc) == [0.1, 0.1, 0.2]
     idx, sc = oracle.topk(np.array([0.3, 0.1, 0.9, 0.1, 0.2]), 0.3, -1)
     assert list(idx) == [1, 3, 4, 0]
+
+
+# OniLDACWrapperTest.scala:53-75 ("createModel"): document ids are positions in distinctDocument
+# (192.168.1.1 -> 0, 10.10.98.123 -> 1, 66.23.45.11 -> 2), word ids come from wordDictionary.
+CREATE_MODEL_TRIPLES = ([0, 1, 2, 0], [0, 1, 2, 3], [8, 4, 2, 5])
+CREATE_MODEL_LINES = ["2 0:8 3:5", "1 1:4", "1 2:2"]
+
+
+def test_create_model_golden(oracle):
+    off, w, c = oracle.triples_to_csr(*CREATE_MODEL_TRIPLES)
+    assert oracle.dat_lines(off, w, c) == CREATE_MODEL_LINES
+    # ids that never occur are empty documents; order inside a document is input order
+    off, w, c = oracle.triples_to_csr([3, 0, 3, 3], [5, 6, 1, 5], [1, 2, 3, 4], num_docs=5)
+    assert list(off) == [0, 1, 1, 1, 4, 4]
+    assert list(w) == [6, 5, 1, 5] and list(c) == [2, 1, 3, 4]
