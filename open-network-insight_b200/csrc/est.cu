@@ -7,6 +7,7 @@
 #include <string.h>
 #include <sys/stat.h>
 
+#include <chrono>
 #include <string>
 #include <vector>
 
@@ -150,6 +151,12 @@ extern "C" int onilda_run_em(const char* start, const char* directory, const oni
     rc = onilda_model_save(model, (dir + "/000").c_str());
     if (rc != ONILDA_OK) { onilda_model_free(model); return rc; }
 
+    const bool timing = getenv("ONILDA_TIMING") != nullptr;
+    const auto now = [] { return std::chrono::steady_clock::now(); };
+    const auto secs = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+        return std::chrono::duration<double>(b - a).count();
+    };
+    const auto t_setup = now();
     EmSet set;
     std::vector<int64_t> bounds;
     split_by_nnz(c, ndev, bounds);
@@ -163,6 +170,7 @@ extern "C" int onilda_run_em(const char* start, const char* directory, const oni
     FILE* lf = fopen((dir + "/likelihood.dat").c_str(), "w");
     if (!lf) { onilda_model_free(model); return onilda_fail(ONILDA_EIO, "cannot write %s/likelihood.dat", directory); }
 
+    const auto t_em = now();
     // lda-estimate.c:186: the loop is entered at least once (i = 0 <= 2 and 0 <= EM_MAX_ITER for any sane setting)
     int keep = (0 <= settings->em_max_iter);
     int iter = 0;
@@ -182,6 +190,7 @@ extern "C" int onilda_run_em(const char* start, const char* directory, const oni
     if (rc != ONILDA_OK) { onilda_model_free(model); return rc; }
 
     // final model + gamma (lda-estimate.c:272-317); each shard owns its gamma rows, no gather traffic
+    const auto t_save = now();
     rc = onilda_em_get_model(set.ems[0], model);
     if (rc == ONILDA_OK) rc = onilda_model_save(model, (dir + "/final").c_str());
     if (rc == ONILDA_OK) {
@@ -190,6 +199,9 @@ extern "C" int onilda_run_em(const char* start, const char* directory, const oni
             rc = onilda_em_get_gamma(set.ems[(size_t)r], gamma.data() + (size_t)bounds[(size_t)r] * num_topics);
         if (rc == ONILDA_OK) rc = onilda_gamma_save((dir + "/final.gamma").c_str(), gamma.data(), c->num_docs, num_topics);
     }
+    if (timing)
+        fprintf(stderr, "[timing] device setup %.3f s, %d EM iterations %.3f s, final.* %.3f s\n", secs(t_setup, t_em), iter,
+                secs(t_em, t_save), secs(t_save, now()));
     onilda_model_free(model);
     return rc;
 }

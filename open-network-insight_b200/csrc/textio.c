@@ -9,9 +9,11 @@
  */
 #include <ctype.h>
 #include <math.h>
+#include <pthread.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <unistd.h>
 
 #include "onilda_internal.h"
 
@@ -86,6 +88,160 @@ static void corpus_finish(onilda_corpus* c)
     c->max_len = max_len;
 }
 
+/* Host threads for parsing and printing the text files (ONILDA_IO_THREADS overrides; 1 = the
+ * sequential code only).  The files are the reference's interface, not its hot path, but at
+ * cfg 2 (1 GB of model.dat, 280 MB of final.gamma) one thread of text work would outlast EM. */
+static int io_threads(void)
+{
+    const char* e = getenv("ONILDA_IO_THREADS");
+    long n = e && *e ? atol(e) : sysconf(_SC_NPROCESSORS_ONLN);
+    if (n < 1) n = 1;
+    if (n > 64) n = 64;
+    return (int)n;
+}
+
+/* ---- parallel reader for the canonical layout
+ * OniLDACWrapper.createModel (OniLDACWrapper.scala:146-168) writes one document per line:
+ * "<n> <w>:<c> ... <w>:<c>\n", plain decimal, single spaces.  On such a file every line can be
+ * parsed on its own, and what a line yields is by construction what read_data's token stream
+ * yields (numbers of at most 9 digits never meet "%10d"'s width limit or int overflow).  Any
+ * deviation - a sign, a longer number, a pair missing or in excess, another separator - makes
+ * the chunk give up and the whole file goes through the sequential scanf emulation below, which
+ * is the definition of the format. */
+typedef struct {
+    const unsigned char* begin;
+    const unsigned char* end;
+    int64_t docs, nnz;          /* pass 1: lines with content, ':' characters */
+    int64_t doc0, nnz0;         /* pass 2: where this chunk's output starts */
+    onilda_corpus* c;
+    int nterms;
+    int ok;
+} dat_chunk;
+
+static void* dat_count(void* arg)
+{
+    dat_chunk* k = (dat_chunk*)arg;
+    int64_t docs = 0, nnz = 0;
+    int content = 0;
+    for (const unsigned char* p = k->begin; p < k->end; p++) {
+        unsigned char ch = *p;
+        if (ch == '\n') { docs += content; content = 0; }
+        else if (ch == ':') { nnz++; content = 1; }
+        else if (ch != ' ' && ch != '\r' && ch != '\t') content = 1;
+    }
+    k->docs = docs + content;
+    k->nnz = nnz;
+    return NULL;
+}
+
+/* decimal digits, 1..9 of them; returns the value or -1 */
+static inline int64_t canon_uint(const unsigned char** pp, const unsigned char* end)
+{
+    const unsigned char* p = *pp;
+    int64_t v = 0;
+    int nd = 0;
+    while (p < end && *p >= '0' && *p <= '9' && nd < 10) { v = v * 10 + (*p - '0'); p++; nd++; }
+    if (nd == 0 || nd > 9) return -1;
+    *pp = p;
+    return v;
+}
+
+static void* dat_parse(void* arg)
+{
+    dat_chunk* k = (dat_chunk*)arg;
+    onilda_corpus* c = k->c;
+    const unsigned char* p = k->begin;
+    const unsigned char* end = k->end;
+    int64_t d = k->doc0, e = k->nnz0;
+    const int64_t d_end = k->doc0 + k->docs, e_end = k->nnz0 + k->nnz;
+    int nterms = 0;
+    k->ok = 0;
+    while (p < end) {
+        if (*p == '\n') { p++; continue; }                      /* empty line: white space to read_data */
+        int64_t len = canon_uint(&p, end);
+        if (len < 0 || d >= d_end || e + len > e_end) return NULL;
+        int total = 0;
+        for (int64_t n = 0; n < len; n++) {
+            if (p >= end || *p != ' ') return NULL;
+            p++;
+            int64_t w = canon_uint(&p, end);
+            if (w < 0 || p >= end || *p != ':') return NULL;
+            p++;
+            int64_t cnt = canon_uint(&p, end);
+            if (cnt < 0) return NULL;
+            c->words[e] = (int32_t)w;
+            c->counts[e] = (int32_t)cnt;
+            e++;
+            total = (int)((unsigned int)total + (unsigned int)cnt);
+            if (w >= nterms) nterms = (int)w + 1;
+        }
+        if (p < end && *p == '\r') p++;
+        if (p < end && *p != '\n') return NULL;
+        p++;
+        c->totals[d] = total;
+        c->offsets[d + 1] = len;                                  /* lengths now, prefix sums after the join */
+        d++;
+    }
+    if (d != d_end || e != e_end) return NULL;
+    k->nterms = nterms;
+    k->ok = 1;
+    return NULL;
+}
+
+/* Returns 1 with *out set, 0 when the file is not in the canonical layout (caller falls back),
+ * or a negative error code. */
+static int corpus_from_dat_parallel(const unsigned char* text, size_t size, int threads, onilda_corpus** out)
+{
+    dat_chunk ch[64];
+    pthread_t tid[64];
+    int T = threads;
+    if ((size_t)T > size / (1u << 20) + 1) T = (int)(size / (1u << 20) + 1);
+    const unsigned char* pos = text;
+    const unsigned char* end = text + size;
+    int used = 0;
+    for (int t = 0; t < T && pos < end; t++) {
+        const unsigned char* stop = t == T - 1 ? end : text + (size / (size_t)T) * (size_t)(t + 1);
+        if (stop < pos) stop = pos;
+        while (stop < end && stop[-1] != '\n' && stop > pos) stop++;      /* to the end of the line */
+        if (stop == pos && pos < end) { const unsigned char* nl = memchr(pos, '\n', (size_t)(end - pos)); stop = nl ? nl + 1 : end; }
+        ch[used].begin = pos;
+        ch[used].end = stop;
+        pos = stop;
+        used++;
+    }
+    if (pos < end) { ch[used - 1].end = end; }
+    T = used;
+    for (int t = 1; t < T; t++) pthread_create(&tid[t], NULL, dat_count, &ch[t]);
+    dat_count(&ch[0]);
+    for (int t = 1; t < T; t++) pthread_join(tid[t], NULL);
+    int64_t docs = 0, nnz = 0;
+    for (int t = 0; t < T; t++) { ch[t].doc0 = docs; ch[t].nnz0 = nnz; docs += ch[t].docs; nnz += ch[t].nnz; }
+    onilda_corpus* c = (onilda_corpus*)calloc(1, sizeof *c);
+    if (!c) return ONILDA_ENOMEM;
+    c->offsets = (int64_t*)malloc(sizeof(int64_t) * (size_t)(docs + 1));
+    c->totals = (int32_t*)malloc(sizeof(int32_t) * (size_t)(docs > 0 ? docs : 1));
+    c->words = (int32_t*)malloc(sizeof(int32_t) * (size_t)(nnz > 0 ? nnz : 1));
+    c->counts = (int32_t*)malloc(sizeof(int32_t) * (size_t)(nnz > 0 ? nnz : 1));
+    if (!c->offsets || !c->totals || !c->words || !c->counts) { onilda_corpus_free(c); return ONILDA_ENOMEM; }
+    for (int t = 0; t < T; t++) ch[t].c = c;
+    for (int t = 1; t < T; t++) pthread_create(&tid[t], NULL, dat_parse, &ch[t]);
+    dat_parse(&ch[0]);
+    for (int t = 1; t < T; t++) pthread_join(tid[t], NULL);
+    int nterms = 0;
+    for (int t = 0; t < T; t++) {
+        if (!ch[t].ok) { onilda_corpus_free(c); return 0; }
+        if (ch[t].nterms > nterms) nterms = ch[t].nterms;
+    }
+    c->offsets[0] = 0;
+    for (int64_t d = 0; d < docs; d++) c->offsets[d + 1] += c->offsets[d];
+    c->num_docs = docs;
+    c->nnz = nnz;
+    c->num_terms = nterms;
+    corpus_finish(c);
+    *out = c;
+    return 1;
+}
+
 /* read_data (lda-data.c:22-59) into CSR. */
 int onilda_corpus_from_dat(const char* path, onilda_corpus** out)
 {
@@ -102,6 +258,18 @@ int onilda_corpus_from_dat(const char* path, onilda_corpus** out)
         return onilda_fail(ONILDA_EIO, "short read on %s", path);
     }
     fclose(f);
+
+    {
+        const int threads = io_threads();
+        if (threads > 1 && size > 0) {
+            int pr = corpus_from_dat_parallel(text, (size_t)size, threads, out);
+            if (pr != 0) {
+                free(text);
+                if (pr < 0) return onilda_fail(pr, "corpus %s: out of host memory", path);
+                return ONILDA_OK;
+            }
+        }
+    }
 
     onilda_corpus* c = (onilda_corpus*)calloc(1, sizeof *c);
     int64_t dcap = 0, tcap = 0, ncap_w = 0, ncap_c = 0;
@@ -356,6 +524,71 @@ int onilda_format_fixed10(double v, char* out)
     return (int)(p - out);
 }
 
+/* ---- parallel "%5.10f" matrix printer (save_lda_model's .beta, save_gamma)
+ * The flat element range is split over the host threads; each formats its part into its own
+ * buffer, the buffers are written in order.  lead != 0: a space before every number (.beta),
+ * else a space between numbers (.gamma). */
+typedef struct {
+    const double* v;
+    int64_t begin, end;
+    int cols, lead;
+    char* buf;
+    size_t len;
+    int failed;
+} fmt_job;
+
+static void* fmt_worker(void* arg)
+{
+    fmt_job* j = (fmt_job*)arg;
+    size_t cap = (size_t)(j->end - j->begin) * 20 + 1024;
+    char* buf = (char*)malloc(cap);
+    char* p = buf;
+    j->failed = buf == NULL;
+    if (!buf) return NULL;
+    int col = (int)(j->begin % j->cols);
+    for (int64_t i = j->begin; i < j->end; i++) {
+        if ((size_t)(p - buf) + 400 > cap) {                     /* "%5.10f" of a huge value is long */
+            size_t used = (size_t)(p - buf);
+            cap = cap * 2 + 1024;
+            char* nb = (char*)realloc(buf, cap);
+            if (!nb) { free(buf); j->failed = 1; return NULL; }
+            buf = nb;
+            p = buf + used;
+        }
+        if (j->lead || col) *p++ = ' ';
+        p += onilda_format_fixed10(j->v[i], p);
+        if (++col == j->cols) { *p++ = '\n'; col = 0; }
+    }
+    j->buf = buf;
+    j->len = (size_t)(p - buf);
+    return NULL;
+}
+
+static int write_matrix(FILE* f, const double* v, int64_t rows, int cols, int lead, const char* name)
+{
+    const int64_t n = rows * (int64_t)cols;
+    if (n == 0) return ONILDA_OK;
+    int T = io_threads();
+    if (n < 200000) T = 1;
+    fmt_job job[64];
+    pthread_t tid[64];
+    for (int t = 0; t < T; t++) {
+        job[t].v = v; job[t].cols = cols; job[t].lead = lead; job[t].buf = NULL; job[t].len = 0; job[t].failed = 0;
+        job[t].begin = n * t / T;
+        job[t].end = n * (t + 1) / T;
+    }
+    for (int t = 1; t < T; t++) pthread_create(&tid[t], NULL, fmt_worker, &job[t]);
+    fmt_worker(&job[0]);
+    for (int t = 1; t < T; t++) pthread_join(tid[t], NULL);
+    int rc = ONILDA_OK;
+    for (int t = 0; t < T && rc == ONILDA_OK; t++) {
+        if (job[t].failed) rc = onilda_fail(ONILDA_ENOMEM, "out of memory while formatting %s", name);
+        else if (job[t].len && fwrite(job[t].buf, 1, job[t].len, f) != job[t].len) rc = onilda_fail(ONILDA_EIO, "write failed on %s", name);
+    }
+    for (int t = 0; t < T; t++) free(job[t].buf);
+    return rc;
+}
+
 /* save_lda_model (lda-model.c:193-217), byte for byte; written to a temporary
  * name and renamed so a failed run never leaves a partial final.* behind. */
 int onilda_model_save(const onilda_model* m, const char* model_root)
@@ -375,16 +608,7 @@ int onilda_model_save(const onilda_model* m, const char* model_root)
     sprintf(tmpname, "%s.beta.tmp", model_root);
     FILE* f = fopen(tmpname, "w");
     if (!f) { rc = onilda_fail(ONILDA_EIO, "cannot write %s", tmpname); goto out; }
-    for (int k = 0; k < K; k++) {
-        char* p = line;
-        const double* row = m->log_beta + (size_t)k * V;
-        for (int w = 0; w < V; w++) {
-            *p++ = ' ';
-            p += onilda_format_fixed10(row[w], p);
-        }
-        *p++ = '\n';
-        if (fwrite(line, 1, (size_t)(p - line), f) != (size_t)(p - line)) { rc = onilda_fail(ONILDA_EIO, "write failed on %s", tmpname); break; }
-    }
+    rc = write_matrix(f, m->log_beta, K, V, 1, tmpname);
     if (fclose(f) != 0 && rc == ONILDA_OK) rc = onilda_fail(ONILDA_EIO, "close failed on %s", tmpname);
     if (rc != ONILDA_OK) { remove(tmpname); goto out; }
     if (rename(tmpname, name) != 0) { rc = onilda_fail(ONILDA_EIO, "cannot rename %s", tmpname); goto out; }
@@ -476,16 +700,7 @@ int onilda_gamma_save(const char* path, const double* gamma, int64_t num_docs, i
     int rc = ONILDA_OK;
     FILE* f = fopen(tmpname, "w");
     if (!f) { rc = onilda_fail(ONILDA_EIO, "cannot write %s", tmpname); goto out; }
-    for (int64_t d = 0; d < num_docs; d++) {
-        const double* row = gamma + d * num_topics;
-        char* p = line;
-        for (int k = 0; k < num_topics; k++) {
-            if (k) *p++ = ' ';
-            p += onilda_format_fixed10(row[k], p);
-        }
-        *p++ = '\n';
-        if (fwrite(line, 1, (size_t)(p - line), f) != (size_t)(p - line)) { rc = onilda_fail(ONILDA_EIO, "write failed on %s", tmpname); break; }
-    }
+    rc = write_matrix(f, gamma, num_docs, num_topics, 0, tmpname);
     if (fclose(f) != 0 && rc == ONILDA_OK) rc = onilda_fail(ONILDA_EIO, "close failed on %s", tmpname);
     if (rc != ONILDA_OK) { remove(tmpname); goto out; }
     if (rename(tmpname, path) != 0) rc = onilda_fail(ONILDA_EIO, "cannot rename %s", tmpname);

@@ -59,7 +59,12 @@ int main(int argc, char* argv[])
         int ntopics = atoi(argv[3]);
         int ndev = atoi(argv[5]);
         if (onilda_settings_read(argv[4], &settings) != 0) return die("settings");
+        struct timespec t0, t1;
+        clock_gettime(CLOCK_MONOTONIC, &t0);
         if (onilda_corpus_from_dat(argv[6], &corpus) != 0) return die("corpus");
+        clock_gettime(CLOCK_MONOTONIC, &t1);
+        if (getenv("ONILDA_TIMING"))
+            fprintf(stderr, "[timing] read %s: %.3f s\n", argv[6], (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec));
         int64_t D, N; int32_t V;
         onilda_corpus_dims(corpus, &D, &N, &V, NULL, NULL);
         printf("number of docs    : %lld\n", (long long)D);

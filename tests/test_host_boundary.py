@@ -215,3 +215,68 @@ def test_compute_fails_loudly_without_gpu(oni):
         oni.Scorer(np.ones((2, 3)) / 3, np.ones((4, 3)) / 4)
     with pytest.raises(oni.OnildaError):
         oni.infer(m, c, oni.Settings.default())
+
+
+def _csr_equal(a, b):
+    return (a.num_docs == b.num_docs and a.num_terms == b.num_terms and a.tokens == b.tokens and a.max_len == b.max_len
+            and all(np.array_equal(x, y) for x, y in zip(a.csr(), b.csr())))
+
+
+def test_parallel_reader_equals_sequential(oni, tmp_path, monkeypatch):
+    """Files in createModel's layout are parsed by several host threads; the result must be what the
+    sequential scanf emulation (the definition of the format) gives, and anything else must fall back."""
+    rng = np.random.default_rng(11)
+    D = 120_000
+    lens = rng.integers(0, 12, D)
+    lens[::1000] = 400
+    off = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    w = rng.integers(0, 999_999_999, off[-1]).astype(np.int32)      # up to nine digits
+    cnt = rng.integers(0, 5000, off[-1]).astype(np.int32)
+    big = tmp_path / "big.dat"
+    oni.Corpus.from_csr(off, w, cnt).save_dat(big)
+    assert big.stat().st_size > 6 << 20                              # several chunks
+    variants = {"plain": big.read_bytes()}
+    variants["no_final_newline"] = variants["plain"][:-1]
+    variants["crlf_and_blank_lines"] = variants["plain"].replace(b"\n", b"\r\n", 50).replace(b"\n4", b"\n\n\n4", 30)
+    # not canonical somewhere in the middle: a tab, a sign, a pair moved to the next line, a ten-digit count
+    mid = len(variants["plain"]) // 2
+    nl = variants["plain"].index(b"\n", mid) + 1
+    while True:                                                      # a document with at least two entries
+        line_end = variants["plain"].index(b"\n", nl)
+        line = variants["plain"][nl:line_end]
+        if line.count(b" ") >= 2:
+            break
+        nl = line_end + 1
+    def patched(new_line):
+        return variants["plain"][:nl] + new_line + variants["plain"][line_end:]
+    variants["tab"] = patched(line.replace(b" ", b"\t", 1))
+    variants["plus"] = patched(line.replace(b" ", b" +", 1))
+    variants["split_line"] = patched(line[::-1].replace(b" ", b"\n", 1)[::-1])
+    variants["ten_digits"] = patched(line + b"\n1 7:1234567890")
+    for name, data in variants.items():
+        p = tmp_path / (name + ".dat")
+        p.write_bytes(data)
+        monkeypatch.setenv("ONILDA_IO_THREADS", "1")
+        seq = oni.Corpus.from_dat(p)
+        for threads in ("2", "7"):
+            monkeypatch.setenv("ONILDA_IO_THREADS", threads)
+            assert _csr_equal(oni.Corpus.from_dat(p), seq), (name, threads)
+    assert 1234567890 in seq.csr()[2]                                # the fallback really parsed the odd line
+
+
+def test_parallel_writer_is_byte_identical(oni, tmp_path, monkeypatch):
+    rng = np.random.default_rng(3)
+    g = np.exp(rng.uniform(-25, 12, (30_011, 20)))
+    g[5, 3] = 1e17                                                   # long "%5.10f" output inside a chunk
+    m = oni.Model.new(7, 40_003)
+    m.log_beta[...] = -np.exp(rng.uniform(-3, 5, (7, 40_003)))
+    out = {}
+    for threads in ("1", "5"):
+        monkeypatch.setenv("ONILDA_IO_THREADS", threads)
+        oni.save_gamma(tmp_path / f"g{threads}", g)
+        m.save(tmp_path / f"m{threads}")
+        out[threads] = ((tmp_path / f"g{threads}").read_bytes(), (tmp_path / f"m{threads}.beta").read_bytes())
+    assert out["1"] == out["5"]
+    first = out["1"][0].split(b"\n", 1)[0].decode()
+    assert first == " ".join("%5.10f" % v for v in g[0])
+    assert out["1"][1].split(b"\n", 1)[0].decode() == "".join(" %5.10f" % v for v in m.log_beta[0])
