@@ -89,6 +89,19 @@ int onilda_corpus_from_csr(const int64_t* offsets, const int32_t* words, const i
  * arrays may be pageable.  n < 2^31. */
 int onilda_corpus_from_triples(const int32_t* doc, const int32_t* word, const int32_t* count, int64_t n,
                                int64_t num_docs, int32_t num_terms, int device, onilda_corpus** out);
+/* Word counts: replaces `.map((ip, word) -> 1).reduceByKey(_ + _)` of FlowPreLDA.scala:131-137 and
+ * DNSPreLDA.scala:114-120 on dense integer ids (the string dictionaries stay with the caller,
+ * OniLDACWrapper.scala:40-60).  n (document id, word id) occurrences -> the distinct pairs with their
+ * number of occurrences, sorted by (document, word).  The *_out arrays need room for n entries;
+ * *n_out = number of distinct pairs.  num_docs / num_terms 0 = max id + 1.  n < 2^31 - 1.
+ * Flow calls it twice (source pairs, destination pairs: the reference reduces the two roles
+ * separately and unions them, which is where a document's repeated word ids come from) and hands
+ * the concatenation to onilda_corpus_from_triples. */
+int onilda_pairs_count(const int32_t* doc, const int32_t* word, int64_t n, int64_t num_docs, int32_t num_terms,
+                       int device, int32_t* doc_out, int32_t* word_out, int32_t* count_out, int64_t* n_out);
+/* Same with device pointers on `stream`, no synchronisation; ids must be in range; *n_out is device memory. */
+int onilda_pairs_count_device(const int32_t* doc, const int32_t* word, int64_t n, int64_t num_docs, int32_t num_terms,
+                              int32_t* doc_out, int32_t* word_out, int32_t* count_out, long long* n_out, void* stream);
 /* The same grouping with everything in device memory, ordered on `stream` (a cudaStream_t), no
  * synchronisation: offsets_out[num_docs + 1], words_out[n], counts_out[n]; totals_out[num_docs]
  * (int sum of counts per document, lda.h:27) and max_len_out[1] may be null.  Ids must already be in

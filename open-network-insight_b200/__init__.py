@@ -72,6 +72,8 @@ def lib():
     L.onilda_corpus_from_dat.argtypes = [C.c_char_p, C.POINTER(_vp)]
     L.onilda_corpus_from_csr.argtypes = [_i64p, _vp, _vp, C.c_int64, C.c_int32, C.POINTER(_vp)]
     L.onilda_corpus_from_triples.argtypes = [_vp, _vp, _vp, C.c_int64, C.c_int64, C.c_int32, C.c_int, C.POINTER(_vp)]
+    L.onilda_pairs_count.argtypes = [_vp, _vp, C.c_int64, C.c_int64, C.c_int32, C.c_int, _vp, _vp, _vp, C.POINTER(C.c_int64)]
+    L.onilda_pairs_count_device.argtypes = [_vp, _vp, C.c_int64, C.c_int64, C.c_int32, _vp, _vp, _vp, _vp, _vp]
     L.onilda_triples_group_device.argtypes = [_vp, _vp, _vp, C.c_int64, C.c_int64, _vp, _vp, _vp, _vp, _vp, _vp]
     L.onilda_corpus_dims.argtypes = [_vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int32),
                                      C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
@@ -274,6 +276,20 @@ class Model:
         if getattr(self, "_h", None) and _lib is not None:
             _lib.onilda_model_free(self._h)
             self._h = None
+
+
+def pairs_count(doc, word, num_docs=0, num_terms=0, device=-1):
+    """(document id, word id) occurrences -> (doc, word, count) of the distinct pairs, sorted by (doc, word):
+    the reduceByKey of FlowPreLDA.scala:131-137 / DNSPreLDA.scala:114-120, on the GPU."""
+    doc = np.ascontiguousarray(doc, np.int32)
+    word = np.ascontiguousarray(word, np.int32)
+    if len(doc) != len(word):
+        raise ValueError("doc and word must have the same length")
+    n = len(doc)
+    od, ow, oc = (np.empty(max(n, 1), np.int32) for _ in range(3))
+    m = C.c_int64()
+    _check(lib().onilda_pairs_count(_ptr(doc), _ptr(word), n, num_docs, num_terms, device, _ptr(od), _ptr(ow), _ptr(oc), C.byref(m)))
+    return od[:m.value].copy(), ow[:m.value].copy(), oc[:m.value].copy()
 
 
 def save_gamma(path, gamma):

@@ -161,6 +161,7 @@ __global__ void __launch_bounds__(kThreads) scan_final_kernel(const unsigned int
 // warp + in lower lanes of its round.  The tile is put in that order in shared memory, one array at a time, and
 // written out from there: a digit's items leave as one contiguous run (kTile / bins items on average) instead
 // of one 4-byte store per sector.
+template <bool TWO>   // TWO: carries (word, count); otherwise one payload (count_in / count_out unused)
 __global__ void __launch_bounds__(kThreads, 3) radix_scatter_kernel(const int32_t* __restrict__ key_in, const int32_t* __restrict__ word_in,
                                                                  const int32_t* __restrict__ count_in, int64_t n, int shift,
                                                                  unsigned int mask, int nblocks, const unsigned int* __restrict__ offs,
@@ -184,7 +185,7 @@ __global__ void __launch_bounds__(kThreads, 3) radix_scatter_kernel(const int32_
         const bool live = i < n;
         k[r] = live ? key_in[i] : 0;
         w[r] = live ? word_in[i] : 0;
-        c[r] = live ? count_in[i] : 0;
+        c[r] = (TWO && live) ? count_in[i] : 0;
     }
     __syncthreads();
     unsigned int lp[kItems];
@@ -255,6 +256,7 @@ __global__ void __launch_bounds__(kThreads, 3) radix_scatter_kernel(const int32_
         const int j = r * kThreads + threadIdx.x;
         if (j < live_count) word_out[dst[r]] = tile[j];
     }
+    if (!TWO) return;
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < kItems; r++)
@@ -265,6 +267,43 @@ __global__ void __launch_bounds__(kThreads, 3) radix_scatter_kernel(const int32_
         const int j = r * kThreads + threadIdx.x;
         if (j < live_count) count_out[dst[r]] = tile[j];
     }
+}
+
+// ---- (document, word) occurrences -> counts: run heads of the sorted pairs, their ranks, run lengths
+__global__ void __launch_bounds__(256) pair_heads_kernel(const int32_t* __restrict__ doc, const int32_t* __restrict__ word, int64_t n,
+                                                         unsigned int* __restrict__ head)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) head[i] = (i == 0 || doc[i] != doc[i - 1] || word[i] != word[i - 1]) ? 1u : 0u;
+}
+
+// rank[i] = heads before i.  A head writes its ids and where its run starts; the last element writes the number of runs.
+__global__ void __launch_bounds__(256) pair_emit_kernel(const int32_t* __restrict__ doc, const int32_t* __restrict__ word, int64_t n,
+                                                        const unsigned int* __restrict__ rank, int32_t* __restrict__ doc_out,
+                                                        int32_t* __restrict__ word_out, unsigned int* __restrict__ start,
+                                                        long long* __restrict__ n_out)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned int r = rank[i];
+    const bool is_head = i == 0 || doc[i] != doc[i - 1] || word[i] != word[i - 1];
+    if (is_head) {
+        doc_out[r] = doc[i];
+        word_out[r] = word[i];
+        start[r] = (unsigned int)i;
+    }
+    if (i == n - 1) {
+        const unsigned int m = r + (is_head ? 1u : 0u);
+        start[m] = (unsigned int)n;
+        *n_out = (long long)m;
+    }
+}
+
+__global__ void __launch_bounds__(256) pair_counts_kernel(const unsigned int* __restrict__ start, const long long* __restrict__ n_out,
+                                                          int32_t* __restrict__ count_out)
+{
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < *n_out) count_out[j] = (int32_t)(start[j + 1] - start[j]);
 }
 
 // Per-document int count sum (document.total, lda.h:27; wraps as lda-c's int does).  Equal documents are
@@ -404,7 +443,7 @@ extern "C" int onilda_triples_group_device(const int32_t* doc, const int32_t* wo
             int32_t* c_out = to_out ? counts_out : ctmp;
             radix_hist_kernel<<<nblocks, kThreads, 0, st>>>(key_in, n, shift, mask, nblocks, hist);
             exclusive_scan(hist, scan_len, sums, offs, st);
-            radix_scatter_kernel<<<nblocks, kThreads, 0, st>>>(key_in, word_in, count_in, n, shift, mask, nblocks, offs, key[pass & 1],
+            radix_scatter_kernel<true><<<nblocks, kThreads, 0, st>>>(key_in, word_in, count_in, n, shift, mask, nblocks, offs, key[pass & 1],
                                                                 w_out, c_out);
             key_in = key[pass & 1];
             word_in = w_out;
@@ -417,6 +456,126 @@ extern "C" int onilda_triples_group_device(const int32_t* doc, const int32_t* wo
     const cudaError_t err = cudaGetLastError();
     if (arena) cudaFreeAsync(arena, st);
     if (err != cudaSuccess) return onilda_fail(ONILDA_ECUDA, "triples_group_device: launch failed: %s", cudaGetErrorString(err));
+    return ONILDA_OK;
+}
+
+// reduceByKey(_ + _) over ((document, word), 1): FlowPreLDA.scala:131-137, DNSPreLDA.scala:114-120.
+// Sort by word, then (stably) by document, one payload; run heads -> ranks -> run lengths.  Output sorted by
+// (document, word).  doc_out / word_out / count_out have room for n entries; *n_out (device) = distinct pairs.
+extern "C" int onilda_pairs_count_device(const int32_t* doc, const int32_t* word, int64_t n, int64_t num_docs, int32_t num_terms,
+                                         int32_t* doc_out, int32_t* word_out, int32_t* count_out, long long* n_out, void* stream)
+{
+    if (n < 0 || num_docs < 0 || num_terms < 0 || !n_out || (n > 0 && (!doc || !word || !doc_out || !word_out || !count_out)))
+        return onilda_fail(ONILDA_EINVAL, "pairs_count_device: bad argument");
+    if (n >= ((int64_t)1 << 31) - 1) return onilda_fail(ONILDA_EINVAL, "pairs_count_device: at most 2^31 - 2 pairs per call");
+    if (n > 0 && (num_docs == 0 || num_terms == 0)) return onilda_fail(ONILDA_EINVAL, "pairs_count_device: pairs but no ids");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n == 0) {
+        cudaMemsetAsync(n_out, 0, sizeof(long long), st);
+        return ONILDA_OK;
+    }
+    const int nblocks = (int)((n + kTile - 1) / kTile);
+    const int64_t scan_len = (int64_t)kMaxBins * nblocks > n + 1 ? (int64_t)kMaxBins * nblocks : n + 1;
+    const size_t b_key = align256(sizeof(int32_t) * (size_t)(n + 1)), b_hist = align256(sizeof(unsigned int) * (size_t)kMaxBins * nblocks),
+                 b_sums = align256(sizeof(unsigned int) * (size_t)((scan_len + kScanTile - 1) / kScanTile + 1));
+    char* arena = nullptr;
+    const size_t total = 4 * b_key + 2 * b_hist + b_sums;
+    if (cudaMallocAsync((void**)&arena, total, st) != cudaSuccess) {
+        cudaGetLastError();
+        return onilda_fail(ONILDA_ENOMEM, "pairs_count_device: %zu bytes of device scratch not available", total);
+    }
+    char* p = arena;
+    int32_t* buf[2][2];      // [pair][0 = the array that was the key of the pass, 1 = its payload]
+    buf[0][0] = (int32_t*)p; p += b_key; buf[0][1] = (int32_t*)p; p += b_key;
+    buf[1][0] = (int32_t*)p; p += b_key; buf[1][1] = (int32_t*)p; p += b_key;
+    unsigned int* hist = (unsigned int*)p; p += b_hist;
+    unsigned int* offs = (unsigned int*)p; p += b_hist;
+    unsigned int* sums = (unsigned int*)p;
+    const int32_t *key_in = word, *pay_in = doc;
+    int flip = 0;
+    for (int phase = 0; phase < 2; phase++) {
+        const int64_t range = phase == 0 ? (int64_t)num_terms : num_docs;
+        int bits = 1;
+        while (((int64_t)1 << bits) < range) bits++;
+        const int passes = (bits + kMaxRadixBits - 1) / kMaxRadixBits;
+        const int digit = (bits + passes - 1) / passes;
+        const unsigned int mask = (1u << digit) - 1u;
+        for (int pass = 0; pass < passes; pass++, flip ^= 1) {
+            radix_hist_kernel<<<nblocks, kThreads, 0, st>>>(key_in, n, pass * digit, mask, nblocks, hist);
+            exclusive_scan(hist, ((int64_t)mask + 1) * nblocks, sums, offs, st);
+            radix_scatter_kernel<false><<<nblocks, kThreads, 0, st>>>(key_in, pay_in, nullptr, n, pass * digit, mask, nblocks, offs,
+                                                                       buf[flip][0], buf[flip][1], nullptr);
+            key_in = buf[flip][0];
+            pay_in = buf[flip][1];
+        }
+        if (phase == 0) {            // now by document, carrying the word
+            const int32_t* t = key_in; key_in = pay_in; pay_in = t;
+        }
+    }
+    // key_in = documents, pay_in = words, sorted by (document, word); the other pair of buffers is free
+    unsigned int* head = (unsigned int*)buf[flip][0];
+    unsigned int* rank = (unsigned int*)buf[flip][1];
+    const unsigned int grid = (unsigned int)((n + 255) / 256);
+    pair_heads_kernel<<<grid, 256, 0, st>>>(key_in, pay_in, n, head);
+    exclusive_scan(head, n, sums, rank, st);
+    pair_emit_kernel<<<grid, 256, 0, st>>>(key_in, pay_in, n, rank, doc_out, word_out, head /* reused: run starts */, n_out);
+    pair_counts_kernel<<<grid, 256, 0, st>>>(head, n_out, count_out);
+    const cudaError_t err = cudaGetLastError();
+    cudaFreeAsync(arena, st);
+    if (err != cudaSuccess) return onilda_fail(ONILDA_ECUDA, "pairs_count_device: launch failed: %s", cudaGetErrorString(err));
+    return ONILDA_OK;
+}
+
+// Host arrays in, host arrays out (room for n entries each); *n_out = distinct pairs.
+extern "C" int onilda_pairs_count(const int32_t* doc, const int32_t* word, int64_t n, int64_t num_docs, int32_t num_terms, int device,
+                                  int32_t* doc_out, int32_t* word_out, int32_t* count_out, int64_t* n_out)
+{
+    if (n < 0 || !n_out || (n > 0 && (!doc || !word || !doc_out || !word_out || !count_out)))
+        return onilda_fail(ONILDA_EINVAL, "pairs_count: bad argument");
+    if (onilda_device_count() == 0)
+        return onilda_fail(ONILDA_ECUDA, "pairs_count: no CUDA device is usable and this library has no CPU path");
+    *n_out = 0;
+    if (n == 0) return ONILDA_OK;
+    int prev = 0;
+    ONILDA_CUDA(cudaGetDevice(&prev));
+    if (device < 0) device = prev;
+    ONILDA_CUDA(cudaSetDevice(device));
+    struct Restore { int d; ~Restore() { cudaSetDevice(d); } } restore{prev};
+    cudaStream_t st = 0;
+    struct DevBuf { void* p = nullptr; ~DevBuf() { cudaFree(p); } } d;
+    const size_t b_n = align256(sizeof(int32_t) * (size_t)n);
+    if (cudaMalloc(&d.p, 5 * b_n + 256) != cudaSuccess) {
+        cudaGetLastError();
+        return onilda_fail(ONILDA_ENOMEM, "pairs_count: %zu bytes of device memory not available", 5 * b_n);
+    }
+    char* base = (char*)d.p;
+    int32_t* d_doc = (int32_t*)base; int32_t* d_word = (int32_t*)(base + b_n);
+    int32_t* o_doc = (int32_t*)(base + 2 * b_n); int32_t* o_word = (int32_t*)(base + 3 * b_n); int32_t* o_cnt = (int32_t*)(base + 4 * b_n);
+    long long* d_range = (long long*)(base + 5 * b_n);          // [0..3]: id range check, [4]: number of runs
+    long long range[5] = {-1, -1, 0, 0, 0};
+    ONILDA_CUDA(cudaMemcpyAsync(d_doc, doc, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, st));
+    ONILDA_CUDA(cudaMemcpyAsync(d_word, word, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, st));
+    ONILDA_CUDA(cudaMemcpyAsync(d_range, range, sizeof range, cudaMemcpyHostToDevice, st));
+    triple_range_kernel<<<148 * 8, 256, 0, st>>>(d_doc, d_word, d_word, n, d_range);
+    ONILDA_CUDA(cudaGetLastError());
+    ONILDA_CUDA(cudaMemcpyAsync(range, d_range, sizeof range, cudaMemcpyDeviceToHost, st));
+    ONILDA_CUDA(cudaStreamSynchronize(st));
+    if (range[2]) return onilda_fail(ONILDA_EINVAL, "pairs_count: negative document or word id");
+    if (num_docs == 0) num_docs = range[0] + 1;
+    if (num_terms == 0) num_terms = (int32_t)(range[1] + 1);
+    if (range[0] >= num_docs || range[1] >= num_terms)
+        return onilda_fail(ONILDA_EINVAL, "pairs_count: id out of range (document %lld of %lld, word %lld of %d)", range[0],
+                           (long long)num_docs, range[1], num_terms);
+    int rc = onilda_pairs_count_device(d_doc, d_word, n, num_docs, num_terms, o_doc, o_word, o_cnt, d_range + 4, st);
+    if (rc != ONILDA_OK) return rc;
+    long long m = 0;
+    ONILDA_CUDA(cudaMemcpyAsync(&m, d_range + 4, sizeof m, cudaMemcpyDeviceToHost, st));
+    ONILDA_CUDA(cudaStreamSynchronize(st));
+    ONILDA_CUDA(cudaMemcpyAsync(doc_out, o_doc, sizeof(int32_t) * (size_t)m, cudaMemcpyDeviceToHost, st));
+    ONILDA_CUDA(cudaMemcpyAsync(word_out, o_word, sizeof(int32_t) * (size_t)m, cudaMemcpyDeviceToHost, st));
+    ONILDA_CUDA(cudaMemcpyAsync(count_out, o_cnt, sizeof(int32_t) * (size_t)m, cudaMemcpyDeviceToHost, st));
+    ONILDA_CUDA(cudaStreamSynchronize(st));
+    *n_out = m;
     return ONILDA_OK;
 }
 

@@ -235,6 +235,18 @@ def topk(scores, threshold, k):
     return idx[:m].copy(), sc[:m].copy()
 
 
+def pairs_count(doc, word):
+    """`.map((ip, word) -> 1).reduceByKey(_ + _)` (FlowPreLDA.scala:131-137, DNSPreLDA.scala:114-120) on integer ids;
+    Spark's output order is unspecified, this one is sorted by (doc, word).  Returns (doc, word, count)."""
+    doc = np.asarray(doc, np.int64)
+    word = np.asarray(word, np.int64)
+    if len(doc) == 0:
+        return np.zeros(0, np.int32), np.zeros(0, np.int32), np.zeros(0, np.int32)
+    span = int(word.max()) + 1
+    key, cnt = np.unique(doc * span + word, return_counts=True)
+    return (key // span).astype(np.int32), (key % span).astype(np.int32), cnt.astype(np.int32)
+
+
 def triples_to_csr(doc, word, count, num_docs=0):
     """OniLDACWrapper.createModel (OniLDACWrapper.scala:146-168) followed by read_data
     (lda-data.c:22-59), without the text in between: documents in id order (the position in

@@ -548,3 +548,41 @@ def test_triples_then_em_equals_dat_route(oni, oracle, corpusgen, tmp_path):
     c2 = oni.Corpus.from_dat(tmp_path / "model.dat")
     for a, b in zip(csr_of(c1), csr_of(c2)):
         assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("n,D,V", [(1, 1, 1), (7, 3, 2), (5000, 40, 30), (300_000, 70_000, 3000), (4_000_000, 1_000_003, 131_073),
+                                   (1_000_000, 2, 3)])
+def test_pairs_count_matches_oracle(oni, oracle, n, D, V):
+    """reduceByKey over ((doc, word), 1): exact against numpy's unique-with-counts."""
+    rng = np.random.default_rng(n + D)
+    doc = (rng.zipf(1.4, n) % D).astype(np.int32)
+    word = (rng.zipf(1.2, n) % V).astype(np.int32)
+    d, w, c = oni.pairs_count(doc, word, num_docs=D, num_terms=V)
+    rd, rw, rc = oracle.pairs_count(doc, word)
+    assert np.array_equal(d, rd) and np.array_equal(w, rw) and np.array_equal(c, rc)
+    assert int(c.sum()) == n
+    d2, w2, c2 = oni.pairs_count(doc, word)                       # ranges derived from the data
+    assert np.array_equal(d2, rd) and np.array_equal(w2, rw) and np.array_equal(c2, rc)
+
+
+def test_flow_word_counts_to_corpus(oni, oracle):
+    """FlowPreLDA.scala:131-139 end to end on ids: source and destination roles are reduced separately and
+    unioned, so an address that meets a word in both roles carries that word twice (SURVEY H: duplicates)."""
+    rng = np.random.default_rng(9)
+    n, D, V = 200_000, 5000, 400
+    sip, dip = rng.integers(0, D, n).astype(np.int32), rng.integers(0, D, n).astype(np.int32)
+    sw, dw = rng.integers(0, V, n).astype(np.int32), rng.integers(0, V, n).astype(np.int32)
+    a = oni.pairs_count(sip, sw, D, V)
+    b = oni.pairs_count(dip, dw, D, V)
+    c = oni.Corpus.from_triples(*(np.concatenate([x, y]) for x, y in zip(a, b)), num_docs=D, num_terms=V)
+    ra, rb = oracle.pairs_count(sip, sw), oracle.pairs_count(dip, dw)
+    roff, rw, rc = oracle.triples_to_csr(*(np.concatenate([x, y]) for x, y in zip(ra, rb)), num_docs=D)
+    off, w, cnt, tot = c.csr()
+    assert np.array_equal(off, roff) and np.array_equal(w, rw) and np.array_equal(cnt, rc)
+    assert c.tokens == 2 * n and np.array_equal(tot, np.add.reduceat(np.append(rc, 0), roff[:-1]) * (np.diff(roff) > 0))
+    assert any(len(np.unique(w[off[d]:off[d + 1]])) < off[d + 1] - off[d] for d in range(50))      # repeated word ids exist
+    assert oni.pairs_count([], [])[0].size == 0
+    with pytest.raises(oni.OnildaError):
+        oni.pairs_count([0, 1], [0, -2])
+    with pytest.raises(oni.OnildaError):
+        oni.pairs_count([0, 9], [0, 1], num_docs=9)

@@ -193,3 +193,9 @@ def test_create_model_golden(oracle):
     off, w, c = oracle.triples_to_csr([3, 0, 3, 3], [5, 6, 1, 5], [1, 2, 3, 4], num_docs=5)
     assert list(off) == [0, 1, 1, 1, 4, 4]
     assert list(w) == [6, 5, 1, 5] and list(c) == [2, 1, 3, 4]
+
+
+def test_pairs_count_restatement(oracle):
+    """FlowPreLDA.scala:131-137 on a hand-checkable case: three distinct (ip, word) pairs."""
+    d, w, c = oracle.pairs_count([2, 0, 2, 2, 0], [5, 1, 5, 0, 1])
+    assert list(d) == [0, 2, 2] and list(w) == [1, 0, 5] and list(c) == [2, 1, 2]

@@ -56,3 +56,30 @@ for _ in range(2):
     t = time.time(); c = oni.Corpus.from_triples(hd, hw, hc, num_docs=D, num_terms=V); print("host entry: %.3f s" % (time.time() - t), flush=True)
 if n <= 200_000_000:
     t = time.time(); o = np.argsort(hd, kind="stable"); w = hw[o]; c = hc[o]; print("numpy stable argsort + gathers: %.3f s" % (time.time() - t))
+
+# ---- word counts (reduceByKey over (doc, word) occurrences)
+del c, o, w2, c2
+od, ow, oc = torch.empty_like(doc), torch.empty_like(doc), torch.empty_like(doc)
+m = torch.zeros(1, dtype=torch.int64, device=dev)
+
+
+def run_pairs():
+    oni._check(L.onilda_pairs_count_device(doc.data_ptr(), word.data_ptr(), n, D, V, od.data_ptr(), ow.data_ptr(), oc.data_ptr(),
+                                           m.data_ptr(), st))
+
+
+for _ in range(3):
+    run_pairs()
+torch.cuda.synchronize()
+e0.record()
+for _ in range(10):
+    run_pairs()
+e1.record()
+torch.cuda.synchronize()
+ms = e0.elapsed_time(e1) / 10
+print("pairs_count device: %.3f ms per %d pairs = %.2f G pairs/s, %d distinct" % (ms, n, n / ms / 1e6, int(m.item())))
+key = doc.to(torch.int64) * V + word
+e0.record(); u, cu = torch.unique(key, return_counts=True); e1.record(); torch.cuda.synchronize()
+print("torch.unique(return_counts) on the 64-bit composite key: %.3f ms" % e0.elapsed_time(e1))
+mm = int(m.item())
+assert mm == len(u) and torch.equal(od[:mm].to(torch.int64) * V + ow[:mm], u) and torch.equal(oc[:mm].to(torch.int64), cu)
