@@ -29,6 +29,7 @@
 #ifndef ONILDA_H
 #define ONILDA_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -89,6 +90,43 @@ int onilda_corpus_from_csr(const int64_t* offsets, const int32_t* words, const i
  * arrays may be pageable.  n < 2^31. */
 int onilda_corpus_from_triples(const int32_t* doc, const int32_t* word, const int32_t* count, int64_t n,
                                int64_t num_docs, int32_t num_terms, int device, onilda_corpus** out);
+/* ------------------------------------------------------- flow word creation
+ * SURVEY section 8(f) row N4 (netflow only; the DNS / proxy word builders work on strings and stay
+ * with the caller).
+ *
+ * onilda_quantiles_i64: Quantiles.computeQuantiles (Quantiles.scala:53-75) of an integer column:
+ * cuts_out[i] = the least x in the data with (count of values <= x) / n >= thresholds[i], compared
+ * in doubles as the reference does; +infinity for an empty column or a threshold above 1.  At
+ * most 16 thresholds.  Values are taken as the doubles the reference converts them to (exact
+ * below 2^53). */
+int onilda_quantiles_i64(const int64_t* values, int64_t n, const double* thresholds, int nq, int device,
+                         double* cuts_out);
+int onilda_quantiles_i64_device(const int64_t* values, int64_t n, const double* thresholds, int nq,
+                                double* cuts_out /* host */, void* stream);
+/* FlowWordCreation.flowWordCreation (FlowWordCreation.scala:14-84): deciles of the time of day
+ * hour + minute/60 + second/3600, deciles of ibyt, quintiles of ipkt (Quantiles.scala:86,94),
+ * Quantiles.bin (:97-99) of the three, and adjustPort (:92-146) per event.  The source and
+ * destination words come back as integer codes
+ *   code = (((port_index * 10 + timeBin) * 10 + ibytBin) * 5 + ipktBin) * 2 + marker
+ * port_index = the word port (0..65535), 65536 for 111111, 65537 for 333333; marker 1 = the
+ * word carries the "-1_" prefix.  onilda_flow_word_string prints a code as the reference's word
+ * string ("-1_23.0_7.0_7.0_4.0").  The ip pair string of adjustPort is not part of any word and
+ * is not produced.  hour 0..23, minute/second 0..59, ports 0..65535, else ONILDA_EINVAL. */
+typedef struct onilda_flow_cuts {
+    double time[10];
+    double ibyt[10];
+    double ipkt[5];
+} onilda_flow_cuts;
+int onilda_flow_words(const int32_t* hour, const int32_t* minute, const int32_t* second, const int64_t* ibyt,
+                      const int64_t* ipkt, const int32_t* sport, const int32_t* dport, int64_t n, int device,
+                      onilda_flow_cuts* cuts_out, int32_t* src_code, int32_t* dst_code);
+/* Columns and codes in device memory; cuts_out on the host (the call synchronises `stream`). */
+int onilda_flow_words_device(const int32_t* hour, const int32_t* minute, const int32_t* second, const int64_t* ibyt,
+                             const int64_t* ipkt, const int32_t* sport, const int32_t* dport, int64_t n,
+                             onilda_flow_cuts* cuts_out, int32_t* src_code, int32_t* dst_code, void* stream);
+/* Returns the string's length, or a negative error code. */
+int onilda_flow_word_string(int32_t code, char* buf, size_t cap);
+
 /* Word counts: replaces `.map((ip, word) -> 1).reduceByKey(_ + _)` of FlowPreLDA.scala:131-137 and
  * DNSPreLDA.scala:114-120 on dense integer ids (the string dictionaries stay with the caller,
  * OniLDACWrapper.scala:40-60).  n (document id, word id) occurrences -> the distinct pairs with their

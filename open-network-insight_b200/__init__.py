@@ -72,6 +72,11 @@ def lib():
     L.onilda_corpus_from_dat.argtypes = [C.c_char_p, C.POINTER(_vp)]
     L.onilda_corpus_from_csr.argtypes = [_i64p, _vp, _vp, C.c_int64, C.c_int32, C.POINTER(_vp)]
     L.onilda_corpus_from_triples.argtypes = [_vp, _vp, _vp, C.c_int64, C.c_int64, C.c_int32, C.c_int, C.POINTER(_vp)]
+    L.onilda_quantiles_i64.argtypes = [_vp, C.c_int64, _vp, C.c_int, C.c_int, _vp]
+    L.onilda_quantiles_i64_device.argtypes = [_vp, C.c_int64, _vp, C.c_int, _vp, _vp]
+    L.onilda_flow_words.argtypes = [_vp] * 7 + [C.c_int64, C.c_int, _vp, _vp, _vp]
+    L.onilda_flow_words_device.argtypes = [_vp] * 7 + [C.c_int64, _vp, _vp, _vp, _vp]
+    L.onilda_flow_word_string.argtypes = [C.c_int32, C.c_char_p, C.c_size_t]
     L.onilda_pairs_count.argtypes = [_vp, _vp, C.c_int64, C.c_int64, C.c_int32, C.c_int, _vp, _vp, _vp, C.POINTER(C.c_int64)]
     L.onilda_pairs_count_device.argtypes = [_vp, _vp, C.c_int64, C.c_int64, C.c_int32, _vp, _vp, _vp, _vp, _vp]
     L.onilda_triples_group_device.argtypes = [_vp, _vp, _vp, C.c_int64, C.c_int64, _vp, _vp, _vp, _vp, _vp, _vp]
@@ -276,6 +281,42 @@ class Model:
         if getattr(self, "_h", None) and _lib is not None:
             _lib.onilda_model_free(self._h)
             self._h = None
+
+
+class FlowCuts(C.Structure):
+    _fields_ = [("time", C.c_double * 10), ("ibyt", C.c_double * 10), ("ipkt", C.c_double * 5)]
+
+
+def quantiles(values, thresholds, device=-1):
+    """Quantiles.computeQuantiles (Quantiles.scala:53-75) of an integer column."""
+    values = np.ascontiguousarray(values, np.int64)
+    thresholds = np.ascontiguousarray(thresholds, np.float64)
+    out = np.empty(len(thresholds), np.float64)
+    _check(lib().onilda_quantiles_i64(_ptr(values), len(values), _ptr(thresholds), len(thresholds), device, _ptr(out)))
+    return out
+
+
+def flow_words(hour, minute, second, ibyt, ipkt, sport, dport, device=-1):
+    """FlowWordCreation.flowWordCreation (FlowWordCreation.scala:14-146) on integer columns.
+    Returns (cuts, src_code, dst_code); flow_word_string(code) gives the reference's word."""
+    cols32 = [np.ascontiguousarray(x, np.int32) for x in (hour, minute, second)]
+    cols64 = [np.ascontiguousarray(x, np.int64) for x in (ibyt, ipkt)]
+    ports = [np.ascontiguousarray(x, np.int32) for x in (sport, dport)]
+    n = len(cols32[0])
+    if any(len(x) != n for x in cols32 + cols64 + ports):
+        raise ValueError("columns must have the same length")
+    cuts = FlowCuts()
+    sc, dc = np.empty(max(n, 1), np.int32), np.empty(max(n, 1), np.int32)
+    _check(lib().onilda_flow_words(*[_ptr(x) for x in cols32 + cols64 + ports], n, device, C.byref(cuts), _ptr(sc), _ptr(dc)))
+    return ({"time": np.array(cuts.time), "ibyt": np.array(cuts.ibyt), "ipkt": np.array(cuts.ipkt)}, sc[:n], dc[:n])
+
+
+def flow_word_string(code):
+    buf = C.create_string_buffer(64)
+    n = lib().onilda_flow_word_string(int(code), buf, 64)
+    if n < 0:
+        _check(n)
+    return buf.value.decode()
 
 
 def pairs_count(doc, word, num_docs=0, num_terms=0, device=-1):

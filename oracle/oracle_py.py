@@ -235,6 +235,92 @@ def topk(scores, threshold, k):
     return idx[:m].copy(), sc[:m].copy()
 
 
+def compute_ecdf(data):
+    """Quantiles.computeEcdf (Quantiles.scala:21-41): (value, fraction of the data <= value) for each distinct value,
+    ascending; the running count is a double sum and the fraction a double division, as there."""
+    data = np.asarray(data, np.float64)
+    if len(data) == 0:
+        return np.zeros(0), np.zeros(0)
+    values, counts = np.unique(data, return_counts=True)
+    return values, np.cumsum(counts.astype(np.float64)) / float(len(data))
+
+
+def compute_quantiles(data, thresholds):
+    """Quantiles.computeQuantiles (Quantiles.scala:53-75): per threshold the least value whose ecdf is >= it,
+    +infinity when there is none."""
+    values, cdf = compute_ecdf(data)
+    out = []
+    for t in thresholds:
+        hit = np.nonzero(cdf >= t)[0]
+        out.append(float(values[hit[0]]) if len(hit) else float("inf"))
+    return np.array(out)
+
+
+DECILES = [0.1, 0.2, 0.3, 0.4, 0.5, 0.6, 0.7, 0.8, 0.9, 1.0]      # Quantiles.scala:86
+QUINTILES = [0.2, 0.4, 0.6, 0.8, 1.0]                              # Quantiles.scala:94
+
+
+def quantile_bin(value, cuts):
+    """Quantiles.bin (Quantiles.scala:97-99): index of the first cut with value <= cut, -1 if none."""
+    for i, c in enumerate(cuts):
+        if value <= c:
+            return i
+    return -1
+
+
+def scala_double(x):
+    """Scala's Double.toString for the values that occur in words: whole numbers print as '23.0'."""
+    return "%d.0" % int(x) if float(x) == int(x) else repr(float(x))
+
+
+def adjust_port(source_ip, destination_ip, destination_port, source_port, ipkt_bin, ibyt_bin, time_bin):
+    """FlowWordCreation.adjustPort (FlowWordCreation.scala:92-146), statement by statement.
+    Returns [wordPort, ipPair, sourceWord, destinationWord]."""
+    word_port = 111111.0
+    ip_pair = destination_ip + " " + source_ip
+    if source_ip < destination_ip and source_ip != 0:
+        ip_pair = source_ip + " " + destination_ip
+    dp, sp = destination_port, source_port
+    if (dp <= 1024 or sp <= 1024) and (dp > 1024 or sp > 1024) and min(dp, sp) != 0:
+        port_case, word_port = 2, float(min(dp, sp))
+    elif dp > 1024 and sp > 1024:
+        port_case, word_port = 3, 333333.0
+    elif dp == 0 and sp != 0:
+        port_case, word_port = 4, float(sp)
+    elif sp == 0 and dp != 0:
+        port_case, word_port = 4, float(dp)
+    else:
+        port_case = 1
+        word_port = float(max(dp, sp)) if min(dp, sp) == 0 else 111111.0
+    word = "_".join([scala_double(word_port), scala_double(time_bin), scala_double(ibyt_bin), scala_double(ipkt_bin)])
+    source_word = destination_word = word
+    if port_case == 2 and dp < sp:
+        destination_word = "-1_" + destination_word
+    elif port_case == 2 and sp < dp:
+        source_word = "-1_" + source_word
+    elif port_case == 4 and dp == 0:
+        source_word = "-1_" + source_word
+    elif port_case == 4 and sp == 0:
+        destination_word = "-1_" + destination_word
+    return [scala_double(word_port), ip_pair, source_word, destination_word]
+
+
+def flow_words(hour, minute, second, ibyt, ipkt, sport, dport):
+    """FlowWordCreation.flowWordCreation (FlowWordCreation.scala:14-84) on columns: the three cut arrays and the
+    (sourceWord, destinationWord) strings per event."""
+    num_time = [float(h) + float(m) / 60 + float(s) / 3600 for h, m, s in zip(hour, minute, second)]   # addTime, :88-90
+    time_cuts = compute_quantiles(num_time, DECILES)
+    ibyt_cuts = compute_quantiles(np.asarray(ibyt, np.float64), DECILES)
+    ipkt_cuts = compute_quantiles(np.asarray(ipkt, np.float64), QUINTILES)
+    src, dst = [], []
+    for i in range(len(num_time)):
+        r = adjust_port("a", "b", int(dport[i]), int(sport[i]), float(quantile_bin(float(ipkt[i]), ipkt_cuts)),
+                        float(quantile_bin(float(ibyt[i]), ibyt_cuts)), float(quantile_bin(num_time[i], time_cuts)))
+        src.append(r[2])
+        dst.append(r[3])
+    return {"time": time_cuts, "ibyt": ibyt_cuts, "ipkt": ipkt_cuts}, src, dst
+
+
 def pairs_count(doc, word):
     """`.map((ip, word) -> 1).reduceByKey(_ + _)` (FlowPreLDA.scala:131-137, DNSPreLDA.scala:114-120) on integer ids;
     Spark's output order is unspecified, this one is sorted by (doc, word).  Returns (doc, word, count)."""

@@ -586,3 +586,88 @@ def test_flow_word_counts_to_corpus(oni, oracle):
         oni.pairs_count([0, 1], [0, -2])
     with pytest.raises(oni.OnildaError):
         oni.pairs_count([0, 9], [0, 1], num_docs=9)
+
+
+# ---------------------------------------------------------------- N4: flow word creation
+def test_quantiles_reference_goldens(oni, oracle):
+    """QuantilesTest.scala through the GPU select."""
+    inf = float("inf")
+    to_ten = list(range(1, 11))
+    assert list(oni.quantiles([], [0.0, 0.5])) == [inf, inf]
+    assert list(oni.quantiles([1] * 5, [0.0, 0.5])) == [1.0, 1.0]
+    assert list(oni.quantiles([1, 2, 1, 2], [0.0, 0.5])) == [1.0, 1.0]
+    assert list(oni.quantiles([1, 2, 1, 2], [0.0, 0.6, 0.99])) == [1.0, 2.0, 2.0]
+    assert list(oni.quantiles(to_ten, [0.0, 0.5])) == [1.0, 5.0]
+    assert list(oni.quantiles(to_ten, oracle.DECILES)) == [float(x) for x in to_ten]
+    assert list(oni.quantiles(to_ten, oracle.QUINTILES)) == [2.0, 4.0, 6.0, 8.0, 10.0]
+    assert list(oni.quantiles(to_ten, [1.5])) == [inf]
+
+
+@pytest.mark.parametrize("n,kind", [(1, "small"), (97, "small"), (50_000, "bytes"), (3_000_000, "bytes"), (200_000, "wide"),
+                                    (100_000, "negative"), (100_000, "constant")])
+def test_quantiles_match_oracle(oni, oracle, n, kind):
+    rng = np.random.default_rng(n)
+    if kind == "small":
+        v = rng.integers(0, 5, n)
+    elif kind == "bytes":
+        v = np.floor(np.exp(rng.normal(7, 3, n))).astype(np.int64)           # heavy tail, many ties at the low end
+    elif kind == "wide":
+        v = rng.integers(0, 1 << 52, n)
+    elif kind == "negative":
+        v = rng.integers(-10**12, 10**12, n)
+    else:
+        v = np.full(n, 123456789012)
+    th = [0.0, 1e-9, 0.1, 0.2, 0.25, 0.3, 0.5, 0.6, 0.7, 0.9, 0.999999, 1.0]
+    assert np.array_equal(oni.quantiles(v, th), oracle.compute_quantiles(v.astype(np.float64), th))
+    assert np.array_equal(oni.quantiles(v, oracle.DECILES), oracle.compute_quantiles(v.astype(np.float64), oracle.DECILES))
+
+
+def test_flow_words_reference_goldens(oni, oracle):
+    """FlowWordCreationTest.scala: the fourteen adjustPort cases, with the bins 7 / 7 / 4 of the test rows produced
+    by the data itself (ten events whose eighth has time and ibyt decile 7 and ipkt quintile 4)."""
+    from test_oracle_golden import ADJUST_PORT_GOLDEN
+    hour = np.arange(10) + 3
+    minute, second = np.full(10, 59), np.full(10, 32)
+    ibyt = (np.arange(10) + 1) * 1000
+    ipkt = np.array([1, 2, 3, 4, 5, 6, 7, 9, 8, 10])
+    for sport, dport, port, sword, dword in ADJUST_PORT_GOLDEN:
+        sp, dp = np.full(10, 5000), np.full(10, 6000)
+        sp[7], dp[7] = sport, dport
+        cuts, sc, dc = oni.flow_words(hour, minute, second, ibyt, ipkt, sp, dp)
+        assert oni.flow_word_string(sc[7]) == sword and oni.flow_word_string(dc[7]) == dword
+        assert oni.flow_word_string(sc[0]) == "333333.0_0.0_0.0_0.0"
+    assert list(cuts["ipkt"]) == [2.0, 4.0, 6.0, 8.0, 10.0] and list(cuts["ibyt"]) == [1000.0 * i for i in range(1, 11)]
+    assert cuts["time"][7] == 10.0 + 59.0 / 60 + 32.0 / 3600
+
+
+@pytest.mark.parametrize("n", [1, 10, 1000, 30_000])
+def test_flow_words_match_oracle(oni, oracle, n):
+    rng = np.random.default_rng(n)
+    hour = rng.integers(0, 24, n)
+    minute = rng.integers(0, 60, n)
+    second = rng.integers(0, 60, n)
+    if n >= 1000:
+        hour[: n // 3] = 12                                               # many events in one minute: ties in the time cuts
+        minute[: n // 3] = 0
+    ibyt = np.floor(np.exp(rng.normal(6, 2.5, n))).astype(np.int64)
+    ipkt = np.maximum(1, ibyt // rng.integers(40, 1500, n))
+    choices = np.array([0, 22, 53, 80, 443, 1024, 1025, 8080, 50123, 65535])
+    sport, dport = rng.choice(choices, n), rng.choice(choices, n)
+    cuts, sc, dc = oni.flow_words(hour, minute, second, ibyt, ipkt, sport, dport)
+    rcuts, rs, rd = oracle.flow_words(hour, minute, second, ibyt, ipkt, sport, dport)
+    for k in ("time", "ibyt", "ipkt"):
+        assert np.array_equal(cuts[k], rcuts[k]), k
+    codes = np.unique(np.concatenate([sc, dc]))
+    text = {int(c): oni.flow_word_string(c) for c in codes}
+    assert [text[int(c)] for c in sc] == rs
+    assert [text[int(c)] for c in dc] == rd
+
+
+def test_flow_words_rejects_bad_columns(oni):
+    one = np.zeros(1, np.int64)
+    with pytest.raises(oni.OnildaError):
+        oni.flow_words([24], [0], [0], one, one, [1], [1])
+    with pytest.raises(oni.OnildaError):
+        oni.flow_words([1], [0], [0], one, one, [70000], [1])
+    cuts, sc, dc = oni.flow_words([], [], [], [], [], [], [])
+    assert len(sc) == 0 and np.all(np.isinf(cuts["time"]))

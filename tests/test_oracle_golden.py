@@ -199,3 +199,49 @@ def test_pairs_count_restatement(oracle):
     """FlowPreLDA.scala:131-137 on a hand-checkable case: three distinct (ip, word) pairs."""
     d, w, c = oracle.pairs_count([2, 0, 2, 2, 0], [5, 1, 5, 0, 1])
     assert list(d) == [0, 2, 2] and list(w) == [1, 0, 5] and list(c) == [2, 1, 2]
+
+
+# ---- QuantilesTest.scala: every case
+def test_quantiles_golden(oracle):
+    all_ones, ones_twos, to_ten = [1.0] * 5, [1.0, 2.0, 1.0, 2.0], [float(i) for i in range(1, 11)]
+    assert len(oracle.compute_ecdf([])[0]) == 0
+    assert [list(x) for x in oracle.compute_ecdf(all_ones)] == [[1.0], [1.0]]
+    assert [list(x) for x in oracle.compute_ecdf(ones_twos)] == [[1.0, 2.0], [0.5, 1.0]]
+    v, c = oracle.compute_ecdf(to_ten)
+    assert list(v) == to_ten and list(c) == [0.1, 0.2, 0.3, 0.4, 0.5, 0.6, 0.7, 0.8, 0.9, 1.0]
+    assert list(oracle.compute_quantiles([], [0.0, 0.5])) == [float("inf")] * 2
+    assert list(oracle.compute_quantiles(all_ones, [0.0, 0.5])) == [1.0, 1.0]
+    assert list(oracle.compute_quantiles(ones_twos, [0.0, 0.5])) == [1.0, 1.0]
+    assert list(oracle.compute_quantiles(ones_twos, [0.0, 0.6, 0.99])) == [1.0, 2.0, 2.0]
+    assert list(oracle.compute_quantiles(to_ten, [0.0, 0.5])) == [1.0, 5.0]
+    assert list(oracle.compute_quantiles(to_ten, oracle.DECILES)) == to_ten
+    assert list(oracle.compute_quantiles(to_ten, oracle.QUINTILES)) == [2.0, 4.0, 6.0, 8.0, 10.0]
+    assert oracle.quantile_bin(3.5, [1.0, 2.0, 3.0, 4.0, 5.0]) == 3
+    assert oracle.quantile_bin(0.0, [1.0, 2.0, 3.0, 4.0, 5.0]) == 0
+
+
+# FlowWordCreationTest.scala: (sport, dport) -> (wordPort, sourceWord, destinationWord) with ipkt/ibyt/time bins 4/7/7;
+# the first seven with sip < dip, the last seven with dip < sip (the ip pair is the same sorted string in all)
+ADJUST_PORT_GOLDEN = [
+    (2132, 23, "23.0", "23.0_7.0_7.0_4.0", "-1_23.0_7.0_7.0_4.0"),
+    (23, 2132, "23.0", "-1_23.0_7.0_7.0_4.0", "23.0_7.0_7.0_4.0"),
+    (8392, 9874, "333333.0", "333333.0_7.0_7.0_4.0", "333333.0_7.0_7.0_4.0"),
+    (80, 0, "80.0", "-1_80.0_7.0_7.0_4.0", "80.0_7.0_7.0_4.0"),
+    (0, 43, "43.0", "43.0_7.0_7.0_4.0", "-1_43.0_7.0_7.0_4.0"),
+    (1024, 80, "111111.0", "111111.0_7.0_7.0_4.0", "111111.0_7.0_7.0_4.0"),
+    (0, 0, "0.0", "0.0_7.0_7.0_4.0", "0.0_7.0_7.0_4.0"),
+    (3245, 43, "43.0", "43.0_7.0_7.0_4.0", "-1_43.0_7.0_7.0_4.0"),
+    (80, 2435, "80.0", "-1_80.0_7.0_7.0_4.0", "80.0_7.0_7.0_4.0"),
+    (2354, 2435, "333333.0", "333333.0_7.0_7.0_4.0", "333333.0_7.0_7.0_4.0"),
+    (80, 0, "80.0", "-1_80.0_7.0_7.0_4.0", "80.0_7.0_7.0_4.0"),
+    (0, 2435, "2435.0", "2435.0_7.0_7.0_4.0", "-1_2435.0_7.0_7.0_4.0"),
+    (80, 1024, "111111.0", "111111.0_7.0_7.0_4.0", "111111.0_7.0_7.0_4.0"),
+    (0, 0, "0.0", "0.0_7.0_7.0_4.0", "0.0_7.0_7.0_4.0"),
+]
+
+
+def test_adjust_port_golden(oracle):
+    for i, (sport, dport, port, sword, dword) in enumerate(ADJUST_PORT_GOLDEN):
+        sip, dip = ("10.0.2.115", "172.16.0.107") if i < 7 else ("172.16.0.107", "10.0.2.115")
+        r = oracle.adjust_port(sip, dip, dport, sport, 4.0, 7.0, 7.0)
+        assert r == [port, "10.0.2.115 172.16.0.107", sword, dword], (i, r)
