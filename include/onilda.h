@@ -295,6 +295,14 @@ int onilda_score_flow_min(onilda_scorer* s, const int32_t* sdoc, const int32_t* 
  * k == -1 keeps all.  idx_out/score_out need room for min(k, n) (n when k == -1). */
 int onilda_topk(onilda_scorer* s, const double* score, int64_t n, double threshold, int64_t k,
                 int64_t* idx_out, double* score_out, int64_t* n_out);
+/* SURVEY section 8(f) row N3.  FlowPostLDA.scala:75-80 in one call: SourceScore, DestinationScore,
+ * their minimum, filter(min <= threshold), orderBy(min), limit(k).  Per kept row, ascending by the
+ * minimum (ties by event index): the event's index (to join its own columns), its source score and
+ * its destination score - the two score columns of flow_results.csv (the minimum is dropped from
+ * the file, :80).  Outputs need room for min(k, n) rows (n when k == -1). */
+int onilda_flow_results(onilda_scorer* s, const int32_t* sdoc, const int32_t* sword, const int32_t* ddoc,
+                        const int32_t* dword, int64_t n, double threshold, int64_t k, int64_t* idx_out,
+                        double* src_score_out, double* dst_score_out, int64_t* n_out);
 /* Fused form for data already on the device (no host copies): scores the
  * events, keeps the running top-k, returns only the k rows.  Device pointers. */
 int onilda_score_flow_topk_device(onilda_scorer* s, const int32_t* sdoc_dev, const int32_t* sword_dev,

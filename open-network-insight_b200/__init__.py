@@ -72,6 +72,7 @@ def lib():
     L.onilda_corpus_from_dat.argtypes = [C.c_char_p, C.POINTER(_vp)]
     L.onilda_corpus_from_csr.argtypes = [_i64p, _vp, _vp, C.c_int64, C.c_int32, C.POINTER(_vp)]
     L.onilda_corpus_from_triples.argtypes = [_vp, _vp, _vp, C.c_int64, C.c_int64, C.c_int32, C.c_int, C.POINTER(_vp)]
+    L.onilda_flow_results.argtypes = [_vp, _vp, _vp, _vp, _vp, C.c_int64, C.c_double, C.c_int64, _vp, _vp, _vp, C.POINTER(C.c_int64)]
     L.onilda_quantiles_i64.argtypes = [_vp, C.c_int64, _vp, C.c_int, C.c_int, _vp]
     L.onilda_quantiles_i64_device.argtypes = [_vp, C.c_int64, _vp, C.c_int, _vp, _vp]
     L.onilda_flow_words.argtypes = [_vp] * 7 + [C.c_int64, C.c_int, _vp, _vp, _vp]
@@ -481,6 +482,17 @@ class Scorer:
         out = np.zeros(len(a[0])) if out is None else out
         _check(lib().onilda_score_flow_min(self._h, _ptr(a[0]), _ptr(a[1]), _ptr(a[2]), _ptr(a[3]), len(a[0]), _ptr(out)))
         return out
+
+    def flow_results(self, sdoc, sword, ddoc, dword, threshold, k):
+        """FlowPostLDA.scala:75-80: (event index, source score, destination score) of the kept rows, most suspicious first."""
+        a = [np.ascontiguousarray(x, np.int32) for x in (sdoc, sword, ddoc, dword)]
+        n = len(a[0])
+        cap = max(1, n if k == -1 else min(k, n))
+        idx, ss, ds = np.zeros(cap, np.int64), np.zeros(cap), np.zeros(cap)
+        m = C.c_int64()
+        _check(lib().onilda_flow_results(self._h, _ptr(a[0]), _ptr(a[1]), _ptr(a[2]), _ptr(a[3]), n, threshold, k,
+                                         _ptr(idx), _ptr(ss), _ptr(ds), C.byref(m)))
+        return idx[:m.value].copy(), ss[:m.value].copy(), ds[:m.value].copy()
 
     def score_raw(self, sdoc_ptr, sword_ptr, ddoc_ptr, dword_ptr, n, out_ptr):
         """Host pointers given as integers (e.g. pinned torch tensors' data_ptr())."""

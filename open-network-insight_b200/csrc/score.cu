@@ -767,6 +767,50 @@ extern "C" int onilda_score_flow_topk_device(onilda_scorer* s, const int32_t* sd
     return rc;
 }
 
+// FlowPostLDA.scala:75-80 in one call: both role scores, their minimum, filter(min <= threshold), orderBy(min),
+// limit(k); what comes back is what the results file needs per kept row (the row index to join the event's own
+// columns, SourceScore and DestinationScore - the minimum itself is dropped from the file, :80).
+extern "C" int onilda_flow_results(onilda_scorer* s, const int32_t* sdoc, const int32_t* sword, const int32_t* ddoc,
+                                   const int32_t* dword, int64_t n, double threshold, int64_t k, int64_t* idx_out,
+                                   double* src_score_out, double* dst_score_out, int64_t* n_out)
+{
+    if (!s || n < 0 || !n_out || k < -1 || (n > 0 && (!sdoc || !sword || !ddoc || !dword)))
+        return onilda_fail(ONILDA_EINVAL, "flow_results: bad argument");
+    *n_out = 0;
+    if (n == 0 || k == 0) return ONILDA_OK;
+    if (!idx_out || !src_score_out || !dst_score_out) return onilda_fail(ONILDA_EINVAL, "flow_results: null output");
+    DeviceGuard g(s->device);
+    int32_t* d_ids = nullptr;
+    double* d_score = nullptr;
+    const size_t b = (sizeof(int32_t) * (size_t)n + 255) & ~(size_t)255;
+    if (cudaMalloc((void**)&d_ids, 4 * b) != cudaSuccess || cudaMalloc((void**)&d_score, sizeof(double) * (size_t)n) != cudaSuccess) {
+        cudaGetLastError();
+        cudaFree(d_ids);
+        return onilda_fail(ONILDA_ENOMEM, "flow_results: device memory for %lld events not available", (long long)n);
+    }
+    struct Free { void *a, *b; ~Free() { cudaFree(a); cudaFree(b); } } fr{d_ids, d_score};
+    const int32_t* host[4] = {sdoc, sword, ddoc, dword};
+    int32_t* dev[4];
+    for (int c = 0; c < 4; c++) {
+        dev[c] = (int32_t*)((char*)d_ids + (size_t)c * b);
+        ONILDA_CUDA(cudaMemcpyAsync(dev[c], host[c], sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, s->stream[0]));
+    }
+    const int64_t cap = k == -1 ? n : (k < n ? k : n);
+    std::vector<double> min_score((size_t)cap);
+    int rc = onilda_score_flow_topk_device(s, dev[0], dev[1], dev[2], dev[3], n, threshold, k, idx_out, min_score.data(), n_out, d_score);
+    if (rc != ONILDA_OK) return rc;
+    // the two role scores of the kept rows (at most k of them): the same kernel on the gathered ids
+    const int64_t m = *n_out;
+    std::vector<int32_t> ids((size_t)(4 * m > 0 ? 4 * m : 1));
+    for (int64_t r = 0; r < m; r++)
+        for (int c = 0; c < 4; c++) ids[(size_t)(c * m + r)] = host[c][idx_out[r]];
+    if (m > 0) {
+        rc = onilda_score(s, ids.data(), ids.data() + m, m, src_score_out);
+        if (rc == ONILDA_OK) rc = onilda_score(s, ids.data() + 2 * m, ids.data() + 3 * m, m, dst_score_out);
+    }
+    return rc;
+}
+
 extern "C" int onilda_scorer_stats(onilda_scorer* s, double* kernel_ms, int64_t* launches)
 {
     if (!s) return onilda_fail(ONILDA_EINVAL, "scorer_stats: null handle");

@@ -671,3 +671,28 @@ def test_flow_words_rejects_bad_columns(oni):
         oni.flow_words([1], [0], [0], one, one, [70000], [1])
     cuts, sc, dc = oni.flow_words([], [], [], [], [], [], [])
     assert len(sc) == 0 and np.all(np.isinf(cuts["time"]))
+
+
+def test_flow_results_rows(oni, oracle):
+    """N3: the rows of flow_results.csv (FlowPostLDA.scala:75-80): filter on the minimum, ascending order, limit,
+    and the two role scores of each kept row, bit for bit against the oracle."""
+    rng = np.random.default_rng(77)
+    D, V, K, n = 3000, 800, 20, 400_000
+    theta = rng.dirichlet(np.full(K, 0.1), D)
+    phi = rng.dirichlet(np.full(V, 0.05), K).T.copy()
+    ids = [rng.integers(-1, m, n).astype(np.int32) for m in (D, V, D, V)]
+    ids[0][:5000] = ids[0][5000:10000]                 # tied scores across events
+    ids[1][:5000] = ids[1][5000:10000]
+    ids[2][:5000] = ids[2][5000:10000]
+    ids[3][:5000] = ids[3][5000:10000]
+    sc = oni.Scorer(theta, phi)
+    rs, rd = oracle.score(ids[0], ids[1], theta, phi), oracle.score(ids[2], ids[3], theta, phi)
+    rmin = np.minimum(rs, rd)
+    for threshold, k in [(1.0, 1000), (float(np.quantile(rmin, 0.001)), 3000), (0.0, 10), (1.0, -1 if n <= 1000 else 17)]:
+        idx, ss, ds = sc.flow_results(*ids, threshold, k)
+        ridx, _ = oracle.topk(rmin, threshold, k)
+        assert np.array_equal(idx, ridx)
+        assert np.array_equal(ss, rs[ridx]) and np.array_equal(ds, rd[ridx])
+    idx, ss, ds = sc.flow_results([], [], [], [], 1.0, 10)
+    assert len(idx) == 0
+    sc.close()
