@@ -696,3 +696,63 @@ def test_flow_results_rows(oni, oracle):
     idx, ss, ds = sc.flow_results([], [], [], [], 1.0, 10)
     assert len(idx) == 0
     sc.close()
+
+
+def test_flow_pipeline_end_to_end(oni, oracle):
+    """The whole flow path on ids, GPU chain against oracle chain: word creation (FlowWordCreation) -> word counts per
+    role (FlowPreLDA) -> corpus (createModel + read_data) -> EM (lda est) -> theta/phi (OniLDACWrapper) -> scores, filter,
+    order, limit (FlowPostLDA)."""
+    rng = np.random.default_rng(2016)
+    n, D = 30_000, 400
+    sip = (rng.zipf(1.5, n) % D).astype(np.int32)
+    dip = (rng.zipf(1.5, n) % D).astype(np.int32)
+    hour, minute, second = rng.integers(0, 24, n), rng.integers(0, 60, n), rng.integers(0, 60, n)
+    ibyt = np.floor(np.exp(rng.normal(6, 2, n))).astype(np.int64)
+    ipkt = np.maximum(1, ibyt // 700)
+    ports = np.array([0, 22, 53, 80, 443, 1025, 8080, 50123])
+    sport, dport = rng.choice(ports, n), rng.choice(ports, n)
+
+    # --- GPU chain
+    cuts, sc_code, dc_code = oni.flow_words(hour, minute, second, ibyt, ipkt, sport, dport)
+    vocab = np.unique(np.concatenate([sc_code, dc_code]))                   # word dictionary (OniLDACWrapper.scala:40-60)
+    sw, dw = np.searchsorted(vocab, sc_code).astype(np.int32), np.searchsorted(vocab, dc_code).astype(np.int32)
+    V = len(vocab)
+    a, b = oni.pairs_count(sip, sw, D, V), oni.pairs_count(dip, dw, D, V)
+    corpus = oni.Corpus.from_triples(*(np.concatenate([x, y]) for x, y in zip(a, b)), num_docs=D, num_terms=V)
+
+    # --- oracle chain, on strings as the reference does
+    rcuts, rs_words, rd_words = oracle.flow_words(hour, minute, second, ibyt, ipkt, sport, dport)
+    text = [oni.flow_word_string(c) for c in vocab]
+    index = {t: i for i, t in enumerate(text)}
+    assert sorted(index) == sorted(set(rs_words) | set(rd_words))            # same vocabulary
+    rsw = np.array([index[t] for t in rs_words], np.int32)
+    rdw = np.array([index[t] for t in rd_words], np.int32)
+    assert np.array_equal(rsw, sw) and np.array_equal(rdw, dw)
+    ra, rb = oracle.pairs_count(sip, rsw), oracle.pairs_count(dip, rdw)
+    roff, rw, rc = oracle.triples_to_csr(*(np.concatenate([x, y]) for x, y in zip(ra, rb)), num_docs=D)
+    off, w, cnt, _ = corpus.csr()
+    assert np.array_equal(off, roff) and np.array_equal(w, rw) and np.array_equal(cnt, rc)
+
+    # --- EM: three iterations from the same random start, then scoring
+    m = oni.Model.new(20, V)
+    m.init_random(77)
+    m.alpha = 2.5
+    st = oni.Settings(20, 1e-6, 2, 1e-6, 1)                                  # em max iter 2 -> three iterations
+    ref = oracle.run_em(roff, rw, rc, V, 2.5, m.log_beta.copy(), oracle.settings(em_max_iter=2))
+    em = oni.EM(corpus, m, st)
+    liks, keep = [], True
+    while keep:
+        lik, _, keep = em.iterate()
+        liks.append(lik)
+    assert len(liks) == len(ref["lik"])
+    assert np.max(np.abs(np.array(liks) - ref["lik"]) / np.abs(ref["lik"])) < LIK_RTOL
+    scorer = oni.Scorer.from_em(em)
+    idx, ss, ds = scorer.flow_results(sip, sw, dip, dw, 1.0, 200)
+    rtheta, rphi = oracle.theta_from_gamma(ref["gamma"]), oracle.phi_from_logbeta(ref["log_beta"])
+    rss, rds = oracle.score(sip, rsw, rtheta, rphi), oracle.score(dip, rdw, rtheta, rphi)
+    rmin = np.minimum(rss, rds)
+    ridx, rtop = oracle.topk(rmin, 1.0, 200)
+    assert np.max(np.abs(ss - rss[idx]) / rss[idx]) < MODEL_RTOL and np.max(np.abs(ds - rds[idx]) / rds[idx]) < MODEL_RTOL
+    assert tie_aware_overlap(idx, rmin, rtop, rtol=MODEL_RTOL) >= 0.99
+    scorer.close()
+    em.close()
