@@ -91,8 +91,7 @@ int onilda_corpus_from_csr(const int64_t* offsets, const int32_t* words, const i
 int onilda_corpus_from_triples(const int32_t* doc, const int32_t* word, const int32_t* count, int64_t n,
                                int64_t num_docs, int32_t num_terms, int device, onilda_corpus** out);
 /* ------------------------------------------------------- flow word creation
- * SURVEY section 8(f) row N4 (netflow only; the DNS / proxy word builders work on strings and stay
- * with the caller).
+ * netflow here, DNS below.
  *
  * onilda_quantiles_i64: Quantiles.computeQuantiles (Quantiles.scala:53-75) of an integer column:
  * cuts_out[i] = the least x in the data with (count of values <= x) / n >= thresholds[i], compared
@@ -126,6 +125,48 @@ int onilda_flow_words_device(const int32_t* hour, const int32_t* minute, const i
                              onilda_flow_cuts* cuts_out, int32_t* src_code, int32_t* dst_code, void* stream);
 /* Returns the string's length, or a negative error code. */
 int onilda_flow_word_string(int32_t code, char* buf, size_t cap);
+
+/* DNSWordCreation.dnsWordCreation (dns/DNSWordCreation.scala:32-145) on a byte buffer of query names
+ * (names[name_offsets[i] .. name_offsets[i+1]), at most 255 bytes each, compared as bytes):
+ * extractSubdomain (:155-196, String.split's dropping of trailing empty parts and the literal "None" of a
+ * missing domain / subdomain included), Entropy.stringEntropy of the subdomain column
+ * (utilities/Entropy.scala:16-23; "None" has entropy 2.0 and takes part in the cuts, as there),
+ * getTopDomain (:147-153) against the caller's list of top-domain labels (the driver already reduces
+ * top-1m.csv to them, :42-45), time and frame-length deciles, quintiles of subdomain length, entropy and
+ * number of parts over their entries > 0 (:82-121), Quantiles.bin of all five and dnsWord (:226-235).
+ * One 64-bit code per event:
+ *   ((((((top*10 + frameBin)*10 + timeBin)*5 + subdomainLengthBin)*5 + entropyBin)*5 + periodsBin) << 32)
+ *     | queryType << 16 | responseCode        (query type and response code 0..65535)
+ * onilda_dns_word_string prints it as the reference's word ("1_4_7_0_2_3_1_0").  Entropy terms are added
+ * largest count first (the reference adds in the unspecified iteration order of a Scala Map: the last bit
+ * of an entropy may differ from a JVM run, the value as a function of the character counts does not). */
+typedef struct onilda_dns_cuts {
+    double time[10];
+    double frame_length[10];
+    double subdomain_length[5];
+    double entropy[5];
+    double num_periods[5];
+} onilda_dns_cuts;
+int onilda_dns_words(const char* names, const int64_t* name_offsets, const int32_t* frame_len,
+                     const int64_t* unix_tstamp, const int32_t* qry_type, const int32_t* qry_rcode, int64_t n,
+                     const char* top_domains, const int64_t* top_offsets, int64_t n_top, int device,
+                     onilda_dns_cuts* cuts_out, int64_t* word_code);
+/* The same, also returning the per-event columns DNSPostLDA keeps beside the word (any of them may be null):
+ * subdomain length, number of parts, subdomain entropy (doubles, as the reference's columns), the top-domain
+ * flag 0/1/2, and spans_out[n][3] = domain begin, domain end, subdomain end as byte positions inside the
+ * name (the subdomain starts at 0; -1 where the reference has "None"). */
+int onilda_dns_words_features(const char* names, const int64_t* name_offsets, const int32_t* frame_len,
+                              const int64_t* unix_tstamp, const int32_t* qry_type, const int32_t* qry_rcode, int64_t n,
+                              const char* top_domains, const int64_t* top_offsets, int64_t n_top, int device,
+                              onilda_dns_cuts* cuts_out, int64_t* word_code, double* subdomain_length_out,
+                              double* num_parts_out, double* entropy_out, int32_t* top_out, int32_t* spans_out);
+/* Everything in device memory except cuts_out; top_slots: open-addressing table over FNV-1a 64 of the
+ * labels (entry = label index or -1, top_capacity a power of two, 0 = no list), as onilda_dns_words builds. */
+int onilda_dns_words_device(const char* names, const int64_t* name_offsets, const int32_t* frame_len,
+                            const int64_t* unix_tstamp, const int32_t* qry_type, const int32_t* qry_rcode, int64_t n,
+                            const char* top_bytes, const int64_t* top_offsets, const int32_t* top_slots,
+                            int64_t top_capacity, onilda_dns_cuts* cuts_out, int64_t* word_code, void* stream);
+int onilda_dns_word_string(int64_t code, char* buf, size_t cap);
 
 /* Word counts: replaces `.map((ip, word) -> 1).reduceByKey(_ + _)` of FlowPreLDA.scala:131-137 and
  * DNSPreLDA.scala:114-120 on dense integer ids (the string dictionaries stay with the caller,

@@ -72,6 +72,9 @@ def lib():
     L.onilda_corpus_from_dat.argtypes = [C.c_char_p, C.POINTER(_vp)]
     L.onilda_corpus_from_csr.argtypes = [_i64p, _vp, _vp, C.c_int64, C.c_int32, C.POINTER(_vp)]
     L.onilda_corpus_from_triples.argtypes = [_vp, _vp, _vp, C.c_int64, C.c_int64, C.c_int32, C.c_int, C.POINTER(_vp)]
+    L.onilda_dns_words.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp, C.c_int64, _vp, _vp, C.c_int64, C.c_int, _vp, _vp]
+    L.onilda_dns_words_features.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp, C.c_int64, _vp, _vp, C.c_int64, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
+    L.onilda_dns_word_string.argtypes = [C.c_int64, C.c_char_p, C.c_size_t]
     L.onilda_flow_results.argtypes = [_vp, _vp, _vp, _vp, _vp, C.c_int64, C.c_double, C.c_int64, _vp, _vp, _vp, C.POINTER(C.c_int64)]
     L.onilda_quantiles_i64.argtypes = [_vp, C.c_int64, _vp, C.c_int, C.c_int, _vp]
     L.onilda_quantiles_i64_device.argtypes = [_vp, C.c_int64, _vp, C.c_int, _vp, _vp]
@@ -315,6 +318,49 @@ def flow_words(hour, minute, second, ibyt, ipkt, sport, dport, device=-1):
 def flow_word_string(code):
     buf = C.create_string_buffer(64)
     n = lib().onilda_flow_word_string(int(code), buf, 64)
+    if n < 0:
+        _check(n)
+    return buf.value.decode()
+
+
+class DnsCuts(C.Structure):
+    _fields_ = [("time", C.c_double * 10), ("frame_length", C.c_double * 10), ("subdomain_length", C.c_double * 5),
+                ("entropy", C.c_double * 5), ("num_periods", C.c_double * 5)]
+
+
+def _pack_strings(strings):
+    raw = [x if isinstance(x, bytes) else str(x).encode() for x in strings]
+    off = np.zeros(len(raw) + 1, np.int64)
+    np.cumsum([len(x) for x in raw], out=off[1:])
+    return np.frombuffer(b"".join(raw) or b"\0", np.uint8).copy(), off
+
+
+def dns_words(names, frame_len, unix_tstamp, qry_type, qry_rcode, top_domains=(), device=-1, features=False):
+    """DNSWordCreation.dnsWordCreation (dns/DNSWordCreation.scala:32-236) on columns.
+    Returns (cuts, word_code int64[, features]); dns_word_string(code) gives the reference's word."""
+    nb, noff = _pack_strings(names)
+    tb, toff = _pack_strings(top_domains)
+    n = len(noff) - 1
+    fl, qt, rc = (np.ascontiguousarray(x, np.int32) for x in (frame_len, qry_type, qry_rcode))
+    ts = np.ascontiguousarray(unix_tstamp, np.int64)
+    if not (len(fl) == len(qt) == len(rc) == len(ts) == n):
+        raise ValueError("columns must have the same length")
+    cuts = DnsCuts()
+    code = np.empty(max(n, 1), np.int64)
+    m = max(n, 1)
+    f = {"subdomain_length": np.zeros(m), "num_parts": np.zeros(m), "entropy": np.zeros(m), "top": np.zeros(m, np.int32),
+         "spans": np.zeros((m, 3), np.int32)} if features else None
+    _check(lib().onilda_dns_words_features(_ptr(nb), _ptr(noff), _ptr(fl), _ptr(ts), _ptr(qt), _ptr(rc), n, _ptr(tb), _ptr(toff),
+                                           len(toff) - 1, device, C.byref(cuts), _ptr(code),
+                                           *([_ptr(f[k]) for k in ("subdomain_length", "num_parts", "entropy", "top", "spans")]
+                                             if features else [None] * 5)))
+    out = ({k: np.array(getattr(cuts, k)) for k, _ in DnsCuts._fields_}, code[:n])
+    return out + ({k: v[:n] for k, v in f.items()},) if features else out
+
+
+def dns_word_string(code):
+    buf = C.create_string_buffer(64)
+    n = lib().onilda_dns_word_string(int(code), buf, 64)
     if n < 0:
         _check(n)
     return buf.value.decode()

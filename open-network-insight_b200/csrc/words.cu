@@ -429,3 +429,441 @@ extern "C" int onilda_flow_word_string(int32_t code, char* buf, size_t cap)
     if (len < 0 || (size_t)len >= cap) return onilda_fail(ONILDA_EINVAL, "flow_word_string: buffer of %zu bytes is too small", cap);
     return len;
 }
+
+// =============================================================================== DNS word creation
+// dns/DNSWordCreation.scala:32-236 and utilities/Entropy.scala:16-23 on a byte buffer of query names.
+namespace {
+
+// ISO country-code suffixes the reference tests the last label against (DNSWordCreation.scala:17-30; the set
+// also holds "krd" and the empty string, which a last label can never equal after String.split drops trailing
+// empty parts).  Sorted, two letters each; "krd" is tested apart.
+__constant__ char kCountry2[] =
+    "acadaeafagaialamanaoaqarasatauawaxazbabbbdbebfbgbhbibjbmbnbobqbrbsbtbvbwbybzcacccdcfcgchcickclcmcncocrcucvcwcxcycz"
+    "dedjdkdmdodzeceeegeheresetfifjfkfmfofrgagbgdgegfggghgiglgmgngpgqgrgsgtgugwgyhkhmhnhrhthuidieiliminioiqirisit"
+    "jejmjojpkekgkhkikmknkpkrkwkykzlalblclilklrlsltlulvlymamcmdmemgmhmkmlmmmnmompmqmrmsmtmumvmwmxmymznancnenfngninlnonpnrnunz"
+    "ompapepfpgphpkplpmpnprpsptpwpyqarerorsrurwsasbscsdsesgshsisjskslsmsnsosrssstsusvsxsysztctdtftgthtjtktltmtntotptrtttvtwtz"
+    "uaugukusuyuzvavcvevgvivnvuwfwsyeytzazmzweu";
+constexpr int kCountry2Count = (int)(sizeof(kCountry2) - 1) / 2;
+
+__device__ __forceinline__ bool is_country(const unsigned char* p, int len)
+{
+    if (len == 3) return p[0] == 'k' && p[1] == 'r' && p[2] == 'd';
+    if (len != 2) return false;
+    for (int i = 0; i < kCountry2Count; i++)
+        if (kCountry2[2 * i] == (char)p[0] && kCountry2[2 * i + 1] == (char)p[1]) return true;
+    return false;
+}
+
+__device__ __forceinline__ bool bytes_equal(const unsigned char* p, int len, const char* lit, int lit_len)
+{
+    if (len != lit_len) return false;
+    for (int i = 0; i < len; i++)
+        if (p[i] != (unsigned char)lit[i]) return false;
+    return true;
+}
+
+__host__ __device__ __forceinline__ unsigned long long fnv1a(const unsigned char* p, int len)
+{
+    unsigned long long h = 1469598103934665603ull;
+    for (int i = 0; i < len; i++) {
+        h ^= p[i];
+        h *= 1099511628211ull;
+    }
+    return h;
+}
+
+struct TopTable {
+    const int32_t* slot;        // index into the top-domain list or -1; capacity a power of two
+    unsigned long long mask;
+    const unsigned char* bytes;
+    const int64_t* offsets;
+};
+
+// Entropy.stringEntropy: sum over the distinct characters of -p log10(p) / log10(2), p = occurrences / length.
+// The terms come from a host-made table term[len][count] (the host's log10, so the device agrees bit for bit with a
+// host evaluation) and are added largest count first, which makes the value a function of the multiset of counts
+// (the reference adds in the iteration order of a Scala Map, which is not specified).
+__device__ double string_entropy(const unsigned char* p, int len, const double* __restrict__ term /* [256][256] */)
+{
+    if (len <= 0) return 0.0;
+    unsigned char counts[256];            // counts of the distinct characters, in order of first occurrence
+    int nd = 0;
+    for (int i = 0; i < len; i++) {
+        const unsigned char c = p[i];
+        bool seen = false;
+        for (int j = 0; j < i; j++)
+            if (p[j] == c) { seen = true; break; }
+        if (seen) continue;
+        int k = 1;
+        for (int j = i + 1; j < len; j++) k += (p[j] == c);
+        counts[nd++] = (unsigned char)(k > 255 ? 255 : k);
+    }
+    double e = 0.0;
+    for (int want = len > 255 ? 255 : len; want >= 1; want--)        // largest count first
+        for (int d = 0; d < nd; d++)
+            if (counts[d] == want) e += len <= 255 ? term[len * 256 + want] : -((double)want / len) * log10((double)want / len) / log10(2.0);
+    return e;
+}
+
+// DNSWordCreation.extractSubdomain (:155-196) + stringEntropy of the subdomain column + getTopDomain (:147-153)
+__global__ void __launch_bounds__(128) dns_features_kernel(const unsigned char* __restrict__ names, const int64_t* __restrict__ off,
+                                                           int64_t n, TopTable top, const double* __restrict__ term,
+                                                           int64_t* __restrict__ sub_len, int64_t* __restrict__ num_parts,
+                                                           int64_t* __restrict__ entropy_bits, int32_t* __restrict__ top_out,
+                                                           int* __restrict__ bad, int32_t* __restrict__ spans /* [n][3] or null */)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned char* s = names + off[i];
+    const int64_t len64 = off[i + 1] - off[i];
+    if (len64 < 0 || len64 > 255) {          // a DNS name has at most 253 characters
+        *bad = 1;
+        return;
+    }
+    const int len = (int)len64;
+    // String.split("[.]"): trailing empty parts are dropped; a string without a dot is one part
+    int e = len, dots = 0;
+    for (int k = 0; k < len; k++) dots += (s[k] == '.');
+    if (dots > 0)
+        while (e > 0 && s[e - 1] == '.') e--;
+    int parts = 0, d1 = -1, d2 = -1, d3 = -1;        // the last three dots of s[0, e)
+    if (dots == 0) parts = 1;
+    else if (e > 0) {
+        parts = 1;
+        for (int k = 0; k < e; k++)
+            if (s[k] == '.') { parts++; d3 = d2; d2 = d1; d1 = k; }
+    }
+    int dom_b = -1, dom_e = -1, sub_e = -1;          // domain = s[dom_b, dom_e), subdomain = s[0, sub_e); -1 = "None"
+    if (parts > 2) {
+        const unsigned char* last = s + d1 + 1;
+        const int last_len = e - d1 - 1;
+        const bool ip = bytes_equal(last, last_len, "arpa", 4) && bytes_equal(s + d2 + 1, d1 - d2 - 1, "in-addr", 7);
+        if (!ip) {
+            if (is_country(last, last_len)) {
+                dom_b = d3 + 1; dom_e = d2;
+                if (parts - 3 >= 1) sub_e = d3;
+            } else {
+                dom_b = d2 + 1; dom_e = d1;
+                sub_e = d2;
+            }
+        }
+    }
+    // the reference keeps "None" as a string: a subdomain that reads None counts as absent, and the entropy column is
+    // the entropy of whatever string is there - 2.0 for "None"
+    const bool sub_none = sub_e < 0 || bytes_equal(s, sub_e, "None", 4);
+    sub_len[i] = sub_none ? 0 : sub_e;
+    num_parts[i] = parts;
+    const unsigned char none[4] = {'N', 'o', 'n', 'e'};
+    const double ent = sub_e < 0 ? string_entropy(none, 4, term) : string_entropy(s, sub_e, term);
+    entropy_bits[i] = ent > 0.0 ? __double_as_longlong(ent) : 0;
+    // a missing domain is the string "None" in the reference and is looked up like any other
+    const unsigned char* dp = dom_b >= 0 ? s + dom_b : none;
+    const int dl = dom_b >= 0 ? dom_e - dom_b : 4;
+    int t = 0;
+    if (bytes_equal(dp, dl, "intel", 5)) t = 2;
+    else if (top.slot) {
+        unsigned long long h = fnv1a(dp, dl) & top.mask;
+        for (;;) {
+            const int32_t idx = top.slot[h];
+            if (idx < 0) break;
+            const int64_t b = top.offsets[idx];
+            if (bytes_equal(dp, dl, (const char*)(top.bytes + b), (int)(top.offsets[idx + 1] - b))) { t = 1; break; }
+            h = (h + 1) & top.mask;
+        }
+    }
+    top_out[i] = t;
+    if (spans) {
+        spans[3 * i] = dom_b;
+        spans[3 * i + 1] = dom_e;
+        spans[3 * i + 2] = sub_e;
+    }
+}
+
+struct DnsCutsDev {
+    long long time[10], frame[10], sub_len[5], entropy[5], periods[5];
+};
+
+__global__ void __launch_bounds__(256) dns_words_kernel(const int32_t* __restrict__ frame_len, const int64_t* __restrict__ tstamp,
+                                                        const int64_t* __restrict__ sub_len, const int64_t* __restrict__ entropy_bits,
+                                                        const int64_t* __restrict__ num_parts, const int32_t* __restrict__ top,
+                                                        const int32_t* __restrict__ qtype, const int32_t* __restrict__ rcode, int64_t n,
+                                                        DnsCutsDev cuts, int64_t* __restrict__ code, int* __restrict__ bad)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const long long f = frame_len[i], t = tstamp[i], sl = sub_len[i], eb = entropy_bits[i], np = num_parts[i];
+    int fb = 0, tb = 0, sb = 0, ebn = 0, pb = 0;
+#pragma unroll
+    for (int q = 0; q < 9; q++) { fb += f > cuts.frame[q]; tb += t > cuts.time[q]; }
+#pragma unroll
+    for (int q = 0; q < 4; q++) { sb += sl > cuts.sub_len[q]; ebn += eb > cuts.entropy[q]; pb += np > cuts.periods[q]; }
+    const int qt = qtype[i], rc = rcode[i];
+    if ((unsigned)qt > 65535u || (unsigned)rc > 65535u) {
+        *bad = 1;
+        return;
+    }
+    long long c = top[i];
+    c = c * 10 + fb; c = c * 10 + tb; c = c * 5 + sb; c = c * 5 + ebn; c = c * 5 + pb;
+    code[i] = (c << 32) | ((long long)qt << 16) | rc;
+}
+
+__global__ void __launch_bounds__(256) widen_kernel(const int32_t* __restrict__ in, int64_t n, int64_t* __restrict__ out)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = in[i];
+}
+
+__global__ void __launch_bounds__(256) count_positive_kernel(const int64_t* __restrict__ v, int64_t n, unsigned long long* __restrict__ out)
+{
+    unsigned int c = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) c += v[i] > 0;
+    c = __reduce_add_sync(0xffffffffu, c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, (unsigned long long)c);
+}
+
+// Quantiles.computeQuantiles over the entries > 0 of a non-negative column (the reference filters "> 0" first,
+// DNSWordCreation.scala:96-121): the zeros sort first, so the ranks shift by their number.
+int quantiles_positive(const int64_t* d_v, int64_t n, const double* thresholds, int nq, long long* out /* LLONG_MAX = +inf */,
+                       cudaStream_t st)
+{
+    unsigned long long* d_cnt = nullptr;
+    ONILDA_CUDA(cudaMalloc(&d_cnt, sizeof *d_cnt));
+    struct G { void* p; ~G() { cudaFree(p); } } g{d_cnt};
+    ONILDA_CUDA(cudaMemsetAsync(d_cnt, 0, sizeof *d_cnt, st));
+    count_positive_kernel<<<148 * 8, 256, 0, st>>>(d_v, n, d_cnt);
+    unsigned long long valid = 0;
+    ONILDA_CUDA(cudaMemcpyAsync(&valid, d_cnt, sizeof valid, cudaMemcpyDeviceToHost, st));
+    ONILDA_CUDA(cudaStreamSynchronize(st));
+    if (valid == 0) {
+        for (int q = 0; q < nq; q++) out[q] = LLONG_MAX;
+        return ONILDA_OK;
+    }
+    long long ranks[kMaxQ];
+    for (int q = 0; q < nq; q++) ranks[q] = rank_of_threshold(thresholds[q], (long long)valid) + (n - (long long)valid);
+    return select_ranks_device(d_v, n, ranks, nq, out, st);
+}
+
+}  // namespace
+
+// features_out (device, may be null): [0] subdomain length, [1] parts, [2] entropy bits, each int64[n]; top flag int32[n];
+// spans int32[n][3] = domain begin, domain end, subdomain end (-1 = "None")
+struct DnsFeatureOut {
+    int64_t *sub_len, *parts, *entropy_bits;
+    int32_t *top, *spans;
+};
+
+static int dns_words_core(const char* names, const int64_t* name_offsets, const int32_t* frame_len, const int64_t* unix_tstamp,
+                          const int32_t* qry_type, const int32_t* qry_rcode, int64_t n, const char* top_bytes,
+                          const int64_t* top_offsets, const int32_t* top_slots, int64_t top_capacity, onilda_dns_cuts* cuts_out,
+                          int64_t* word_code, void* stream, const DnsFeatureOut* fo)
+{
+    int32_t* features_spans = fo ? fo->spans : nullptr;
+    if (n < 0 || !cuts_out || (n > 0 && (!names || !name_offsets || !frame_len || !unix_tstamp || !qry_type || !qry_rcode || !word_code)))
+        return onilda_fail(ONILDA_EINVAL, "dns_words: bad argument");
+    if (top_capacity < 0 || (top_capacity & (top_capacity - 1)) || (top_capacity > 0 && (!top_bytes || !top_offsets || !top_slots)))
+        return onilda_fail(ONILDA_EINVAL, "dns_words: the top-domain table needs a power-of-two capacity");
+    for (int q = 0; q < 10; q++) cuts_out->time[q] = cuts_out->frame_length[q] = INFINITY;
+    for (int q = 0; q < 5; q++) cuts_out->subdomain_length[q] = cuts_out->entropy[q] = cuts_out->num_periods[q] = INFINITY;
+    if (n == 0) return ONILDA_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    static const double deciles[10] = {0.1, 0.2, 0.3, 0.4, 0.5, 0.6, 0.7, 0.8, 0.9, 1.0};
+    static const double quintiles[5] = {0.2, 0.4, 0.6, 0.8, 1.0};
+    // the table of entropy terms, from the host's log10
+    std::vector<double> term(256 * 256, 0.0);
+    for (int len = 1; len < 256; len++)
+        for (int k = 1; k <= len; k++) {
+            const double p = (double)k / (double)len;
+            term[(size_t)len * 256 + k] = -p * log10(p) / log10(2.0);
+        }
+    DevMem d_term, d_cols, d_top, d_bad;
+    int rc;
+    const size_t b8 = (sizeof(int64_t) * (size_t)n + 255) & ~(size_t)255, b4 = (sizeof(int32_t) * (size_t)n + 255) & ~(size_t)255;
+    if ((rc = d_term.alloc(sizeof(double) * term.size(), "dns_words")) != ONILDA_OK) return rc;
+    if ((rc = d_cols.alloc(4 * b8 + b4, "dns_words")) != ONILDA_OK) return rc;
+    if ((rc = d_bad.alloc(sizeof(int), "dns_words")) != ONILDA_OK) return rc;
+    ONILDA_CUDA(cudaMemcpyAsync(d_term.p, term.data(), sizeof(double) * term.size(), cudaMemcpyHostToDevice, st));
+    ONILDA_CUDA(cudaMemsetAsync(d_bad.p, 0, sizeof(int), st));
+    char* p = (char*)d_cols.p;
+    int64_t* d_sub = (int64_t*)p; p += b8;
+    int64_t* d_parts = (int64_t*)p; p += b8;
+    int64_t* d_ent = (int64_t*)p; p += b8;
+    int64_t* d_frame = (int64_t*)p; p += b8;
+    int32_t* d_topflag = (int32_t*)p;
+    TopTable top{top_capacity > 0 ? top_slots : nullptr, (unsigned long long)(top_capacity > 0 ? top_capacity - 1 : 0),
+                 (const unsigned char*)top_bytes, top_offsets};
+    dns_features_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>((const unsigned char*)names, name_offsets, n, top,
+                                                                      (const double*)d_term.p, d_sub, d_parts, d_ent, d_topflag,
+                                                                      (int*)d_bad.p, features_spans);
+    widen_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(frame_len, n, d_frame);
+    ONILDA_CUDA(cudaGetLastError());
+    {
+        int bad0 = 0;
+        ONILDA_CUDA(cudaMemcpyAsync(&bad0, d_bad.p, sizeof bad0, cudaMemcpyDeviceToHost, st));
+        ONILDA_CUDA(cudaStreamSynchronize(st));
+        if (bad0) return onilda_fail(ONILDA_EINVAL, "dns_words: a query name is longer than 255 bytes (or the offsets decrease)");
+    }
+    DnsCutsDev cuts;
+    double c10[10];
+    if ((rc = onilda_quantiles_i64_device(unix_tstamp, n, deciles, 10, c10, stream)) != ONILDA_OK) return rc;
+    for (int q = 0; q < 10; q++) { cuts_out->time[q] = c10[q]; cuts.time[q] = (long long)c10[q]; }
+    if ((rc = onilda_quantiles_i64_device(d_frame, n, deciles, 10, c10, stream)) != ONILDA_OK) return rc;
+    for (int q = 0; q < 10; q++) { cuts_out->frame_length[q] = c10[q]; cuts.frame[q] = (long long)c10[q]; }
+    if ((rc = quantiles_positive(d_sub, n, quintiles, 5, cuts.sub_len, st)) != ONILDA_OK) return rc;
+    if ((rc = quantiles_positive(d_ent, n, quintiles, 5, cuts.entropy, st)) != ONILDA_OK) return rc;
+    if ((rc = quantiles_positive(d_parts, n, quintiles, 5, cuts.periods, st)) != ONILDA_OK) return rc;
+    for (int q = 0; q < 5; q++) {
+        cuts_out->subdomain_length[q] = cuts.sub_len[q] == LLONG_MAX ? INFINITY : (double)cuts.sub_len[q];
+        cuts_out->num_periods[q] = cuts.periods[q] == LLONG_MAX ? INFINITY : (double)cuts.periods[q];
+        if (cuts.entropy[q] == LLONG_MAX) cuts_out->entropy[q] = INFINITY;
+        else memcpy(&cuts_out->entropy[q], &cuts.entropy[q], sizeof(double));
+    }
+    dns_words_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(frame_len, unix_tstamp, d_sub, d_ent, d_parts, d_topflag, qry_type,
+                                                                   qry_rcode, n, cuts, word_code, (int*)d_bad.p);
+    ONILDA_CUDA(cudaGetLastError());
+    int bad = 0;
+    ONILDA_CUDA(cudaMemcpyAsync(&bad, d_bad.p, sizeof bad, cudaMemcpyDeviceToHost, st));
+    ONILDA_CUDA(cudaStreamSynchronize(st));
+    if (bad) return onilda_fail(ONILDA_EINVAL, "dns_words: query type / response code outside 0-65535");
+    if (fo) {
+        ONILDA_CUDA(cudaMemcpyAsync(fo->sub_len, d_sub, sizeof(int64_t) * (size_t)n, cudaMemcpyDeviceToDevice, st));
+        ONILDA_CUDA(cudaMemcpyAsync(fo->parts, d_parts, sizeof(int64_t) * (size_t)n, cudaMemcpyDeviceToDevice, st));
+        ONILDA_CUDA(cudaMemcpyAsync(fo->entropy_bits, d_ent, sizeof(int64_t) * (size_t)n, cudaMemcpyDeviceToDevice, st));
+        ONILDA_CUDA(cudaMemcpyAsync(fo->top, d_topflag, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToDevice, st));
+        ONILDA_CUDA(cudaStreamSynchronize(st));
+    }
+    return ONILDA_OK;
+}
+
+extern "C" int onilda_dns_words_device(const char* names, const int64_t* name_offsets, const int32_t* frame_len,
+                                       const int64_t* unix_tstamp, const int32_t* qry_type, const int32_t* qry_rcode, int64_t n,
+                                       const char* top_bytes, const int64_t* top_offsets, const int32_t* top_slots,
+                                       int64_t top_capacity, onilda_dns_cuts* cuts_out, int64_t* word_code, void* stream)
+{
+    return dns_words_core(names, name_offsets, frame_len, unix_tstamp, qry_type, qry_rcode, n, top_bytes, top_offsets, top_slots,
+                          top_capacity, cuts_out, word_code, stream, nullptr);
+}
+
+extern "C" int onilda_dns_words(const char* names, const int64_t* name_offsets, const int32_t* frame_len, const int64_t* unix_tstamp,
+                                const int32_t* qry_type, const int32_t* qry_rcode, int64_t n, const char* top_domains,
+                                const int64_t* top_offsets, int64_t n_top, int device, onilda_dns_cuts* cuts_out, int64_t* word_code)
+{
+    return onilda_dns_words_features(names, name_offsets, frame_len, unix_tstamp, qry_type, qry_rcode, n, top_domains, top_offsets,
+                                     n_top, device, cuts_out, word_code, nullptr, nullptr, nullptr, nullptr, nullptr);
+}
+
+// The same with the per-event columns DNSPostLDA keeps beside the word (subdomain length, number of parts, subdomain
+// entropy, top-domain flag) and the byte spans of domain and subdomain inside each name ({-1,-1} / -1 = "None").
+extern "C" int onilda_dns_words_features(const char* names, const int64_t* name_offsets, const int32_t* frame_len,
+                                         const int64_t* unix_tstamp, const int32_t* qry_type, const int32_t* qry_rcode, int64_t n,
+                                         const char* top_domains, const int64_t* top_offsets, int64_t n_top, int device,
+                                         onilda_dns_cuts* cuts_out, int64_t* word_code, double* subdomain_length_out,
+                                         double* num_parts_out, double* entropy_out, int32_t* top_out, int32_t* spans_out)
+{
+    if (n < 0 || n_top < 0 || !cuts_out || (n > 0 && (!names || !name_offsets || !frame_len || !unix_tstamp || !qry_type || !qry_rcode || !word_code)) ||
+        (n_top > 0 && (!top_domains || !top_offsets)))
+        return onilda_fail(ONILDA_EINVAL, "dns_words: bad argument");
+    if (onilda_device_count() == 0)
+        return onilda_fail(ONILDA_ECUDA, "dns_words: no CUDA device is usable and this library has no CPU path");
+    DeviceScope scope;
+    int rc = scope.enter(device);
+    if (rc != ONILDA_OK) return rc;
+    if (n == 0) return onilda_dns_words_device(nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, nullptr, nullptr, nullptr, 0, cuts_out, nullptr, nullptr);
+    const bool want_features = subdomain_length_out || num_parts_out || entropy_out || top_out || spans_out;
+    // hash set of the top domains: open addressing over FNV-1a, exact (the device compares the bytes)
+    int64_t cap = 0;
+    std::vector<int32_t> slots;
+    if (n_top > 0) {
+        if (n_top >= ((int64_t)1 << 30)) return onilda_fail(ONILDA_EINVAL, "dns_words: too many top domains");
+        cap = 1;
+        while (cap < 2 * n_top) cap <<= 1;
+        slots.assign((size_t)cap, -1);
+        for (int64_t t = 0; t < n_top; t++) {
+            const unsigned char* b = (const unsigned char*)top_domains + top_offsets[t];
+            const int len = (int)(top_offsets[t + 1] - top_offsets[t]);
+            unsigned long long h = fnv1a(b, len) & (unsigned long long)(cap - 1);
+            bool dup = false;
+            while (slots[(size_t)h] >= 0) {
+                const int32_t o = slots[(size_t)h];
+                const int olen = (int)(top_offsets[o + 1] - top_offsets[o]);
+                if (olen == len && memcmp(top_domains + top_offsets[o], b, (size_t)len) == 0) { dup = true; break; }
+                h = (h + 1) & (unsigned long long)(cap - 1);
+            }
+            if (!dup) slots[(size_t)h] = (int32_t)t;
+        }
+    }
+    const size_t name_bytes = (size_t)name_offsets[n], top_bytes = n_top > 0 ? (size_t)top_offsets[n_top] : 0;
+    DevMem d;
+    const size_t a = 256;
+    auto up = [&](size_t x) { return (x + a - 1) & ~(a - 1); };
+    const size_t total = up(name_bytes) + up(sizeof(int64_t) * (size_t)(n + 1)) + 3 * up(sizeof(int32_t) * (size_t)n) +
+                         2 * up(sizeof(int64_t) * (size_t)n) + up(top_bytes) + up(sizeof(int64_t) * (size_t)(n_top + 1)) +
+                         up(sizeof(int32_t) * (size_t)cap);
+    if ((rc = d.alloc(total, "dns_words")) != ONILDA_OK) return rc;
+    char* p = (char*)d.p;
+    auto put = [&](const void* src, size_t bytes) -> void* {
+        void* dst = p;
+        if (bytes) cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, 0);
+        p += up(bytes);
+        return dst;
+    };
+    const char* d_names = (const char*)put(names, name_bytes);
+    const int64_t* d_off = (const int64_t*)put(name_offsets, sizeof(int64_t) * (size_t)(n + 1));
+    const int32_t* d_frame = (const int32_t*)put(frame_len, sizeof(int32_t) * (size_t)n);
+    const int32_t* d_qt = (const int32_t*)put(qry_type, sizeof(int32_t) * (size_t)n);
+    const int32_t* d_rc = (const int32_t*)put(qry_rcode, sizeof(int32_t) * (size_t)n);
+    const int64_t* d_ts = (const int64_t*)put(unix_tstamp, sizeof(int64_t) * (size_t)n);
+    int64_t* d_code = (int64_t*)p; p += up(sizeof(int64_t) * (size_t)n);
+    const char* d_top = (const char*)put(top_domains, top_bytes);
+    const int64_t* d_topoff = (const int64_t*)put(top_offsets, n_top > 0 ? sizeof(int64_t) * (size_t)(n_top + 1) : 0);
+    const int32_t* d_slots = (const int32_t*)put(slots.data(), sizeof(int32_t) * (size_t)cap);
+    ONILDA_CUDA(cudaGetLastError());
+    DevMem d_feat;
+    DnsFeatureOut fo{nullptr, nullptr, nullptr, nullptr, nullptr};
+    if (want_features) {
+        const size_t f8 = up(sizeof(int64_t) * (size_t)n), f4 = up(sizeof(int32_t) * (size_t)n);
+        if ((rc = d_feat.alloc(3 * f8 + f4 + 3 * f4, "dns_words")) != ONILDA_OK) return rc;
+        char* q = (char*)d_feat.p;
+        fo.sub_len = (int64_t*)q; q += f8;
+        fo.parts = (int64_t*)q; q += f8;
+        fo.entropy_bits = (int64_t*)q; q += f8;
+        fo.top = (int32_t*)q; q += f4;
+        fo.spans = (int32_t*)q;
+    }
+    rc = dns_words_core(d_names, d_off, d_frame, d_ts, d_qt, d_rc, n, d_top, d_topoff, d_slots, cap, cuts_out, d_code, nullptr,
+                        want_features ? &fo : nullptr);
+    if (rc != ONILDA_OK) return rc;
+    ONILDA_CUDA(cudaMemcpy(word_code, d_code, sizeof(int64_t) * (size_t)n, cudaMemcpyDeviceToHost));
+    if (want_features) {
+        std::vector<int64_t> tmp((size_t)n);
+        if (subdomain_length_out) {
+            ONILDA_CUDA(cudaMemcpy(tmp.data(), fo.sub_len, sizeof(int64_t) * (size_t)n, cudaMemcpyDeviceToHost));
+            for (int64_t i = 0; i < n; i++) subdomain_length_out[i] = (double)tmp[(size_t)i];
+        }
+        if (num_parts_out) {
+            ONILDA_CUDA(cudaMemcpy(tmp.data(), fo.parts, sizeof(int64_t) * (size_t)n, cudaMemcpyDeviceToHost));
+            for (int64_t i = 0; i < n; i++) num_parts_out[i] = (double)tmp[(size_t)i];
+        }
+        if (entropy_out) ONILDA_CUDA(cudaMemcpy(entropy_out, fo.entropy_bits, sizeof(int64_t) * (size_t)n, cudaMemcpyDeviceToHost));
+        if (top_out) ONILDA_CUDA(cudaMemcpy(top_out, fo.top, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost));
+        if (spans_out) ONILDA_CUDA(cudaMemcpy(spans_out, fo.spans, 3 * sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost));
+    }
+    return ONILDA_OK;
+}
+
+// The reference's word of a code: top_frameBin_timeBin_subdomainLengthBin_entropyBin_periodsBin_queryType_responseCode
+// (DNSWordCreation.scala:226-235).  Returns the length or a negative error code.
+extern "C" int onilda_dns_word_string(int64_t code, char* buf, size_t cap)
+{
+    if (code < 0 || !buf) return onilda_fail(ONILDA_EINVAL, "dns_word_string: bad argument");
+    const int rc = (int)(code & 0xffff), qt = (int)((code >> 16) & 0xffff);
+    long long c = code >> 32;
+    const int pb = (int)(c % 5); c /= 5;
+    const int eb = (int)(c % 5); c /= 5;
+    const int sb = (int)(c % 5); c /= 5;
+    const int tb = (int)(c % 10); c /= 10;
+    const int fb = (int)(c % 10); c /= 10;
+    if (c > 2) return onilda_fail(ONILDA_EINVAL, "dns_word_string: not a word code");
+    const int len = snprintf(buf, cap, "%d_%d_%d_%d_%d_%d_%d_%d", (int)c, fb, tb, sb, eb, pb, qt, rc);
+    if (len < 0 || (size_t)len >= cap) return onilda_fail(ONILDA_EINVAL, "dns_word_string: buffer of %zu bytes is too small", cap);
+    return len;
+}

@@ -321,6 +321,84 @@ def flow_words(hour, minute, second, ibyt, ipkt, sport, dport):
     return {"time": time_cuts, "ibyt": ibyt_cuts, "ipkt": ipkt_cuts}, src, dst
 
 
+# ISO country-code labels of DNSWordCreation.scala:17-30 (the set there also holds "" - never a last label)
+COUNTRY_CODES = set("""ac ad ae af ag ai al am an ao aq ar as at au aw ax az ba bb bd be bf bg bh bi bj bm bn bo bq br bs bt
+bv bw by bz ca cc cd cf cg ch ci ck cl cm cn co cr cu cv cw cx cy cz de dj dk dm do dz ec ee eg eh er es et eu fi fj fk fm
+fo fr ga gb gd ge gf gg gh gi gl gm gn gp gq gr gs gt gu gw gy hk hm hn hr ht hu id ie il im in io iq ir is it je jm jo jp
+ke kg kh ki km kn kp kr krd kw ky kz la lb lc li lk lr ls lt lu lv ly ma mc md me mg mh mk ml mm mn mo mp mq mr ms mt mu mv
+mw mx my mz na nc ne nf ng ni nl no np nr nu nz om pa pe pf pg ph pk pl pm pn pr ps pt pw py qa re ro rs ru rw sa sb sc sd
+se sg sh si sj sk sl sm sn so sr ss st su sv sx sy sz tc td tf tg th tj tk tl tm tn to tp tr tt tv tw tz ua ug uk us uy uz
+va vc ve vg vi vn vu wf ws ye yt za zm zw""".split()) | {""}
+
+
+def java_split_dots(url):
+    """String.split("[.]"): trailing empty strings are removed; no dot -> the string itself."""
+    parts = url.split(".")
+    if len(parts) > 1:
+        while parts and parts[-1] == "":
+            parts.pop()
+    return parts
+
+
+def extract_subdomain(url):
+    """DNSWordCreation.extractSubdomain (dns/DNSWordCreation.scala:155-196): [domain, subdomain, subdomain length, parts]."""
+    parts = java_split_dots(url)
+    n = len(parts)
+    domain = subdomain = "None"
+    is_ip = ("IP" if parts[n - 1] == "arpa" and parts[n - 2] == "in-addr" else "Name") if n > 2 else "Unknown"
+    if n > 2 and is_ip != "IP":
+        if parts[n - 1] in COUNTRY_CODES:
+            domain = parts[n - 3]
+            if 1 <= n - 3:
+                subdomain = ".".join(parts[0:n - 3])
+        else:
+            domain = parts[n - 2]
+            subdomain = ".".join(parts[0:n - 2])
+    return [domain, subdomain, float(len(subdomain)) if subdomain != "None" else 0.0, float(n)]
+
+
+def string_entropy(v):
+    """Entropy.stringEntropy (utilities/Entropy.scala:16-23): sum over distinct characters of -p log10(p) / log10(2).
+    The reference adds in the iteration order of a Scala Map (unspecified); here the largest count goes first, so that
+    the value depends on the counts only."""
+    import math
+    counts = {}
+    for ch in v:
+        counts[ch] = counts.get(ch, 0) + 1
+    total = 0.0
+    for k in sorted(counts.values(), reverse=True):
+        p = float(k) / len(v)
+        total += -p * math.log10(p) / math.log10(2)
+    return total
+
+
+def get_top_domain(top_domains, domain):
+    """DNSWordCreation.getTopDomain (:147-153)."""
+    return "2" if domain == "intel" else ("1" if domain in top_domains else "0")
+
+
+def dns_words(names, frame_len, unix_tstamp, qry_type, qry_rcode, top_domains=()):
+    """DNSWordCreation.dnsWordCreation (:32-145) + dnsWord (:213-235) on columns: the five cut arrays and the words."""
+    top = set(top_domains)
+    feats = [extract_subdomain(u) for u in names]
+    entropy = [string_entropy(f[1]) for f in feats]
+    cuts = {
+        "time": compute_quantiles(np.asarray(unix_tstamp, np.float64), DECILES),
+        "frame_length": compute_quantiles(np.asarray(frame_len, np.float64), DECILES),
+        "subdomain_length": compute_quantiles([f[2] for f in feats if f[2] > 0], QUINTILES),
+        "entropy": compute_quantiles([e for e in entropy if e > 0], QUINTILES),
+        "num_periods": compute_quantiles([f[3] for f in feats if f[3] > 0], QUINTILES),
+    }
+    words = []
+    for i, f in enumerate(feats):
+        words.append("_".join(str(x) for x in [
+            get_top_domain(top, f[0]), quantile_bin(float(frame_len[i]), cuts["frame_length"]),
+            quantile_bin(float(unix_tstamp[i]), cuts["time"]), quantile_bin(f[2], cuts["subdomain_length"]),
+            quantile_bin(entropy[i], cuts["entropy"]), quantile_bin(f[3], cuts["num_periods"]),
+            int(qry_type[i]), int(qry_rcode[i])]))
+    return cuts, words
+
+
 def pairs_count(doc, word):
     """`.map((ip, word) -> 1).reduceByKey(_ + _)` (FlowPreLDA.scala:131-137, DNSPreLDA.scala:114-120) on integer ids;
     Spark's output order is unspecified, this one is sorted by (doc, word).  Returns (doc, word, count)."""

@@ -756,3 +756,78 @@ def test_flow_pipeline_end_to_end(oni, oracle):
     assert tie_aware_overlap(idx, rmin, rtop, rtol=MODEL_RTOL) >= 0.99
     scorer.close()
     em.close()
+
+
+# ---------------------------------------------------------------- N4: DNS word creation
+DNS_TIE = 1e-12      # entropy terms come from the host's log10 on both sides: in practice the values are bit-equal
+
+
+def dns_columns(rng, n):
+    labels = ["www", "mail", "a", "xn--bcher-kva", "cdn-7", "None", "x" * 40, "api.v2", "0123456789abcdef" * 2, ""]
+    domains = ["amazon", "intel", "google", "example", "zz-top", "None"]
+    tlds = ["com", "org", "com.mx", "co.uk", "krd", "de", "arpa", "in-addr.arpa", "net."]
+    names = []
+    for _ in range(n):
+        k = rng.integers(0, 8)
+        if k == 0:
+            names.append("%d.%d.%d.%d.in-addr.arpa" % tuple(rng.integers(0, 255, 4)))
+        elif k == 1:
+            names.append(rng.choice(["localhost", "", ".", "..", "a.b", ".a.com", "a..b.com", "com.mx", "x.y.z."]))
+        else:
+            sub = ".".join(rng.choice(labels, rng.integers(0, 4)))
+            names.append(".".join(x for x in [sub, rng.choice(domains), rng.choice(tlds)] if x != "" or rng.random() < 0.1))
+    frame = rng.integers(60, 1500, n)
+    ts = 1_462_000_000 + rng.integers(0, 86400, n)
+    qt = rng.choice([1, 28, 12, 255, 65535], n)
+    rc = rng.choice([0, 3, 2], n)
+    return names, frame, ts, qt, rc
+
+
+def test_dns_reference_goldens(oni, oracle):
+    """DNSWordCreationTest.scala through the GPU path: the five extractSubdomain cases and the entropy of abcdefg."""
+    names = ["123.103.104.10.in-addr.arpa", "services.amazon.com.mx", "amazon.com.mx", "services.amazon.com", "amazon.com",
+             "abcdefg.example.com"]
+    n = len(names)
+    cuts, code, f = oni.dns_words(names, [100] * n, [1] * n, [1] * n, [0] * n, top_domains=["amazon"], features=True)
+    want = [("None", "None", 0, 6), ("amazon", "services", 8, 4), ("amazon", "None", 0, 3), ("amazon", "services", 8, 3),
+            ("None", "None", 0, 2)]
+    for i, (dom, sub, sl, parts) in enumerate(want):
+        b, e, se = f["spans"][i]
+        assert (names[i][b:e] if b >= 0 else "None") == dom and (names[i][:se] if se >= 0 else "None") == sub
+        assert f["subdomain_length"][i] == sl and f["num_parts"][i] == parts
+    assert f["entropy"][5] == 2.807354922057604                       # Entropy.stringEntropy("abcdefg")
+    assert list(f["top"]) == [0, 1, 1, 1, 0, 0]
+    assert f["entropy"][0] == 2.0                                      # the entropy of the string "None"
+
+
+@pytest.mark.parametrize("n", [1, 50, 4000])
+def test_dns_words_match_oracle(oni, oracle, n):
+    rng = np.random.default_rng(100 + n)
+    names, frame, ts, qt, rc = dns_columns(rng, n)
+    top = ["amazon", "google", "None", "example", "intel"]
+    cuts, code, f = oni.dns_words(names, frame, ts, qt, rc, top_domains=top, features=True)
+    rcuts, rwords = oracle.dns_words(names, frame, ts, qt, rc, top)
+    feats = [oracle.extract_subdomain(u) for u in names]
+    assert np.array_equal(f["subdomain_length"], [x[2] for x in feats]) and np.array_equal(f["num_parts"], [x[3] for x in feats])
+    ent = np.array([oracle.string_entropy(x[1]) for x in feats])
+    assert np.allclose(f["entropy"], ent, rtol=DNS_TIE, atol=0)
+    for k in rcuts:
+        assert np.allclose(cuts[k], rcuts[k], rtol=DNS_TIE, atol=0), k
+    words = [oni.dns_word_string(c) for c in code]
+    assert words == rwords
+    for i, u in enumerate(names):
+        b, e, se = f["spans"][i]
+        assert (u[b:e] if b >= 0 else "None") == feats[i][0] and (u[:se] if se >= 0 else "None") == feats[i][1]
+
+
+def test_dns_words_edge_cases(oni, oracle):
+    cuts, code = oni.dns_words([], [], [], [], [])
+    assert len(code) == 0 and np.all(np.isinf(cuts["entropy"]))
+    # no subdomain anywhere: every subdomain is "None" (entropy 2.0, length 0): length cuts stay +infinity
+    cuts, code = oni.dns_words(["a.com", "b.org"], [60, 70], [5, 6], [1, 1], [0, 0])
+    assert np.all(np.isinf(cuts["subdomain_length"])) and list(cuts["entropy"]) == [2.0] * 5
+    assert [oni.dns_word_string(c) for c in code] == oracle.dns_words(["a.com", "b.org"], [60, 70], [5, 6], [1, 1], [0, 0])[1]
+    with pytest.raises(oni.OnildaError):
+        oni.dns_words(["x" * 300 + ".com"], [1], [1], [1], [0])
+    with pytest.raises(oni.OnildaError):
+        oni.dns_words(["a.b.com"], [1], [1], [70000], [0])

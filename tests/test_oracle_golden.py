@@ -245,3 +245,29 @@ def test_adjust_port_golden(oracle):
         sip, dip = ("10.0.2.115", "172.16.0.107") if i < 7 else ("172.16.0.107", "10.0.2.115")
         r = oracle.adjust_port(sip, dip, dport, sport, 4.0, 7.0, 7.0)
         assert r == [port, "10.0.2.115 172.16.0.107", sword, dword], (i, r)
+
+
+# ---- DNSWordCreationTest.scala: every case
+def test_dns_word_creation_golden(oracle):
+    assert oracle.extract_subdomain("123.103.104.10.in-addr.arpa") == ["None", "None", 0.0, 6.0]
+    assert oracle.extract_subdomain("services.amazon.com.mx") == ["amazon", "services", 8.0, 4.0]
+    assert oracle.extract_subdomain("amazon.com.mx") == ["amazon", "None", 0.0, 3.0]
+    assert oracle.extract_subdomain("services.amazon.com") == ["amazon", "services", 8.0, 3.0]
+    assert oracle.extract_subdomain("amazon.com") == ["None", "None", 0.0, 2.0]
+    assert oracle.string_entropy("abcdefg") == 2.807354922057604
+    assert oracle.string_entropy("None") == 2.0 and oracle.string_entropy("") == 0.0
+
+
+def test_country_codes_match_reference(oracle):
+    """The oracle's and the kernel's label lists against the reference's own set, where the reference is present."""
+    import re
+    root = Path(__file__).resolve().parent.parent
+    src = (root / "open-network-insight_b200" / "csrc" / "words.cu").read_text()
+    body = "".join(re.findall(r'"([a-z]+)"', src[src.index("kCountry2[] ="):src.index("constexpr int kCountry2Count")]))
+    kernel = {body[i:i + 2] for i in range(0, len(body), 2)} | {"krd", ""}
+    assert len(body) % 2 == 0 and kernel == oracle.COUNTRY_CODES
+    ref = Path("/root/reference/oni-ml/src/main/scala/org/opennetworkinsight/dns/DNSWordCreation.scala")
+    if ref.exists():
+        text = ref.read_text()
+        listed = set(re.findall(r'"([a-z]*)"', text[text.index("val countryCodes = Set("):text.index("def dnsWordCreation")]))
+        assert listed == oracle.COUNTRY_CODES
