@@ -831,3 +831,47 @@ def test_dns_words_edge_cases(oni, oracle):
         oni.dns_words(["x" * 300 + ".com"], [1], [1], [1], [0])
     with pytest.raises(oni.OnildaError):
         oni.dns_words(["a.b.com"], [1], [1], [70000], [0])
+
+
+def test_dns_pipeline_end_to_end(oni, oracle):
+    """The DNS path on the GPU against the oracle chain: DNSWordCreation -> word counts per client ip (DNSPreLDA.scala:114-122)
+    -> corpus -> EM -> theta/phi -> score(ip, word), filter, order, limit (DNSPostLDA)."""
+    rng = np.random.default_rng(53)
+    n, D = 20_000, 300
+    names, frame, ts, qt, rc = dns_columns(rng, n)
+    ip = (rng.zipf(1.4, n) % D).astype(np.int32)
+    top = ["amazon", "google"]
+    cuts, code = oni.dns_words(names, frame, ts, qt, rc, top_domains=top)
+    vocab = np.unique(code)
+    word = np.searchsorted(vocab, code).astype(np.int32)
+    V = len(vocab)
+    trip = oni.pairs_count(ip, word, D, V)
+    corpus = oni.Corpus.from_triples(*trip, num_docs=D, num_terms=V)
+
+    rcuts, rwords = oracle.dns_words(names, frame, ts, qt, rc, top)
+    index = {oni.dns_word_string(c): i for i, c in enumerate(vocab)}
+    rword = np.array([index[wd] for wd in rwords], np.int32)                 # KeyError = a word the GPU never produced
+    assert np.array_equal(rword, word)
+    roff, rw, rcnt = oracle.triples_to_csr(*oracle.pairs_count(ip, rword), num_docs=D)
+    off, w, cnt, _ = corpus.csr()
+    assert np.array_equal(off, roff) and np.array_equal(w, rw) and np.array_equal(cnt, rcnt)
+
+    m = oni.Model.new(20, V)
+    m.init_random(5)
+    m.alpha = 2.5
+    ref = oracle.run_em(roff, rw, rcnt, V, 2.5, m.log_beta.copy(), oracle.settings(em_max_iter=1))
+    em = oni.EM(corpus, m, oni.Settings(20, 1e-6, 1, 1e-6, 1))
+    liks, keep = [], True
+    while keep:
+        lik, _, keep = em.iterate()
+        liks.append(lik)
+    assert len(liks) == len(ref["lik"]) and np.max(np.abs(np.array(liks) - ref["lik"]) / np.abs(ref["lik"])) < LIK_RTOL
+    scorer = oni.Scorer.from_em(em)
+    s = scorer.score(ip, word)
+    rs = oracle.score(ip, rword, oracle.theta_from_gamma(ref["gamma"]), oracle.phi_from_logbeta(ref["log_beta"]))
+    assert np.max(np.abs(s - rs) / rs) < MODEL_RTOL
+    idx, top_s = scorer.topk(s, float(np.quantile(rs, 0.05)), 100)
+    ridx, rtop = oracle.topk(rs, float(np.quantile(rs, 0.05)), 100)
+    assert tie_aware_overlap(idx, rs, rtop, rtol=MODEL_RTOL) >= 0.99
+    scorer.close()
+    em.close()
