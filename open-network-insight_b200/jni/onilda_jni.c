@@ -115,3 +115,107 @@ JNIEXPORT void JNICALL FN(destroy)(JNIEnv* e, jobject self, jlong h)
     (void)e; (void)self;
     onilda_scorer_destroy((onilda_scorer*)(intptr_t)h);
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * The steps either side of LDA.  Scala side:
+ *
+ *   @native def flowWords(hour: Array[Int], minute: Array[Int], second: Array[Int], ibyt: Array[Long], ipkt: Array[Long],
+ *                         sport: Array[Int], dport: Array[Int], cuts: Array[Double] (25: time, ibyt, ipkt),
+ *                         srcCode: Array[Int], dstCode: Array[Int]): Unit          // FlowWordCreation.flowWordCreation
+ *   @native def flowWordString(code: Int): String
+ *   @native def pairsCount(doc: Array[Int], word: Array[Int], numDocs: Long, numTerms: Int,
+ *                          docOut: Array[Int], wordOut: Array[Int], countOut: Array[Int]): Long   // reduceByKey(_ + _)
+ *   @native def corpusFromTriples(doc: Array[Int], word: Array[Int], count: Array[Int], numDocs: Long, numTerms: Int): Long
+ *   @native def corpusSaveDat(corpus: Long, path: String): Unit                   // createModel's lines, when the file is wanted
+ *   @native def flowResults(h: Long, sdoc: Array[Int], sword: Array[Int], ddoc: Array[Int], dword: Array[Int],
+ *                           threshold: Double, k: Long, idx: Array[Long], srcScore: Array[Double], dstScore: Array[Double]): Long
+ */
+#define PIN(arr) ((arr) ? (*e)->GetPrimitiveArrayCritical(e, (arr), NULL) : NULL)
+#define UNPIN(arr, p, mode) do { if (p) (*e)->ReleasePrimitiveArrayCritical(e, (arr), (p), (mode)); } while (0)
+
+JNIEXPORT void JNICALL FN(flowWords)(JNIEnv* e, jobject self, jintArray hour, jintArray minute, jintArray second, jlongArray ibyt,
+                                     jlongArray ipkt, jintArray sport, jintArray dport, jdoubleArray cuts, jintArray src_code,
+                                     jintArray dst_code)
+{
+    (void)self;
+    const jsize n = (*e)->GetArrayLength(e, hour);
+    jint *h = PIN(hour), *m = PIN(minute), *s = PIN(second), *sp = PIN(sport), *dp = PIN(dport), *sc = PIN(src_code), *dc = PIN(dst_code);
+    jlong *b = PIN(ibyt), *p = PIN(ipkt);
+    jdouble* c = PIN(cuts);
+    onilda_flow_cuts fc;
+    int rc = onilda_flow_words((const int32_t*)h, (const int32_t*)m, (const int32_t*)s, (const int64_t*)b, (const int64_t*)p,
+                               (const int32_t*)sp, (const int32_t*)dp, n, -1, &fc, (int32_t*)sc, (int32_t*)dc);
+    if (rc == ONILDA_OK && c) {
+        for (int q = 0; q < 10; q++) { c[q] = fc.time[q]; c[10 + q] = fc.ibyt[q]; }
+        for (int q = 0; q < 5; q++) c[20 + q] = fc.ipkt[q];
+    }
+    UNPIN(cuts, c, 0); UNPIN(dst_code, dc, 0); UNPIN(src_code, sc, 0);
+    UNPIN(ipkt, p, JNI_ABORT); UNPIN(ibyt, b, JNI_ABORT); UNPIN(dport, dp, JNI_ABORT); UNPIN(sport, sp, JNI_ABORT);
+    UNPIN(second, s, JNI_ABORT); UNPIN(minute, m, JNI_ABORT); UNPIN(hour, h, JNI_ABORT);
+    if (rc != ONILDA_OK) throw_last(e);
+}
+
+JNIEXPORT jstring JNICALL FN(flowWordString)(JNIEnv* e, jobject self, jint code)
+{
+    (void)self;
+    char buf[64];
+    if (onilda_flow_word_string(code, buf, sizeof buf) < 0) { throw_last(e); return NULL; }
+    return (*e)->NewStringUTF(e, buf);
+}
+
+JNIEXPORT jlong JNICALL FN(pairsCount)(JNIEnv* e, jobject self, jintArray doc, jintArray word, jlong num_docs, jint num_terms,
+                                       jintArray doc_out, jintArray word_out, jintArray count_out)
+{
+    (void)self;
+    const jsize n = (*e)->GetArrayLength(e, doc);
+    jint *d = PIN(doc), *w = PIN(word), *od = PIN(doc_out), *ow = PIN(word_out), *oc = PIN(count_out);
+    int64_t m = 0;
+    int rc = onilda_pairs_count((const int32_t*)d, (const int32_t*)w, n, num_docs, num_terms, -1, (int32_t*)od, (int32_t*)ow,
+                                (int32_t*)oc, &m);
+    UNPIN(count_out, oc, 0); UNPIN(word_out, ow, 0); UNPIN(doc_out, od, 0); UNPIN(word, w, JNI_ABORT); UNPIN(doc, d, JNI_ABORT);
+    if (rc != ONILDA_OK) { throw_last(e); return 0; }
+    return (jlong)m;
+}
+
+JNIEXPORT jlong JNICALL FN(corpusFromTriples)(JNIEnv* e, jobject self, jintArray doc, jintArray word, jintArray count, jlong num_docs,
+                                              jint num_terms)
+{
+    (void)self;
+    const jsize n = (*e)->GetArrayLength(e, doc);
+    jint *d = PIN(doc), *w = PIN(word), *c = PIN(count);
+    onilda_corpus* corpus = NULL;
+    int rc = onilda_corpus_from_triples((const int32_t*)d, (const int32_t*)w, (const int32_t*)c, n, num_docs, num_terms, -1, &corpus);
+    UNPIN(count, c, JNI_ABORT); UNPIN(word, w, JNI_ABORT); UNPIN(doc, d, JNI_ABORT);
+    if (rc != ONILDA_OK) { throw_last(e); return 0; }
+    return (jlong)(intptr_t)corpus;
+}
+
+JNIEXPORT void JNICALL FN(corpusSaveDat)(JNIEnv* e, jobject self, jlong corpus, jstring path)
+{
+    (void)self;
+    const onilda_corpus* c = (const onilda_corpus*)(intptr_t)corpus;
+    int64_t docs = 0;
+    const char* p = (*e)->GetStringUTFChars(e, path, NULL);
+    int rc = p ? onilda_corpus_dims(c, &docs, NULL, NULL, NULL, NULL) : ONILDA_ENOMEM;
+    if (rc == ONILDA_OK) rc = onilda_corpus_save_dat(c, 0, docs, p);
+    if (p) (*e)->ReleaseStringUTFChars(e, path, p);
+    if (rc != ONILDA_OK) throw_last(e);
+}
+
+JNIEXPORT jlong JNICALL FN(flowResults)(JNIEnv* e, jobject self, jlong h, jintArray sdoc, jintArray sword, jintArray ddoc,
+                                        jintArray dword, jdouble threshold, jlong k, jlongArray idx, jdoubleArray src_score,
+                                        jdoubleArray dst_score)
+{
+    (void)self;
+    const jsize n = (*e)->GetArrayLength(e, sdoc);
+    jint *a = PIN(sdoc), *b = PIN(sword), *c = PIN(ddoc), *d = PIN(dword);
+    jlong* oi = PIN(idx);
+    jdouble *os = PIN(src_score), *od = PIN(dst_score);
+    int64_t kept = 0;
+    int rc = onilda_flow_results((onilda_scorer*)(intptr_t)h, (const int32_t*)a, (const int32_t*)b, (const int32_t*)c,
+                                 (const int32_t*)d, n, threshold, k, (int64_t*)oi, os, od, &kept);
+    UNPIN(dst_score, od, 0); UNPIN(src_score, os, 0); UNPIN(idx, oi, 0);
+    UNPIN(dword, d, JNI_ABORT); UNPIN(ddoc, c, JNI_ABORT); UNPIN(sword, b, JNI_ABORT); UNPIN(sdoc, a, JNI_ABORT);
+    if (rc != ONILDA_OK) { throw_last(e); return 0; }
+    return (jlong)kept;
+}
