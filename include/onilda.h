@@ -168,6 +168,22 @@ int onilda_dns_words_device(const char* names, const int64_t* name_offsets, cons
                             int64_t top_capacity, onilda_dns_cuts* cuts_out, int64_t* word_code, void* stream);
 int onilda_dns_word_string(int64_t code, char* buf, size_t cap);
 
+/* Word codes are below this (the size of the code space above). */
+#define ONILDA_FLOW_CODE_SPACE 65538000
+/* FlowPreLDA.flowPreLDA (netflow/FlowPreLDA.scala:128-139) + the word dictionary and createModel of
+ * OniLDACWrapper (OniLDACWrapper.scala:46-68, 146-168) in one call, with everything between the event
+ * columns and the corpus kept on the device: flow words, the dictionary (word id = rank of the code
+ * among the distinct codes, ascending; the codes come back in vocab_codes_out[0 .. *num_terms_out),
+ * room for vocab_cap), word counts of the source role and of the destination role, their union grouped
+ * into the corpus.  sip / dip are the caller's dense address ids (the ip dictionary stays with the
+ * caller); num_docs 0 = max id + 1.  src_word_out / dst_word_out (n each, may be null) are the events'
+ * word ids, which the scorer needs later.  n < 2^30. */
+int onilda_flow_prelda(const int32_t* hour, const int32_t* minute, const int32_t* second, const int64_t* ibyt,
+                       const int64_t* ipkt, const int32_t* sport, const int32_t* dport, const int32_t* sip,
+                       const int32_t* dip, int64_t n, int64_t num_docs, int device, onilda_flow_cuts* cuts_out,
+                       onilda_corpus** corpus_out, int32_t* vocab_codes_out, int32_t vocab_cap, int32_t* num_terms_out,
+                       int32_t* src_word_out, int32_t* dst_word_out);
+
 /* Word counts: replaces `.map((ip, word) -> 1).reduceByKey(_ + _)` of FlowPreLDA.scala:131-137 and
  * DNSPreLDA.scala:114-120 on dense integer ids (the string dictionaries stay with the caller,
  * OniLDACWrapper.scala:40-60).  n (document id, word id) occurrences -> the distinct pairs with their

@@ -72,6 +72,7 @@ def lib():
     L.onilda_corpus_from_dat.argtypes = [C.c_char_p, C.POINTER(_vp)]
     L.onilda_corpus_from_csr.argtypes = [_i64p, _vp, _vp, C.c_int64, C.c_int32, C.POINTER(_vp)]
     L.onilda_corpus_from_triples.argtypes = [_vp, _vp, _vp, C.c_int64, C.c_int64, C.c_int32, C.c_int, C.POINTER(_vp)]
+    L.onilda_flow_prelda.argtypes = [_vp] * 9 + [C.c_int64, C.c_int64, C.c_int, _vp, C.POINTER(_vp), _vp, C.c_int32, C.POINTER(C.c_int32), _vp, _vp]
     L.onilda_dns_words.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp, C.c_int64, _vp, _vp, C.c_int64, C.c_int, _vp, _vp]
     L.onilda_dns_words_features.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp, C.c_int64, _vp, _vp, C.c_int64, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
     L.onilda_dns_word_string.argtypes = [C.c_int64, C.c_char_p, C.c_size_t]
@@ -313,6 +314,26 @@ def flow_words(hour, minute, second, ibyt, ipkt, sport, dport, device=-1):
     sc, dc = np.empty(max(n, 1), np.int32), np.empty(max(n, 1), np.int32)
     _check(lib().onilda_flow_words(*[_ptr(x) for x in cols32 + cols64 + ports], n, device, C.byref(cuts), _ptr(sc), _ptr(dc)))
     return ({"time": np.array(cuts.time), "ibyt": np.array(cuts.ibyt), "ipkt": np.array(cuts.ipkt)}, sc[:n], dc[:n])
+
+
+def flow_prelda(hour, minute, second, ibyt, ipkt, sport, dport, sip, dip, num_docs=0, device=-1, vocab_cap=1 << 20):
+    """FlowPreLDA + word dictionary + createModel in one call (FlowPreLDA.scala:128-139, OniLDACWrapper.scala:46-68,146-168).
+    Returns (cuts, Corpus, vocab codes, source word ids, destination word ids)."""
+    c32 = [np.ascontiguousarray(x, np.int32) for x in (hour, minute, second)]
+    c64 = [np.ascontiguousarray(x, np.int64) for x in (ibyt, ipkt)]
+    rest = [np.ascontiguousarray(x, np.int32) for x in (sport, dport, sip, dip)]
+    n = len(c32[0])
+    if any(len(x) != n for x in c32 + c64 + rest):
+        raise ValueError("columns must have the same length")
+    cuts = FlowCuts()
+    h = _vp()
+    vocab = np.empty(max(vocab_cap, 1), np.int32)
+    V = C.c_int32()
+    sw, dw = np.empty(max(n, 1), np.int32), np.empty(max(n, 1), np.int32)
+    _check(lib().onilda_flow_prelda(*[_ptr(x) for x in c32 + c64 + rest], n, num_docs, device, C.byref(cuts), C.byref(h),
+                                    _ptr(vocab), vocab_cap, C.byref(V), _ptr(sw), _ptr(dw)))
+    return ({"time": np.array(cuts.time), "ibyt": np.array(cuts.ibyt), "ipkt": np.array(cuts.ipkt)}, Corpus(h),
+            vocab[:V.value].copy(), sw[:n], dw[:n])
 
 
 def flow_word_string(code):

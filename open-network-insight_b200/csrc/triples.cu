@@ -17,6 +17,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <vector>
+
 #include "kernels.cuh"
 
 namespace {
@@ -602,6 +604,60 @@ extern "C" int onilda_pairs_count(const int32_t* doc, const int32_t* word, int64
     return ONILDA_OK;
 }
 
+// Device triples (ids in range) -> grouped on the device -> host corpus.
+static int corpus_from_device_triples(const int32_t* d_doc, const int32_t* d_word, const int32_t* d_count, int64_t n, int64_t num_docs,
+                                      int32_t num_terms, long long tokens, cudaStream_t st, onilda_corpus** out)
+{
+    struct DevBuf {
+        void* p = nullptr;
+        ~DevBuf() { cudaFree(p); }
+    } d_out;
+    const size_t b_n = align256(sizeof(int32_t) * (size_t)n);
+    onilda_corpus* c = (onilda_corpus*)calloc(1, sizeof *c);
+    if (!c) return onilda_fail(ONILDA_ENOMEM, "corpus_from_triples: out of host memory");
+    c->num_docs = num_docs;
+    c->nnz = n;
+    c->tokens = tokens;
+    c->num_terms = num_terms;
+    c->offsets = (int64_t*)malloc(sizeof(int64_t) * (size_t)(num_docs + 1));
+    c->totals = (int32_t*)malloc(sizeof(int32_t) * (size_t)(num_docs > 0 ? num_docs : 1));
+    c->words = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
+    c->counts = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
+    if (!c->offsets || !c->totals || !c->words || !c->counts) {
+        onilda_corpus_free(c);
+        return onilda_fail(ONILDA_ENOMEM, "corpus_from_triples: out of host memory");
+    }
+    const size_t b_off = align256(sizeof(int64_t) * (size_t)(num_docs + 1)), b_tot = align256(sizeof(int32_t) * (size_t)(num_docs + 1));
+    if (cudaMalloc(&d_out.p, b_off + b_tot + 2 * b_n + 256) != cudaSuccess) {
+        cudaGetLastError();
+        onilda_corpus_free(c);
+        return onilda_fail(ONILDA_ENOMEM, "corpus_from_triples: device memory for the grouped corpus not available");
+    }
+    char* o = (char*)d_out.p;
+    int64_t* d_off = (int64_t*)o;
+    int32_t* d_tot = (int32_t*)(o + b_off);
+    int32_t* d_w = (int32_t*)(o + b_off + b_tot);
+    int32_t* d_c = (int32_t*)(o + b_off + b_tot + b_n);
+    int32_t* d_maxlen = (int32_t*)(o + b_off + b_tot + 2 * b_n);
+    int rc = onilda_triples_group_device(d_doc, d_word, d_count, n, num_docs, d_off, d_w, d_c, d_tot, d_maxlen, st);
+    cudaError_t err = cudaSuccess;
+    if (rc == ONILDA_OK) {
+        err = cudaMemcpyAsync(c->offsets, d_off, sizeof(int64_t) * (size_t)(num_docs + 1), cudaMemcpyDeviceToHost, st);
+        if (err == cudaSuccess && num_docs > 0) err = cudaMemcpyAsync(c->totals, d_tot, sizeof(int32_t) * (size_t)num_docs, cudaMemcpyDeviceToHost, st);
+        if (err == cudaSuccess && n > 0) err = cudaMemcpyAsync(c->words, d_w, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, st);
+        if (err == cudaSuccess && n > 0) err = cudaMemcpyAsync(c->counts, d_c, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, st);
+        if (err == cudaSuccess) err = cudaMemcpyAsync(&c->max_len, d_maxlen, sizeof(int32_t), cudaMemcpyDeviceToHost, st);
+        if (err == cudaSuccess) err = cudaStreamSynchronize(st);
+        if (err != cudaSuccess) rc = onilda_fail(ONILDA_ECUDA, "corpus_from_triples: %s", cudaGetErrorString(err));
+    }
+    if (rc != ONILDA_OK) {
+        onilda_corpus_free(c);
+        return rc;
+    }
+    *out = c;
+    return ONILDA_OK;
+}
+
 extern "C" int onilda_corpus_from_triples(const int32_t* doc, const int32_t* word, const int32_t* count, int64_t n,
                                           int64_t num_docs, int32_t num_terms, int device, onilda_corpus** out)
 {
@@ -620,7 +676,7 @@ extern "C" int onilda_corpus_from_triples(const int32_t* doc, const int32_t* wor
     struct DevBuf {
         void* p = nullptr;
         ~DevBuf() { cudaFree(p); }
-    } d_in, d_out, d_range;
+    } d_in, d_range;
     const size_t b_n = align256(sizeof(int32_t) * (size_t)n);
     long long range[4] = {-1, -1, 0, 0};
     if (n > 0) {
@@ -643,49 +699,156 @@ extern "C" int onilda_corpus_from_triples(const int32_t* doc, const int32_t* wor
         if (range[0] >= num_docs)
             return onilda_fail(ONILDA_EINVAL, "corpus_from_triples: document id %lld >= num_docs %lld", range[0], (long long)num_docs);
     }
-    onilda_corpus* c = (onilda_corpus*)calloc(1, sizeof *c);
-    if (!c) return onilda_fail(ONILDA_ENOMEM, "corpus_from_triples: out of host memory");
-    c->num_docs = num_docs;
-    c->nnz = n;
-    c->tokens = range[3];
-    c->num_terms = num_terms > (int32_t)(range[1] + 1) ? num_terms : (int32_t)(range[1] + 1);
-    c->offsets = (int64_t*)malloc(sizeof(int64_t) * (size_t)(num_docs + 1));
-    c->totals = (int32_t*)malloc(sizeof(int32_t) * (size_t)(num_docs > 0 ? num_docs : 1));
-    c->words = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
-    c->counts = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
-    if (!c->offsets || !c->totals || !c->words || !c->counts) {
-        onilda_corpus_free(c);
-        return onilda_fail(ONILDA_ENOMEM, "corpus_from_triples: out of host memory");
-    }
-    const size_t b_off = align256(sizeof(int64_t) * (size_t)(num_docs + 1)), b_tot = align256(sizeof(int32_t) * (size_t)(num_docs + 1));
-    if (cudaMalloc(&d_out.p, b_off + b_tot + 2 * b_n + 256) != cudaSuccess) {
-        cudaGetLastError();
-        onilda_corpus_free(c);
-        return onilda_fail(ONILDA_ENOMEM, "corpus_from_triples: device memory for the grouped corpus not available");
-    }
-    char* o = (char*)d_out.p;
-    int64_t* d_off = (int64_t*)o;
-    int32_t* d_tot = (int32_t*)(o + b_off);
-    int32_t* d_w = (int32_t*)(o + b_off + b_tot);
-    int32_t* d_c = (int32_t*)(o + b_off + b_tot + b_n);
-    int32_t* d_maxlen = (int32_t*)(o + b_off + b_tot + 2 * b_n);
     const char* in = (const char*)d_in.p;
-    int rc = onilda_triples_group_device((const int32_t*)in, (const int32_t*)(in + b_n), (const int32_t*)(in + 2 * b_n), n, num_docs,
-                                         d_off, d_w, d_c, d_tot, d_maxlen, st);
-    cudaError_t err = cudaSuccess;
-    if (rc == ONILDA_OK) {
-        err = cudaMemcpyAsync(c->offsets, d_off, sizeof(int64_t) * (size_t)(num_docs + 1), cudaMemcpyDeviceToHost, st);
-        if (err == cudaSuccess && num_docs > 0) err = cudaMemcpyAsync(c->totals, d_tot, sizeof(int32_t) * (size_t)num_docs, cudaMemcpyDeviceToHost, st);
-        if (err == cudaSuccess && n > 0) err = cudaMemcpyAsync(c->words, d_w, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, st);
-        if (err == cudaSuccess && n > 0) err = cudaMemcpyAsync(c->counts, d_c, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, st);
-        if (err == cudaSuccess) err = cudaMemcpyAsync(&c->max_len, d_maxlen, sizeof(int32_t), cudaMemcpyDeviceToHost, st);
-        if (err == cudaSuccess) err = cudaStreamSynchronize(st);
-        if (err != cudaSuccess) rc = onilda_fail(ONILDA_ECUDA, "corpus_from_triples: %s", cudaGetErrorString(err));
+    return corpus_from_device_triples((const int32_t*)in, (const int32_t*)(in + b_n), (const int32_t*)(in + 2 * b_n), n, num_docs,
+                                      num_terms > (int32_t)(range[1] + 1) ? num_terms : (int32_t)(range[1] + 1), range[3], st, out);
+}
+
+// ---- FlowPreLDA in one call: event columns -> words -> dictionary -> word counts per role -> corpus
+namespace {
+
+__global__ void __launch_bounds__(256) mark_codes_kernel(const int32_t* __restrict__ a, const int32_t* __restrict__ b, int64_t n,
+                                                         unsigned int* __restrict__ bitmap)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned int ca = (unsigned int)a[i], cb = (unsigned int)b[i];
+    // most events of a warp share a handful of words: test before the atomic
+    if (!(bitmap[ca >> 5] >> (ca & 31) & 1u)) atomicOr(&bitmap[ca >> 5], 1u << (ca & 31));
+    if (!(bitmap[cb >> 5] >> (cb & 31) & 1u)) atomicOr(&bitmap[cb >> 5], 1u << (cb & 31));
+}
+
+__global__ void __launch_bounds__(256) popc_kernel(const unsigned int* __restrict__ bitmap, int64_t words, unsigned int* __restrict__ cnt)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < words) cnt[i] = (unsigned int)__popc(bitmap[i]);
+}
+
+// word id = number of distinct codes below this one (the dictionary is the sorted list of distinct codes)
+__global__ void __launch_bounds__(256) code_ranks_kernel(const int32_t* __restrict__ code, int64_t n, const unsigned int* __restrict__ bitmap,
+                                                         const unsigned int* __restrict__ before, int32_t* __restrict__ word)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned int c = (unsigned int)code[i];
+    word[i] = (int32_t)(before[c >> 5] + (unsigned int)__popc(bitmap[c >> 5] & ((1u << (c & 31)) - 1u)));
+}
+
+__global__ void __launch_bounds__(256) vocab_kernel(const unsigned int* __restrict__ bitmap, int64_t words,
+                                                    const unsigned int* __restrict__ before, int32_t* __restrict__ vocab)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= words) return;
+    unsigned int m = bitmap[i], r = before[i];
+    while (m) {
+        const int b = __ffs(m) - 1;
+        vocab[r++] = (int32_t)(i * 32 + b);
+        m &= m - 1;
     }
-    if (rc != ONILDA_OK) {
-        onilda_corpus_free(c);
-        return rc;
+}
+
+}  // namespace
+
+extern "C" int onilda_flow_prelda(const int32_t* hour, const int32_t* minute, const int32_t* second, const int64_t* ibyt,
+                                  const int64_t* ipkt, const int32_t* sport, const int32_t* dport, const int32_t* sip,
+                                  const int32_t* dip, int64_t n, int64_t num_docs, int device, onilda_flow_cuts* cuts_out,
+                                  onilda_corpus** corpus_out, int32_t* vocab_codes_out, int32_t vocab_cap, int32_t* num_terms_out,
+                                  int32_t* src_word_out, int32_t* dst_word_out)
+{
+    if (n < 0 || num_docs < 0 || !cuts_out || !corpus_out || !num_terms_out || vocab_cap < 0 || (vocab_cap > 0 && !vocab_codes_out) ||
+        (n > 0 && (!hour || !minute || !second || !ibyt || !ipkt || !sport || !dport || !sip || !dip)))
+        return onilda_fail(ONILDA_EINVAL, "flow_prelda: bad argument");
+    if (2 * n >= ((int64_t)1 << 31) - 1) return onilda_fail(ONILDA_EINVAL, "flow_prelda: at most 2^30 - 1 events per call");
+    if (onilda_device_count() == 0)
+        return onilda_fail(ONILDA_ECUDA, "flow_prelda: no CUDA device is usable and this library has no CPU path");
+    int prev = 0;
+    ONILDA_CUDA(cudaGetDevice(&prev));
+    if (device < 0) device = prev;
+    ONILDA_CUDA(cudaSetDevice(device));
+    struct Restore { int d; ~Restore() { cudaSetDevice(d); } } restore{prev};
+    cudaStream_t st = 0;
+    *num_terms_out = 0;
+    if (n == 0) {
+        int rc = onilda_flow_words_device(nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, cuts_out, nullptr, nullptr, nullptr);
+        if (rc != ONILDA_OK) return rc;
+        std::vector<int64_t> off((size_t)num_docs + 1, 0);
+        int32_t dummy = 0;
+        return onilda_corpus_from_csr(off.data(), &dummy, &dummy, num_docs, 0, corpus_out);
     }
-    *out = c;
-    return ONILDA_OK;
+    struct DevBuf { void* p = nullptr; ~DevBuf() { cudaFree(p); } } d_cols, d_work;
+    const size_t b4 = align256(sizeof(int32_t) * (size_t)n), b8 = align256(sizeof(int64_t) * (size_t)n);
+    const int64_t bm_words = (ONILDA_FLOW_CODE_SPACE + 31) / 32;
+    const size_t b_bm = align256(sizeof(unsigned int) * (size_t)bm_words);
+    if (cudaMalloc(&d_cols.p, 7 * b4 + 2 * b8 + 4 * b4) != cudaSuccess ||
+        cudaMalloc(&d_work.p, 3 * b_bm + align256(sizeof(unsigned int) * (size_t)(bm_words / 2048 + 2)) + 6 * b4 + 512) != cudaSuccess) {
+        cudaGetLastError();
+        return onilda_fail(ONILDA_ENOMEM, "flow_prelda: device memory for %lld events not available", (long long)n);
+    }
+    char* p = (char*)d_cols.p;
+    int64_t* d_ibyt = (int64_t*)p; p += b8;
+    int64_t* d_ipkt = (int64_t*)p; p += b8;
+    int32_t* col[11];
+    for (int k = 0; k < 11; k++) { col[k] = (int32_t*)p; p += b4; }
+    const int32_t* src[7] = {hour, minute, second, sport, dport, sip, dip};
+    for (int k = 0; k < 7; k++) ONILDA_CUDA(cudaMemcpyAsync(col[k], src[k], sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, st));
+    ONILDA_CUDA(cudaMemcpyAsync(d_ibyt, ibyt, sizeof(int64_t) * (size_t)n, cudaMemcpyHostToDevice, st));
+    ONILDA_CUDA(cudaMemcpyAsync(d_ipkt, ipkt, sizeof(int64_t) * (size_t)n, cudaMemcpyHostToDevice, st));
+    int32_t *d_sip = col[5], *d_dip = col[6], *d_scode = col[7], *d_dcode = col[8], *d_sw = col[9], *d_dw = col[10];
+    char* q = (char*)d_work.p;
+    unsigned int* bitmap = (unsigned int*)q; q += b_bm;
+    unsigned int* cnt = (unsigned int*)q; q += b_bm;
+    unsigned int* before = (unsigned int*)q; q += b_bm;
+    unsigned int* sums = (unsigned int*)q; q += align256(sizeof(unsigned int) * (size_t)(bm_words / 2048 + 2));
+    int32_t* o_doc = (int32_t*)q; q += 2 * b4;
+    int32_t* o_word = (int32_t*)q; q += 2 * b4;
+    int32_t* o_cnt = (int32_t*)q; q += 2 * b4;
+    long long* d_scalars = (long long*)q;      // [0..3] id range, [4] m1, [5] m2
+    // address ids
+    long long range[6] = {-1, -1, 0, 0, 0, 0};
+    ONILDA_CUDA(cudaMemcpyAsync(d_scalars, range, sizeof range, cudaMemcpyHostToDevice, st));
+    triple_range_kernel<<<148 * 8, 256, 0, st>>>(d_sip, d_dip, d_dip, n, d_scalars);
+    ONILDA_CUDA(cudaGetLastError());
+    ONILDA_CUDA(cudaMemcpyAsync(range, d_scalars, sizeof range, cudaMemcpyDeviceToHost, st));
+    ONILDA_CUDA(cudaStreamSynchronize(st));
+    if (range[2]) return onilda_fail(ONILDA_EINVAL, "flow_prelda: negative address id");
+    const long long max_ip = range[0] > range[1] ? range[0] : range[1];
+    if (num_docs == 0) num_docs = max_ip + 1;
+    if (max_ip >= num_docs) return onilda_fail(ONILDA_EINVAL, "flow_prelda: address id %lld >= num_docs %lld", max_ip, (long long)num_docs);
+    // words (FlowWordCreation), then the dictionary: the sorted distinct codes
+    int rc = onilda_flow_words_device(col[0], col[1], col[2], d_ibyt, d_ipkt, col[3], col[4], n, cuts_out, d_scode, d_dcode, nullptr);
+    if (rc != ONILDA_OK) return rc;
+    const unsigned int grid_n = (unsigned int)((n + 255) / 256), grid_w = (unsigned int)((bm_words + 255) / 256);
+    ONILDA_CUDA(cudaMemsetAsync(bitmap, 0, sizeof(unsigned int) * (size_t)bm_words, st));
+    mark_codes_kernel<<<grid_n, 256, 0, st>>>(d_scode, d_dcode, n, bitmap);
+    popc_kernel<<<grid_w, 256, 0, st>>>(bitmap, bm_words, cnt);
+    exclusive_scan(cnt, bm_words, sums, before, st);
+    unsigned int last_before = 0, last_cnt = 0;
+    ONILDA_CUDA(cudaMemcpyAsync(&last_before, before + bm_words - 1, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
+    ONILDA_CUDA(cudaMemcpyAsync(&last_cnt, cnt + bm_words - 1, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
+    ONILDA_CUDA(cudaStreamSynchronize(st));
+    const int32_t V = (int32_t)(last_before + last_cnt);
+    *num_terms_out = V;
+    if ((int64_t)V > bm_words) return onilda_fail(ONILDA_EINVAL, "flow_prelda: %d distinct words is more than this call handles", V);
+    if (vocab_codes_out && V > vocab_cap)
+        return onilda_fail(ONILDA_EINVAL, "flow_prelda: %d distinct words, room for %d (the number is in *num_terms_out)", V, vocab_cap);
+    code_ranks_kernel<<<grid_n, 256, 0, st>>>(d_scode, n, bitmap, before, d_sw);
+    code_ranks_kernel<<<grid_n, 256, 0, st>>>(d_dcode, n, bitmap, before, d_dw);
+    if (vocab_codes_out) {
+        vocab_kernel<<<grid_w, 256, 0, st>>>(bitmap, bm_words, before, (int32_t*)cnt /* reused: V <= bm_words */);
+        ONILDA_CUDA(cudaMemcpyAsync(vocab_codes_out, cnt, sizeof(int32_t) * (size_t)V, cudaMemcpyDeviceToHost, st));
+    }
+    ONILDA_CUDA(cudaGetLastError());
+    // word counts per role (FlowPreLDA.scala:131-137), the union, the corpus
+    rc = onilda_pairs_count_device(d_sip, d_sw, n, num_docs, V, o_doc, o_word, o_cnt, d_scalars + 4, st);
+    if (rc != ONILDA_OK) return rc;
+    long long m1 = 0, m2 = 0;
+    ONILDA_CUDA(cudaMemcpyAsync(&m1, d_scalars + 4, sizeof m1, cudaMemcpyDeviceToHost, st));
+    ONILDA_CUDA(cudaStreamSynchronize(st));
+    rc = onilda_pairs_count_device(d_dip, d_dw, n, num_docs, V, o_doc + m1, o_word + m1, o_cnt + m1, d_scalars + 5, st);
+    if (rc != ONILDA_OK) return rc;
+    ONILDA_CUDA(cudaMemcpyAsync(&m2, d_scalars + 5, sizeof m2, cudaMemcpyDeviceToHost, st));
+    ONILDA_CUDA(cudaStreamSynchronize(st));
+    if (src_word_out) ONILDA_CUDA(cudaMemcpyAsync(src_word_out, d_sw, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, st));
+    if (dst_word_out) ONILDA_CUDA(cudaMemcpyAsync(dst_word_out, d_dw, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, st));
+    return corpus_from_device_triples(o_doc, o_word, o_cnt, m1 + m2, num_docs, V, 2 * (long long)n, st, corpus_out);
 }

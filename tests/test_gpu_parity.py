@@ -875,3 +875,39 @@ def test_dns_pipeline_end_to_end(oni, oracle):
     assert tie_aware_overlap(idx, rs, rtop, rtol=MODEL_RTOL) >= 0.99
     scorer.close()
     em.close()
+
+
+@pytest.mark.parametrize("n", [1, 257, 60_000])
+def test_flow_prelda_one_call(oni, oracle, n):
+    """onilda_flow_prelda = flow words + dictionary + word counts per role + corpus with nothing leaving the device in
+    between: equal to the step-by-step route (each step checked against the oracle above) and, for the small sizes, to
+    the oracle chain on strings."""
+    rng = np.random.default_rng(7 * n)
+    D = max(2, n // 50)
+    sip, dip = (rng.zipf(1.5, n) % D).astype(np.int32), (rng.zipf(1.5, n) % D).astype(np.int32)
+    hour, minute, second = rng.integers(0, 24, n), rng.integers(0, 60, n), rng.integers(0, 60, n)
+    ibyt = np.floor(np.exp(rng.normal(6, 2, n))).astype(np.int64)
+    ipkt = np.maximum(1, ibyt // 300)
+    ports = np.array([0, 22, 53, 80, 443, 1024, 1025, 8080, 50123, 65535])
+    sport, dport = rng.choice(ports, n), rng.choice(ports, n)
+    cuts, corpus, vocab, sw, dw = oni.flow_prelda(hour, minute, second, ibyt, ipkt, sport, dport, sip, dip, num_docs=D)
+    cuts2, sc, dc = oni.flow_words(hour, minute, second, ibyt, ipkt, sport, dport)
+    assert all(np.array_equal(cuts[k], cuts2[k]) for k in cuts)
+    vocab2 = np.unique(np.concatenate([sc, dc]))
+    assert np.array_equal(vocab, vocab2)
+    assert np.array_equal(sw, np.searchsorted(vocab2, sc)) and np.array_equal(dw, np.searchsorted(vocab2, dc))
+    a, b = oni.pairs_count(sip, sw, D, len(vocab)), oni.pairs_count(dip, dw, D, len(vocab))
+    c2 = oni.Corpus.from_triples(*(np.concatenate([x, y]) for x, y in zip(a, b)), num_docs=D, num_terms=len(vocab))
+    for x, y in zip(corpus.csr(), c2.csr()):
+        assert np.array_equal(x, y)
+    assert corpus.num_terms == len(vocab) and corpus.tokens == 2 * n and corpus.num_docs == D
+    if n <= 1000:
+        _, rs, rd = oracle.flow_words(hour, minute, second, ibyt, ipkt, sport, dport)
+        index = {oni.flow_word_string(c): i for i, c in enumerate(vocab)}
+        ra = oracle.pairs_count(sip, np.array([index[t] for t in rs], np.int32))
+        rb = oracle.pairs_count(dip, np.array([index[t] for t in rd], np.int32))
+        roff, rw, rc = oracle.triples_to_csr(*(np.concatenate([x, y]) for x, y in zip(ra, rb)), num_docs=D)
+        off, w, cnt, _ = corpus.csr()
+        assert np.array_equal(off, roff) and np.array_equal(w, rw) and np.array_equal(cnt, rc)
+    with pytest.raises(oni.OnildaError):                                     # more address ids than documents
+        oni.flow_prelda(hour, minute, second, ibyt, ipkt, sport, dport, sip + D, dip, num_docs=D)

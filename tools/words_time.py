@@ -49,3 +49,18 @@ print("ibyt cuts match sorted column:", want == list(cuts.ibyt))
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record(); torch.sort(ibyt); e1.record(); torch.cuda.synchronize()
 print("torch.sort of the ibyt column alone: %.2f ms" % e0.elapsed_time(e1))
+
+# ---- the whole pre-LDA chain in one call, from host columns (pageable) to a host corpus
+m = min(n, 100_000_000)
+D = 1_000_000
+sip = (torch.rand(m, device=dev, generator=g) ** 4 * D).to(torch.int32).clamp_(0, D - 1).cpu().numpy()
+dip = (torch.rand(m, device=dev, generator=g) ** 4 * D).to(torch.int32).clamp_(0, D - 1).cpu().numpy()
+cols = [x[:m].cpu().numpy() for x in (hour, minute, second, ibyt, ipkt, sport, dport)]
+del srt, sc, dc
+torch.cuda.empty_cache()
+for _ in range(2):
+    t0 = time.perf_counter()
+    cuts2, corpus, vocab, sw, dw = oni.flow_prelda(*cols, sip, dip, num_docs=D)
+    dt = time.perf_counter() - t0
+print("flow_prelda (host columns -> host corpus): %.3f s per %d events = %.2f G events/s; corpus %d docs, %d entries, %d words" % (
+    dt, m, m / dt / 1e9, corpus.num_docs, corpus.nnz, corpus.num_terms))
