@@ -62,6 +62,9 @@ const char* onilda_last_error(void);
 const char* onilda_version(void);
 /* Number of usable CUDA devices (0 when none; never fails). */
 int onilda_device_count(void);
+/* Creates the CUDA contexts of the first ndev devices (<= 0: all) ahead of time.  No reference counterpart: it
+ * exists so that a host program can overlap context creation with reading its input (host/lda_main.c does). */
+int onilda_device_warmup(int ndev);
 
 /* ------------------------------------------------------------------ settings
  * replaces read_settings (oni-ml/oni-lda-c/lda-estimate.c:331-350): five literal

@@ -109,6 +109,23 @@ extern "C" int onilda_device_count(void)
     return n;
 }
 
+// Creates the CUDA context of the first `ndev` devices (all when ndev <= 0).  Context creation takes several hundred
+// milliseconds; a caller with host work to do first (reading model.dat) runs this on another thread meanwhile.
+extern "C" int onilda_device_warmup(int ndev)
+{
+    const int avail = onilda_device_count();
+    if (avail == 0) return onilda_fail(ONILDA_ECUDA, "device_warmup: no CUDA device is usable");
+    if (ndev <= 0 || ndev > avail) ndev = avail;
+    int prev = 0;
+    ONILDA_CUDA(cudaGetDevice(&prev));
+    for (int d = 0; d < ndev; d++) {
+        ONILDA_CUDA(cudaSetDevice(d));
+        ONILDA_CUDA(cudaFree(0));
+    }
+    ONILDA_CUDA(cudaSetDevice(prev));
+    return ONILDA_OK;
+}
+
 extern "C" int onilda_corpus_pin(onilda_corpus* c)
 {
     if (!c) return onilda_fail(ONILDA_EINVAL, "corpus_pin: null corpus");

@@ -18,6 +18,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <pthread.h>
 #include <time.h>
 
 #include "onilda.h"
@@ -36,6 +37,13 @@ static int die(const char* what)
 {
     fprintf(stderr, "lda: %s: %s\n", what, onilda_last_error());
     return 1;
+}
+
+/* CUDA context creation runs beside the parse of model.dat (both take about half a second at cfg 2) */
+static void* warmup_thread(void* arg)
+{
+    onilda_device_warmup(*(int*)arg);
+    return NULL;
 }
 
 int main(int argc, char* argv[])
@@ -60,9 +68,14 @@ int main(int argc, char* argv[])
         int ndev = atoi(argv[5]);
         if (onilda_settings_read(argv[4], &settings) != 0) return die("settings");
         struct timespec t0, t1;
+        pthread_t warm;
+        int warm_ndev = ndev;
+        const int warming = pthread_create(&warm, NULL, warmup_thread, &warm_ndev) == 0;
         clock_gettime(CLOCK_MONOTONIC, &t0);
-        if (onilda_corpus_from_dat(argv[6], &corpus) != 0) return die("corpus");
+        const int parse_rc = onilda_corpus_from_dat(argv[6], &corpus);
         clock_gettime(CLOCK_MONOTONIC, &t1);
+        if (warming) pthread_join(warm, NULL);     /* a failure there is reported by run_em with its own message */
+        if (parse_rc != 0) return die("corpus");
         if (getenv("ONILDA_TIMING"))
             fprintf(stderr, "[timing] read %s: %.3f s\n", argv[6], (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec));
         int64_t D, N; int32_t V;
