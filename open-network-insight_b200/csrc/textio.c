@@ -100,6 +100,42 @@ static int io_threads(void)
     return (int)n;
 }
 
+/* The file into memory, by several threads where it is large (a copy out of the page cache runs at a few GB/s per
+ * thread, and model.dat is 850 MB at cfg 2). */
+typedef struct { int fd; unsigned char* dst; size_t begin, end; int failed; } read_job;
+
+static void* read_worker(void* arg)
+{
+    read_job* j = (read_job*)arg;
+    size_t pos = j->begin;
+    while (pos < j->end) {
+        ssize_t got = pread(j->fd, j->dst + pos, j->end - pos, (off_t)pos);
+        if (got <= 0) { j->failed = 1; return NULL; }
+        pos += (size_t)got;
+    }
+    return NULL;
+}
+
+static int read_whole(FILE* f, unsigned char* dst, size_t size)
+{
+    int T = io_threads();
+    if (size < ((size_t)8 << 20)) T = 1;
+    if (T > 16) T = 16;
+    read_job job[16];
+    pthread_t tid[16];
+    const int fd = fileno(f);
+    for (int t = 0; t < T; t++) {
+        job[t].fd = fd; job[t].dst = dst; job[t].failed = 0;
+        job[t].begin = size / (size_t)T * (size_t)t;
+        job[t].end = t == T - 1 ? size : size / (size_t)T * (size_t)(t + 1);
+    }
+    for (int t = 1; t < T; t++) pthread_create(&tid[t], NULL, read_worker, &job[t]);
+    read_worker(&job[0]);
+    for (int t = 1; t < T; t++) pthread_join(tid[t], NULL);
+    for (int t = 0; t < T; t++) if (job[t].failed) return -1;
+    return 0;
+}
+
 /* ---- parallel reader for the canonical layout
  * OniLDACWrapper.createModel (OniLDACWrapper.scala:146-168) writes one document per line:
  * "<n> <w>:<c> ... <w>:<c>\n", plain decimal, single spaces.  On such a file every line can be
@@ -253,7 +289,7 @@ int onilda_corpus_from_dat(const char* path, onilda_corpus** out)
     fseek(f, 0, SEEK_SET);
     unsigned char* text = (unsigned char*)malloc((size_t)size + 1);
     if (!text) { fclose(f); return onilda_fail(ONILDA_ENOMEM, "corpus %s: %ld bytes do not fit in memory", path, size); }
-    if (size > 0 && fread(text, 1, (size_t)size, f) != (size_t)size) {
+    if (size > 0 && read_whole(f, text, (size_t)size) != 0) {
         fclose(f); free(text);
         return onilda_fail(ONILDA_EIO, "short read on %s", path);
     }
