@@ -219,12 +219,9 @@ int select_ranks_device(const int64_t* d_v, int64_t n, const long long* ranks, i
     const int levels = bits == 0 ? 0 : (bits + kSelBits - 1) / kSelBits;
     std::vector<unsigned long long> prefix((size_t)nq, 0ull), hist((size_t)kMaxQ * kSelBins);
     std::vector<long long> remaining(ranks, ranks + nq);
-    static bool attr_set = false;
-    if (!attr_set) {
-        ONILDA_CUDA(cudaFuncSetAttribute(multi_select_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)(sizeof(unsigned int) * kMaxQ * kSelBins)));
-        attr_set = true;
-    }
+    // per device, so on every call (the current device may differ from the last call's)
+    ONILDA_CUDA(cudaFuncSetAttribute(multi_select_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)(sizeof(unsigned int) * kMaxQ * kSelBins)));
     for (int level = levels - 1; level >= 0; level--) {
         SelLevel lv;
         lv.shift = level * kSelBits;

@@ -911,3 +911,31 @@ def test_flow_prelda_one_call(oni, oracle, n):
         assert np.array_equal(off, roff) and np.array_equal(w, rw) and np.array_equal(cnt, rc)
     with pytest.raises(oni.OnildaError):                                     # more address ids than documents
         oni.flow_prelda(hour, minute, second, ibyt, ipkt, sport, dport, sip + D, dip, num_docs=D)
+
+
+def test_side_steps_on_second_device(oni):
+    """Every entry point either side of the path takes a device index: device 1 must give what device 0 gives
+    (per-device kernel attributes, the device restored afterwards)."""
+    if oni.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    rng = np.random.default_rng(3)
+    n, D = 300_000, 2000
+    hour, minute, second = rng.integers(0, 24, n), rng.integers(0, 60, n), rng.integers(0, 60, n)
+    ibyt = np.floor(np.exp(rng.normal(6, 2.5, n))).astype(np.int64)
+    ipkt = np.maximum(1, ibyt // 400)
+    ports = np.array([0, 22, 80, 443, 1025, 50123])
+    sport, dport = rng.choice(ports, n), rng.choice(ports, n)
+    sip, dip = rng.integers(0, D, n).astype(np.int32), rng.integers(0, D, n).astype(np.int32)
+    out = []
+    for dev in (0, 1):
+        cuts, corpus, vocab, sw, dw = oni.flow_prelda(hour, minute, second, ibyt, ipkt, sport, dport, sip, dip, num_docs=D, device=dev)
+        q = oni.quantiles(ibyt, [0.1, 0.5, 0.9, 1.0], device=dev)
+        pc = oni.pairs_count(sip, sw, D, len(vocab), device=dev)
+        names, frame, ts, qt, rc = dns_columns(np.random.default_rng(8), 3000)
+        dcuts, dcode = oni.dns_words(names, frame, ts, qt, rc, top_domains=["amazon"], device=dev)
+        out.append((cuts, corpus.csr(), vocab, sw, dw, q, pc, dcuts, dcode))
+    a, b = out
+    assert all(np.array_equal(a[0][k], b[0][k]) for k in a[0]) and all(np.array_equal(x, y) for x, y in zip(a[1], b[1]))
+    assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3]) and np.array_equal(a[4], b[4]) and np.array_equal(a[5], b[5])
+    assert all(np.array_equal(x, y) for x, y in zip(a[6], b[6]))
+    assert all(np.array_equal(a[7][k], b[7][k]) for k in a[7]) and np.array_equal(a[8], b[8])
