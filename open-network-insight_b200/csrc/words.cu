@@ -434,7 +434,7 @@ namespace {
 // ISO country-code suffixes the reference tests the last label against (DNSWordCreation.scala:17-30; the set
 // also holds "krd" and the empty string, which a last label can never equal after String.split drops trailing
 // empty parts).  Sorted, two letters each; "krd" is tested apart.
-__constant__ char kCountry2[] =
+static const char kCountry2[] =
     "acadaeafagaialamanaoaqarasatauawaxazbabbbdbebfbgbhbibjbmbnbobqbrbsbtbvbwbybzcacccdcfcgchcickclcmcncocrcucvcwcxcycz"
     "dedjdkdmdodzeceeegeheresetfifjfkfmfofrgagbgdgegfggghgiglgmgngpgqgrgsgtgugwgyhkhmhnhrhthuidieiliminioiqirisit"
     "jejmjojpkekgkhkikmknkpkrkwkykzlalblclilklrlsltlulvlymamcmdmemgmhmkmlmmmnmompmqmrmsmtmumvmwmxmymznancnenfngninlnonpnrnunz"
@@ -442,13 +442,17 @@ __constant__ char kCountry2[] =
     "uaugukusuyuzvavcvevgvivnvuwfwsyeytzazmzweu";
 constexpr int kCountry2Count = (int)(sizeof(kCountry2) - 1) / 2;
 
+// 26 x 26 bits, one per pair of lower-case letters; filled from kCountry2 on each call (per device)
+__constant__ unsigned int kCountryBits[22];
+
 __device__ __forceinline__ bool is_country(const unsigned char* p, int len)
 {
     if (len == 3) return p[0] == 'k' && p[1] == 'r' && p[2] == 'd';
     if (len != 2) return false;
-    for (int i = 0; i < kCountry2Count; i++)
-        if (kCountry2[2 * i] == (char)p[0] && kCountry2[2 * i + 1] == (char)p[1]) return true;
-    return false;
+    const unsigned int a = p[0] - 'a', b = p[1] - 'a';
+    if (a >= 26u || b >= 26u) return false;
+    const unsigned int bit = a * 26 + b;
+    return (kCountryBits[bit >> 5] >> (bit & 31)) & 1u;
 }
 
 __device__ __forceinline__ bool bytes_equal(const unsigned char* p, int len, const char* lit, int lit_len)
@@ -686,6 +690,14 @@ static int dns_words_core(const char* names, const int64_t* name_offsets, const 
     int64_t* d_ent = (int64_t*)p; p += b8;
     int64_t* d_frame = (int64_t*)p; p += b8;
     int32_t* d_topflag = (int32_t*)p;
+    {
+        unsigned int bits[22] = {0};
+        for (int i = 0; i < kCountry2Count; i++) {
+            const unsigned int bit = (unsigned int)(kCountry2[2 * i] - 'a') * 26 + (unsigned int)(kCountry2[2 * i + 1] - 'a');
+            bits[bit >> 5] |= 1u << (bit & 31);
+        }
+        ONILDA_CUDA(cudaMemcpyToSymbolAsync(kCountryBits, bits, sizeof bits, 0, cudaMemcpyHostToDevice, st));
+    }
     TopTable top{top_capacity > 0 ? top_slots : nullptr, (unsigned long long)(top_capacity > 0 ? top_capacity - 1 : 0),
                  (const unsigned char*)top_bytes, top_offsets};
     dns_features_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>((const unsigned char*)names, name_offsets, n, top,
