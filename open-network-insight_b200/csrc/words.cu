@@ -507,21 +507,12 @@ __device__ double string_entropy(const unsigned char* p, int len, const double* 
 }
 
 // DNSWordCreation.extractSubdomain (:155-196) + stringEntropy of the subdomain column + getTopDomain (:147-153)
-__global__ void __launch_bounds__(128) dns_features_kernel(const unsigned char* __restrict__ names, const int64_t* __restrict__ off,
-                                                           int64_t n, TopTable top, const double* __restrict__ term,
-                                                           int64_t* __restrict__ sub_len, int64_t* __restrict__ num_parts,
-                                                           int64_t* __restrict__ entropy_bits, int32_t* __restrict__ top_out,
-                                                           int* __restrict__ bad, int32_t* __restrict__ spans /* [n][3] or null */)
+// One name: s[0, len) (generic pointer: shared-memory stage or global), results to index i.
+__device__ __forceinline__ void dns_features_one(const unsigned char* s, int len, int64_t i, const TopTable& top,
+                                                 const double* __restrict__ term, int64_t* __restrict__ sub_len,
+                                                 int64_t* __restrict__ num_parts, int64_t* __restrict__ entropy_bits,
+                                                 int32_t* __restrict__ top_out, int32_t* __restrict__ spans)
 {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const unsigned char* s = names + off[i];
-    const int64_t len64 = off[i + 1] - off[i];
-    if (len64 < 0 || len64 > 255) {          // a DNS name has at most 253 characters
-        *bad = 1;
-        return;
-    }
-    const int len = (int)len64;
     // String.split("[.]"): trailing empty parts are dropped; a string without a dot is one part
     int e = len, dots = 0;
     for (int k = 0; k < len; k++) dots += (s[k] == '.');
@@ -578,6 +569,50 @@ __global__ void __launch_bounds__(128) dns_features_kernel(const unsigned char* 
         spans[3 * i + 1] = dom_e;
         spans[3 * i + 2] = sub_e;
     }
+}
+
+// DNSWordCreation.extractSubdomain (:155-196) + stringEntropy of the subdomain column + getTopDomain (:147-153).
+// One thread per name.  The names of a warp are contiguous in the buffer: the warp copies them into shared memory
+// with 16-byte loads first (a thread walking its own name byte by byte in global memory costs a cache-line lookup
+// per lane per byte), and falls back to global memory when its 32 names do not fit the stage.
+constexpr int kDnsStage = 2048;
+
+__global__ void __launch_bounds__(128) dns_features_kernel(const unsigned char* __restrict__ names, const int64_t* __restrict__ off,
+                                                           int64_t n, TopTable top, const double* __restrict__ term,
+                                                           int64_t* __restrict__ sub_len, int64_t* __restrict__ num_parts,
+                                                           int64_t* __restrict__ entropy_bits, int32_t* __restrict__ top_out,
+                                                           int* __restrict__ bad, int32_t* __restrict__ spans /* [n][3] or null */)
+{
+    __shared__ __align__(16) unsigned char stage[4][kDnsStage + 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool in_range = i < n;
+    const int64_t b = in_range ? off[i] : 0, e = in_range ? off[i + 1] : 0;
+    const int64_t len64 = e - b;
+    bool live = in_range;
+    if (in_range && (b < 0 || len64 < 0 || len64 > 255)) {          // a DNS name has at most 253 characters
+        *bad = 1;
+        live = false;
+    }
+    // the byte range of the warp's names (lane 0 holds the lowest index of the warp)
+    const int64_t first = __shfl_sync(0xffffffffu, b, 0);
+    long long rel_end = live ? e - first : 0;
+    if (rel_end < 0) rel_end = 0;
+    if (rel_end > (1ll << 30)) rel_end = 1ll << 30;
+    const int span = __reduce_max_sync(0xffffffffu, (int)rel_end);
+    const bool ordered = __all_sync(0xffffffffu, !live || b >= first);
+    const unsigned char* s = names + b;
+    const uintptr_t base_addr = (uintptr_t)(names + first);
+    const int lead = (int)(base_addr & 15);                   // the copy starts at the 16-byte boundary below the first byte
+    if (ordered && span > 0 && span + lead <= kDnsStage) {
+        const uint4* src = reinterpret_cast<const uint4*>(base_addr - lead);
+        uint4* dst = reinterpret_cast<uint4*>(stage[warp]);
+        const int chunks = (span + lead + 15) / 16;
+        for (int c = lane; c < chunks; c += 32) dst[c] = src[c];
+        __syncwarp();
+        s = stage[warp] + lead + (b - first);
+    }
+    if (live) dns_features_one(s, (int)len64, i, top, term, sub_len, num_parts, entropy_bits, top_out, spans);
 }
 
 struct DnsCutsDev {
