@@ -28,7 +28,10 @@ def pkg():
 
 @pytest.fixture(scope="session")
 def oni():
-    return pkg()
+    m = pkg()
+    if not m.LIB_PATH.exists() or not m.LDA_BIN.exists():
+        m.build()            # a fresh checkout: nvcc cross-compiles without a GPU (same as __graft_entry__.build())
+    return m
 
 
 @pytest.fixture(scope="session")
