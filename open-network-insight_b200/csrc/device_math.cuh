@@ -235,13 +235,26 @@ ONILDA_TABLE LogTabEntry kLogTab[128] = {
     {0.5009784735812133, 0.691192145724142}
 };
 
-ONILDA_HD double fast_log_tab(double x, const LogTabEntry* tab)
+// Table access is a template parameter of the routines below: the kernels read the tables from shared
+// memory through 32-bit shared-window addresses (estep.cu), the host tests through plain pointers.
+struct MathTablesPtr {
+    const struct PsiRow* psi;
+    const double* exp2;
+    const LogTabEntry* log;
+    ONILDA_HD void log_entry(int i, double& inv_c, double& log_c) const { inv_c = log[i].inv_c; log_c = log[i].log_c; }
+    ONILDA_HD double exp2_frac(int i) const { return exp2[i]; }
+    ONILDA_HD void psi_row(int row, double (&a)[6]) const;
+};
+
+template <class Tables>
+ONILDA_HD double fast_log_tab(double x, const Tables& tb)
 {
     const int hi = double_hi(x);
     const int e = (hi >> 20) - 1023;
-    const LogTabEntry t = tab[(hi >> 13) & 127];
+    double inv_c, log_c;
+    tb.log_entry((hi >> 13) & 127, inv_c, log_c);
     const double m = hilo_to_double((hi & 0x000FFFFF) | 0x3FF00000, double_lo(x));
-    const double r = fma(m, t.inv_c, -1.0);
+    const double r = fma(m, inv_c, -1.0);
     // log1p(r) = r - r^2/2 + r^3/3 - r^4/4 + r^5/5 - r^6/6
     const double r2 = r * r;
     const double a = fma(r, 0.3333333333333333, -0.5);
@@ -250,12 +263,21 @@ ONILDA_HD double fast_log_tab(double x, const LogTabEntry* tab)
     const double p = fma(r2, c, a);                           // -1/2 + r/3 - r^2/4 + r^3/5 - r^4/6
     const double ed = (double)e;
     const double lo = fma(ed, kLn2[1], fma(r2, p, r));
-    return fma(ed, kLn2[0], t.log_c) + lo;
+    return fma(ed, kLn2[0], log_c) + lo;
+}
+
+ONILDA_HD double fast_log_tab(double x, const LogTabEntry* tab)
+{
+    MathTablesPtr tb;
+    tb.psi = nullptr;
+    tb.exp2 = nullptr;
+    tb.log = tab;
+    return fast_log_tab(x, tb);
 }
 
 // 1/x for finite normal x.  The hardware seed (MUFU.RCP64H) is good to 2^-20 (measured on B200,
 // tools/microbench.cu), so one cubic step reaches 2^-60; no special cases.
-ONILDA_HD double fast_rcp(double x)
+ONILDA_HD double rcp_seed(double x)
 {
     double r;
 #if defined(__CUDA_ARCH__)
@@ -263,6 +285,12 @@ ONILDA_HD double fast_rcp(double x)
 #else
     r = hilo_to_double(double_hi(1.0 / x) & ~0x1, 0);     // host stand-in for the seed: 19 good bits
 #endif
+    return r;
+}
+
+ONILDA_HD double fast_rcp(double x)
+{
+    const double r = rcp_seed(x);
     double e = fma(-x, r, 1.0);
     e = fma(e, e, e);
     return fma(r, e, r);
@@ -325,6 +353,126 @@ ONILDA_HD double fast_exp(double x)
     k = k > -1021 ? k : -1021;
     // scale by 2^k through the exponent field (q in [0.7, 1.42], k in [-1021, 1011])
     return hilo_to_double(double_hi(q) + (k << 20), double_lo(q));
+}
+
+// ---------------------------------------------------------------------------------------------
+// psi and exp by table: the per-(word, topic) forms of the E-step.
+//
+// The reference's digamma (utils.c:55-64) splits exactly as psi(x) = R(x) - 1/x, with
+//     R(x) = series(1/(x+6)^2) + log(x+6) - 0.5/(x+6) - sum_{j=1..5} 1/(x+j)
+// analytic for x > -1.  R is tabulated as a function of t = x + 1 >= 1: the exponent and the top
+// kPsiMantBits mantissa bits of t pick a cell (64 per octave, kPsiOctaves octaves, t < 2^20), and a
+// degree-5 polynomial in u = t - (cell centre) interpolates the REFERENCE's series (truncated
+// coefficients included) at six Chebyshev nodes of the cell; the host builds the rows in long
+// double (hostmath.c).  Interpolation error <= 8e-15 absolute on [1, 2), less above.  One
+// reciprocal supplies the pole.  7 + 4 FP64 instructions against 37 for the rational form plus its
+// logarithm.  48-byte rows: three 16-byte shared-memory loads whose 16-byte chunk index 3i + j
+// spreads over all eight bank groups (a 64-byte row would put every lane in two of them).
+//
+// exp: x = (64 k + i) ln2/64 + r, |r| <= ln2/128; 2^(i/64) from a 64-entry table, degree-5 Taylor
+// in r (3.5e-17), the scale 2^k through the exponent field.  8 FP64 instructions against 14.
+constexpr int kPsiMantBits = 6;
+constexpr int kPsiOctaves = 20;
+constexpr int kPsiRows = kPsiOctaves << kPsiMantBits;     // 1280 rows, 61440 bytes
+constexpr int kExpTabSize = 64;
+struct alignas(16) PsiRow {
+    double a[6];
+};
+
+// row of t (t >= 1); rows past the table (t >= 2^20) are the caller's business
+ONILDA_HD int psi_row_of(double t) { return (double_hi(t) >> (20 - kPsiMantBits)) - (1023 << kPsiMantBits); }
+
+// u = t - centre of t's cell (exact)
+ONILDA_HD double psi_cell_offset(double t)
+{
+    const int keep = ~((1 << (20 - kPsiMantBits)) - 1);
+    const int hc = (double_hi(t) & keep) | (1 << (19 - kPsiMantBits));
+    return t - hilo_to_double(hc, 0);
+}
+
+ONILDA_HD void MathTablesPtr::psi_row(int row, double (&a)[6]) const
+{
+    for (int i = 0; i < 6; i++) a[i] = psi[row].a[i];
+}
+
+// R by Horner (five dependent DFMA: the throughput form) or Estrin (seven, depth three: the form
+// for the one-document-per-warp kernel, which waits on its own dependency chain)
+template <bool kShallow>
+ONILDA_HD double psi_poly(const double (&a)[6], double u)
+{
+    if (kShallow) {
+        const double u2 = u * u;
+        const double p01 = fma(a[1], u, a[0]);
+        const double p23 = fma(a[3], u, a[2]);
+        const double p45 = fma(a[5], u, a[4]);
+        const double u4 = u2 * u2;
+        return fma(p45, u4, fma(p23, u2, p01));
+    } else {
+        double p = fma(a[5], u, a[4]);
+        p = fma(p, u, a[3]);
+        p = fma(p, u, a[2]);
+        p = fma(p, u, a[1]);
+        return fma(p, u, a[0]);
+    }
+}
+
+// 64/ln2 and ln2/64.  The reduction r = x - kd*(ln2/64) is ONE fma with the rounded constant: its error,
+// |kd| * 1.2e-18, is 3e-15 for |x| <= 30 (where exp(psi) matters) and 8e-14 at x = -700.
+ONILDA_CONST double kExpTabC[2] = {92.33248261689366, 0.010830424696249145};
+// 1/2, 1/6, 1/24, 1/120
+ONILDA_CONST double kExpTabP[4] = {0.5, 0.16666666666666666, 0.041666666666666664, 0.008333333333333333};
+
+// exp(x) for -1e9 < x <= ~700 with the table of 2^(i/64); x below about -708 gives a tiny positive value.
+// (Callers guarantee x > -1e9: psi(gamma) with gamma >= 1e-8, see estep.cu.)
+template <bool kShallow, class Tables>
+ONILDA_HD double fast_exp_tab(double x, const Tables& tb)
+{
+    const double magic = 6755399441055744.0;
+    const double t = fma(x, kExpTabC[0], magic);
+    const int n = double_lo(t);
+    const double kd = t - magic;
+    const double r = fma(kd, -kExpTabC[1], x);
+    const double T = tb.exp2_frac(n & (kExpTabSize - 1));
+    int k = n >> 6;
+    double q;                                              // exp(r) - 1 = r + r^2/2 + ... + r^5/120
+    if (kShallow) {
+        const double r2 = r * r;
+        const double qa = fma(kExpTabP[0], r, 1.0);
+        const double q34 = fma(kExpTabP[2], r, kExpTabP[1]);
+        const double r3 = r2 * r;
+        const double qb = fma(kExpTabP[3], r2, q34);
+        q = fma(r3, qb, r * qa);
+    } else {
+        q = fma(kExpTabP[3], r, kExpTabP[2]);
+        q = fma(q, r, kExpTabP[1]);
+        q = fma(q, r, kExpTabP[0]);
+        q = fma(q, r, 1.0);
+        q = q * r;
+    }
+    const double v = fma(T, q, T);                         // in [0.99, 2.02)
+    k = k > -1021 ? k : -1021;
+    return hilo_to_double(double_hi(v) + (k << 20), double_lo(v));
+}
+
+struct PsiExp {
+    double psi;   // the reference's digamma(x)
+    double e;     // exp(psi)
+};
+
+// psi(x) and exp(psi(x)) for 1e-8 <= x, x + 1 < 2^kPsiOctaves (the caller keeps other arguments away:
+// the row index is not clamped)
+template <bool kShallow, class Tables>
+ONILDA_HD PsiExp psi_exp_tab(double x, const Tables& tb)
+{
+    const double t = x + 1.0;
+    double a[6];
+    tb.psi_row(psi_row_of(t), a);
+    const double u = psi_cell_offset(t);
+    const double inv = fast_rcp(x);
+    PsiExp out;
+    out.psi = psi_poly<kShallow>(a, u) - inv;
+    out.e = fast_exp_tab<kShallow>(out.psi, tb);
+    return out;
 }
 
 struct DigammaParts {

@@ -7,6 +7,7 @@
 
 #include <vector>
 
+#include "device_math.cuh"
 #include "kernels.cuh"
 
 using namespace onilda;
@@ -21,7 +22,7 @@ struct onilda_em {
     cudaEvent_t ev_long_end, ev_bulk_end;   // ONILDA_TIMING=1: when each of the two concurrent launches ended
     int timing;
     int64_t num_long;           // documents of at least long_len entries: prefix of d_order
-    int long_len, long_group, long_smem, bulk_group, bulk_per_sm;
+    int long_len, long_group, long_smem, long_threads, long_per_sm, bulk_group, bulk_per_sm, bulk_threads;
     // shard
     int64_t doc_begin, doc_end, num_docs, nnz;
     int K, V;
@@ -46,6 +47,7 @@ struct onilda_em {
     unsigned long long* d_queue;   // [2]: bulk, long
     int* d_error;
     double* d_kv;               // [K][V] staging for import / export
+    double* d_math_tab;         // psi rows, then the 2^(i/64) table (device_math.cuh)
     // stats
     double estep_ms, mstep_ms;
     int64_t launches;
@@ -160,7 +162,7 @@ extern "C" void onilda_em_destroy(onilda_em* em)
     cudaFree(em->d_log_beta_wk); cudaFree(em->d_beta_scaled); cudaFree(em->d_lbmax); cudaFree(em->d_ss);
     cudaFree(em->d_class_total); cudaFree(em->d_partial); cudaFree(em->d_phi); cudaFree(em->d_gamma);
     cudaFree(em->d_doc_lik); cudaFree(em->d_doc_ass); cudaFree(em->d_doc_sweeps); cudaFree(em->d_queue);
-    cudaFree(em->d_error); cudaFree(em->d_kv);
+    cudaFree(em->d_error); cudaFree(em->d_kv); cudaFree(em->d_math_tab);
     if (em->ev0) cudaEventDestroy(em->ev0);
     if (em->ev1) cudaEventDestroy(em->ev1);
     if (em->ev2) cudaEventDestroy(em->ev2);
@@ -239,8 +241,8 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
     TRY(dev_alloc(&em->d_totals, (size_t)D));
     TRY(dev_alloc(&em->d_order, (size_t)D));
     TRY(dev_alloc(&em->d_log_beta_wk, table));
-    TRY(dev_alloc(&em->d_beta_scaled, table));
-    TRY(dev_alloc(&em->d_lbmax, (size_t)em->V));
+    TRY(dev_alloc(&em->d_beta_scaled, table + lay.kpad));       // + the idle row (kernels.cuh: EStepArgs)
+    TRY(dev_alloc(&em->d_lbmax, (size_t)em->V + 1));
     TRY(dev_alloc(&em->d_ss, table + SS_TAIL));
     TRY(dev_alloc(&em->d_class_total, (size_t)lay.kpad));
     TRY(dev_alloc(&em->d_partial, (size_t)mstep_partial_doubles(em->V, lay, D)));
@@ -252,6 +254,17 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
     TRY(dev_alloc(&em->d_queue, 2));
     TRY(dev_alloc(&em->d_error, 1));
     TRY(dev_alloc(&em->d_kv, (size_t)em->K * em->V));
+    TRY(dev_alloc(&em->d_math_tab, (size_t)6 * kPsiRows + kExpTabSize));
+    {
+        std::vector<double> tab((size_t)6 * kPsiRows + kExpTabSize);
+        onilda_build_psi_table(tab.data(), kPsiMantBits, kPsiOctaves);
+        onilda_build_exp_table(tab.data() + (size_t)6 * kPsiRows, kExpTabSize);
+        TRYCUDA(cudaMemcpy(em->d_math_tab, tab.data(), sizeof(double) * tab.size(), cudaMemcpyHostToDevice));
+        std::vector<double> idle((size_t)lay.kpad + 1, 0.0);     // beta' = 1 for the real topics, then lbmax = 0
+        for (int k = 0; k < em->K; k++) idle[(size_t)k] = 1.0;
+        TRYCUDA(cudaMemcpy(em->d_beta_scaled + table, idle.data(), sizeof(double) * lay.kpad, cudaMemcpyHostToDevice));
+        TRYCUDA(cudaMemcpy(em->d_lbmax + em->V, idle.data() + lay.kpad, sizeof(double), cudaMemcpyHostToDevice));
+    }
 
     // shard-local CSR
     {
@@ -279,15 +292,17 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
         if (em->bulk_group < lay.group || (em->bulk_group & (em->bulk_group - 1)) || em->bulk_group > 32) em->bulk_group = lay.group;
         const char* env_bps = getenv("ONILDA_BULK_PER_SM");
         em->bulk_per_sm = env_bps ? atoi(env_bps) : 0;
+        // The long-document launch: blocks of eight warps, one block per SM, i.e. two long documents per SM
+        // sub-partition (measured at cfg 2 in round 1: with three on some sub-partitions their documents
+        // finish last, 155-160 -> 145 ms).
         const char* env_smem = getenv("ONILDA_LONG_SMEM");
-        // Default: eight one-warp blocks per SM, i.e. two long documents per SM sub-partition.  With
-        // every long document resident at once (9-10 per SM at cfg 2) some sub-partitions carry three and
-        // their documents finish last; the cap is enforced by asking for an eighth of the SM's shared
-        // memory per block, which the kernel never touches (measured at cfg 2: 155-160 -> 145 ms).
-        int smem_sm = 0;
-        if (cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, device) != cudaSuccess) smem_sm = 0;
-        cudaGetLastError();
-        em->long_smem = env_smem ? atoi(env_smem) : (smem_sm >= 65536 ? smem_sm / 8 - 1184 : 0);
+        const char* env_lt = getenv("ONILDA_LONG_THREADS");
+        const char* env_lps = getenv("ONILDA_LONG_PER_SM");
+        const char* env_bt = getenv("ONILDA_BULK_THREADS");
+        em->long_smem = env_smem ? atoi(env_smem) : 0;
+        em->long_threads = env_lt ? atoi(env_lt) : 256;
+        em->long_per_sm = env_lps ? atoi(env_lps) : 1;
+        em->bulk_threads = env_bt ? atoi(env_bt) : 384;
         em->num_long = 0;
         if (em->long_len > 0 && em->long_group != lay.group)
             while (em->num_long < D && off[(size_t)order[(size_t)em->num_long] + 1] - off[(size_t)order[(size_t)em->num_long]] >= em->long_len) em->num_long++;
@@ -350,7 +365,8 @@ static int run_estep(onilda_em* em, bool accumulate)
     EStepArgs a;
     a.offsets = em->d_offsets; a.words = em->d_words; a.counts = em->d_counts; a.totals = em->d_totals;
     a.order = em->d_order;
-    a.beta_scaled = em->d_beta_scaled; a.lbmax = em->d_lbmax; a.num_topics = em->K; a.kstride = em->lay.kpad;
+    a.psi_tab = em->d_math_tab; a.exp_tab = em->d_math_tab + (size_t)6 * kPsiRows;
+    a.beta_scaled = em->d_beta_scaled; a.lbmax = em->d_lbmax; a.num_topics = em->K; a.num_terms = em->V; a.kstride = em->lay.kpad;
     a.alpha = em->alpha;
     a.lik_const = lgamma(em->alpha * em->K) - em->K * lgamma(em->alpha);
     a.var_max_iter = em->var_max_iter;
@@ -368,13 +384,13 @@ static int run_estep(onilda_em* em, bool accumulate)
         ONILDA_CUDA(cudaStreamWaitEvent(em->long_stream, em->ev_fork, 0));
         EStepArgs b = a;
         b.order_begin = 0; b.order_count = em->num_long; b.queue = em->d_queue + 1;
-        rc = launch_estep(em->long_group, b, em->sm_count, 32, em->long_smem, 0, em->long_stream, &l);
+        rc = launch_estep(em->long_group, b, em->sm_count, em->long_threads, em->long_smem, em->long_per_sm, em->long_stream, &l);
         if (rc != ONILDA_OK) return rc;
         if (em->timing) ONILDA_CUDA(cudaEventRecord(em->ev_long_end, em->long_stream));
         ONILDA_CUDA(cudaEventRecord(em->ev_join, em->long_stream));
     }
     a.order_begin = em->num_long; a.order_count = em->num_docs - em->num_long; a.queue = em->d_queue;
-    rc = launch_estep(em->bulk_group, a, em->sm_count, 128, 0, em->num_long > 0 ? em->bulk_per_sm : 0, em->stream, &l);
+    rc = launch_estep(em->bulk_group, a, em->sm_count, em->bulk_threads, 0, em->num_long > 0 ? em->bulk_per_sm : 0, em->stream, &l);
     if (rc != ONILDA_OK) return rc;
     if (em->timing) ONILDA_CUDA(cudaEventRecord(em->ev_bulk_end, em->stream));
     if (em->num_long > 0) ONILDA_CUDA(cudaStreamWaitEvent(em->stream, em->ev_join, 0));

@@ -7,30 +7,34 @@
 //
 // Mapping
 //   * a document is owned by a group of G lanes; lane j keeps topics
-//     k = t*G + j in registers (gamma, E, and psi(gamma) as two parts).  A warp
+//     k = t*G + j in registers (gamma, psi(gamma), E = exp(psi(gamma))).  A warp
 //     therefore advances 32/G documents at once.  G = 4 is the efficient form
-//     (no idle lanes at K = 20, 72 instructions per document-word); G = 32, one
-//     topic per lane, is the low-latency form for long documents, whose serial
-//     word chain would otherwise bound the whole E-step.
+//     (no idle lanes at K = 20); G = 32, one topic per lane, is the low-latency
+//     form for long documents, whose serial word chain would otherwise bound
+//     the whole E-step.
 //   * words of a document are visited strictly in file order and gamma /
 //     digamma are refreshed after EVERY word (lda-inference.c:66-74): the
 //     Gauss-Seidel order of the reference is kept; parallelism is over topics
 //     and over documents only.
-//   * persistent warps pull "bundles" of 32/G consecutive documents of a
-//     length-sorted order from an atomic queue (longest first), so the groups
-//     of a warp run documents of near-equal length in lockstep and a warp that
+//   * persistent warps take "bundles" of 32/G consecutive documents of a
+//     length-sorted order: the first bundle of every warp is fixed (warp w of
+//     block b takes bundle w*gridDim + b, which puts the longest documents on
+//     different SMs), the rest come from an atomic queue, so the groups of a
+//     warp run documents of near-equal length in lockstep and a warp that
 //     finishes early steals the next bundle.  Each document leaves the sweep
 //     loop on its own convergence test (in-kernel early exit).
 //
-// Arithmetic (all fp64).  With E_k = exp(psi(gamma_k) - shift) and the table
+// Arithmetic (all fp64).  With E_k = exp(psi(gamma_k)) and the table
 // beta'[w][k] = exp(log_beta[k][w] - lbmax[w]) built once per EM iteration,
 //     phi_nk = E_k beta'_kw / s_n,   s_n = sum_j E_j beta'_jw
 // which is the reference's exp(psi_k + log_beta_kw - log_sum) without a
-// log_sum/exp per (word, topic): one log per WORD (log s_n) remains.  Per (word,
-// topic) the update costs two reciprocals, one exp and one log (device_math.cuh).  shift is
-// psi(alpha + total/K), the value every topic starts from, so E starts at 1 and
-// s_n can neither overflow nor vanish in practice; if it ever leaves
-// [1e-290, 1e290] that word is redone in log space (the reference's own form).
+// log_sum/exp per (word, topic): one log per WORD (log s_n) remains.  psi and
+// exp(psi) come from shared-memory tables (device_math.cuh: psi = R(gamma) - 1/gamma
+// with R a piecewise degree-5 fit of the reference's own series, exp with a
+// 64-entry table of 2^(i/64)): 28 FP64 instructions per (word, topic) where the
+// closed forms took 68.  If s_n ever leaves [1e-290, 1e290] that word is redone
+// in log space (the reference's own form); a gamma beyond the table (>= 2^20 - 1)
+// takes the closed forms.
 // The bound needs log phi_nk = psi_k(at word n) + log_beta_kw - lse_n; inserting
 // it and gamma_k = alpha + sum_n c_n phi_nk into lda-inference.c:106-125 the
 // (psi_k - psi_sum) terms cancel exactly and
@@ -42,6 +46,9 @@
 
 #ifndef ONILDA_PHI_AHEAD
 #define ONILDA_PHI_AHEAD 8
+#endif
+#ifndef ONILDA_ESTEP_MAX_THREADS
+#define ONILDA_ESTEP_MAX_THREADS 384
 #endif
 
 namespace onilda {
@@ -65,56 +72,151 @@ __device__ __forceinline__ double group_max(double v)
     return v;
 }
 
+// The math tables in shared memory, addressed through the 32-bit shared window (a generic pointer
+// costs a window-base computation per access).
+struct SmemTables {
+    uint32_t psi, exp2, log;
+    __device__ __forceinline__ static void lds2(uint32_t addr, double& x, double& y)
+    {
+        asm("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(x), "=d"(y) : "r"(addr));
+    }
+    __device__ __forceinline__ void log_entry(int i, double& inv_c, double& log_c) const { lds2(log + (uint32_t)i * 16u, inv_c, log_c); }
+    __device__ __forceinline__ double exp2_frac(int i) const
+    {
+        double v;
+        asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(exp2 + (uint32_t)i * 8u));
+        return v;
+    }
+    __device__ __forceinline__ void psi_row(int row, double (&a)[6]) const
+    {
+        const uint32_t p = psi + (uint32_t)row * (uint32_t)sizeof(PsiRow);
+        lds2(p, a[0], a[1]);
+        lds2(p + 16, a[2], a[3]);
+        lds2(p + 32, a[4], a[5]);
+    }
+};
+
 template <int TPL>
 struct WordItem {
-    int word;            // -1: this group idles at this word
+    int word;            // the sentinel row (num_terms) where this group idles at this word
     double count;
     double lbmax;
     double beta[TPL];
     double old_phi[TPL];
 };
 
+// The rare paths are kept out of line so that the word loop stays compact in the instruction cache.
+__device__ __noinline__ PsiExp psi_exp_closed(double g)
+{
+    const DigammaParts dp = digamma_rational(g);
+    PsiExp out;
+    out.psi = dp.rational + fast_log(dp.y);
+    out.e = fast_exp(out.psi);
+    return out;
+}
+
+// One word of one document group in log space: phi_k = exp(psi_k + log beta'_k - lse).  Called by the whole
+// warp (the shuffles inside need it converged).
+template <int TPL>
+struct LogSpaceWord {
+    double psi[TPL], beta[TPL];       // in: beta' = 0 marks a padding topic or a true zero
+    double y[TPL], inv_sum, lse;      // out: phi_k = y_k * inv_sum; lse is relative to lbmax
+};
+
 template <int G, int TPL>
-__global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long long num_bundles)
+__device__ __noinline__ void redo_word_in_log_space(LogSpaceWord<TPL>* w)
+{
+    double av[TPL], m = -INFINITY;
+#pragma unroll
+    for (int t = 0; t < TPL; t++) {
+        av[t] = (w->beta[t] > 0.0) ? w->psi[t] + log(w->beta[t]) : -INFINITY;
+        m = fmax(m, av[t]);
+    }
+    m = group_max<G>(m);
+    double ps = 0.0;
+#pragma unroll
+    for (int t = 0; t < TPL; t++) {
+        w->y[t] = (av[t] > -INFINITY) ? exp(av[t] - m) : 0.0;
+        ps += w->y[t];
+    }
+    ps = group_sum<G>(ps);
+    w->inv_sum = 1.0 / ps;
+    w->lse = m + log(ps);
+}
+
+// largest gamma the psi table serves (t = gamma + 1 < 2^kPsiOctaves), smallest the table exp takes (psi > -1e9)
+__device__ constexpr double kPsiTableMax = (double)(1 << kPsiOctaves) - 1.0;
+__device__ constexpr double kPsiTableMin = 1e-8;
+
+// KC: the number of topics when known at compile time (0: taken from the arguments).  With it the
+// row stride, the padding tests and every row address are constants or one multiply-add.
+template <int G, int TPL, int KC>
+__global__ void __launch_bounds__(ONILDA_ESTEP_MAX_THREADS) estep_kernel(EStepArgs a, unsigned long long num_bundles)
 {
     constexpr int DPW = 32 / G;      // documents per warp
+    // The one-document-per-warp form waits on its own dependency chain: shallow (Estrin) polynomials.
+    // The others are bound by FP64 issue: Horner, fewest instructions.
+    constexpr bool kShallow = (G == 32);
     const int lane = threadIdx.x & 31;
     const int grp = lane / G;
     const int j = lane % G;
-    const int K = a.num_topics;
-    const int KS = a.kstride;
+    const int K = KC ? KC : a.num_topics;
+    const uint32_t KS = KC ? (uint32_t)kpad_for(KC) : (uint32_t)a.kstride;
+    const int32_t idle_word = a.num_terms;     // table row V: beta' = 1, lbmax = 0
     const double inv_K = 1.0 / K;
     bool valid[TPL];
+    double start_phi[TPL];                     // phi before the first sweep: 1/K (lda-inference.c:41)
 #pragma unroll
-    for (int t = 0; t < TPL; t++) valid[t] = (t * G + j) < K;
+    for (int t = 0; t < TPL; t++) {
+        valid[t] = (t * G + j) < K;
+        start_phi[t] = valid[t] ? inv_K : 0.0;
+    }
 
-    const double* __restrict__ beta_scaled = a.beta_scaled;
-    double* __restrict__ phi = a.phi;
+    // kernel parameters used in the word loop are pinned in registers the same way (a constant-bank read
+    // has a scoreboard latency that the serial chain would wait for)
+    const double* __restrict__ beta_scaled = a.beta_scaled + j;
+    const double* __restrict__ lbmax = a.lbmax;
+    asm volatile("" : "+l"(beta_scaled), "+l"(lbmax));
 
-    // Where several warps share an SM sub-partition (G < 32) the two logarithms per word go through a
-    // 128-entry table in shared memory (10 FP64 instructions instead of 19).  The one-document-per-warp
-    // instantiation keeps the table-free form: alone on its sub-partition it is bound by the latency of
-    // its own instruction stream, and the table's shared-memory round trip costs it more than the
-    // nine instructions (measured: 155 -> 186 ms per E-step at cfg 2 with the table).
-    constexpr bool kTableLog = (G < 32);
-    __shared__ LogTabEntry logtab[kTableLog ? 128 : 1];
-    if constexpr (kTableLog) {
+    // Tables in shared memory, one copy per block: lanes index them divergently (constant memory
+    // would serialise, L1 would fetch a sector per lane).
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ LogTabEntry logtab[128];
+    {
+        const int4* src = reinterpret_cast<const int4*>(a.psi_tab);
+        int4* dst = reinterpret_cast<int4*>(smem_raw);
+        constexpr int chunks = (int)((sizeof(PsiRow) * kPsiRows + sizeof(double) * kExpTabSize) / sizeof(int4));
+        for (int i = threadIdx.x; i < chunks; i += blockDim.x) dst[i] = src[i];     // psi rows, then 2^(i/64)
         for (int i = threadIdx.x; i < 128; i += blockDim.x) logtab[i] = kLogTab[i];
         __syncthreads();
     }
-    auto log_of = [&](double v) -> double {
-        if constexpr (kTableLog) return fast_log_tab(v, logtab);
-        else return fast_log(v);
-    };
+    // The shared-window addresses are taken once and pinned in registers (volatile asm): the compiler would
+    // otherwise re-derive the window base from a special register at every use, a ~15-cycle read on the chain.
+    SmemTables tb;
+    tb.psi = (uint32_t)__cvta_generic_to_shared(smem_raw);
+    tb.log = (uint32_t)__cvta_generic_to_shared(logtab);
+    asm volatile("" : "+r"(tb.psi), "+r"(tb.log));
+    tb.exp2 = tb.psi + (uint32_t)(sizeof(PsiRow) * kPsiRows);
+
+    const unsigned int warps_per_block = blockDim.x >> 5;
+    const unsigned long long first_bundle = (unsigned long long)(threadIdx.x >> 5) * gridDim.x + blockIdx.x;
+    const unsigned long long queue_base = (unsigned long long)gridDim.x * warps_per_block;
+    bool first_claim = true;
 
     for (;;) {
         // Warp-uniform values are produced with redux/vote (their results live in uniform
         // registers), so the compiler can prove the warp converged at every shuffle below and
         // emits them without a divergence branch (BRA.DIV), which would otherwise fence its
         // instruction scheduling around each one.
-        unsigned int claimed = 0;
-        if (lane == 0) claimed = (unsigned int)atomicAdd(a.queue, 1ull);
-        const unsigned long long bundle = __reduce_max_sync(0xffffffffu, claimed);
+        unsigned long long bundle;
+        if (first_claim) {
+            bundle = first_bundle;
+            first_claim = false;
+        } else {
+            unsigned int claimed = 0;
+            if (lane == 0) claimed = (unsigned int)atomicAdd(a.queue, 1ull);
+            bundle = queue_base + __reduce_max_sync(0xffffffffu, claimed);
+        }
         if (bundle >= num_bundles) break;
 
         const int64_t slot = (int64_t)bundle * DPW + grp;
@@ -124,21 +226,37 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
         const int len = has_doc ? (int)(a.offsets[d + 1] - beg) : 0;
         const int total = has_doc ? a.totals[d] : 0;
         const int max_len = __reduce_max_sync(0xffffffffu, len);
+        const int32_t* __restrict__ doc_words = a.words + beg;
+        const int32_t* __restrict__ doc_counts = a.counts + beg;
+        double* __restrict__ doc_phi = a.phi + beg * (int64_t)KS + j;
 
-        // posterior Dirichlet start (lda-inference.c:37-43)
-        const double gamma0 = a.alpha + (total / ((double)K));
-        const DigammaParts d0 = digamma_rational(gamma0);
-        const double shift = d0.rational + fast_log(d0.y);
-        // per topic: gamma, E = exp(psi(gamma) - shift), and psi(gamma) kept as its two parts
-        // (rational part, y = gamma + 6) so that the logarithm can be taken one word later
-        double gam[TPL], E[TPL], rat[TPL], yy[TPL];
+        // Every gamma of a document stays within [alpha, alpha + total] up to rounding.  Where that
+        // interval leaves the tables' range the whole bundle takes the closed forms (warp-uniform).
+        const bool closed_forms = __any_sync(0xffffffffu, !(a.alpha >= kPsiTableMin && a.alpha + total + 1.0 < kPsiTableMax));
+        auto psi_exp = [&](double (&g)[TPL], double (&psi)[TPL], double (&E)[TPL]) {
+            if (__builtin_expect(closed_forms, 0)) {
 #pragma unroll
-        for (int t = 0; t < TPL; t++) {
-            gam[t] = valid[t] ? gamma0 : 1.0;
-            E[t] = 1.0;
-            rat[t] = d0.rational;
-            yy[t] = d0.y;
-        }
+                for (int t = 0; t < TPL; t++) {
+                    const PsiExp pe = psi_exp_closed(g[t]);
+                    psi[t] = pe.psi;
+                    E[t] = pe.e;
+                }
+            } else {
+#pragma unroll
+                for (int t = 0; t < TPL; t++) {
+                    const PsiExp pe = psi_exp_tab<kShallow>(g[t], tb);
+                    psi[t] = pe.psi;
+                    E[t] = pe.e;
+                }
+            }
+        };
+
+        // posterior Dirichlet start (lda-inference.c:37-43); per topic: gamma, psi(gamma), E = exp(psi(gamma))
+        const double gamma0 = a.alpha + (total / ((double)K));
+        double gam[TPL], psi[TPL], E[TPL];
+#pragma unroll
+        for (int t = 0; t < TPL; t++) gam[t] = valid[t] ? gamma0 : 1.0;
+        psi_exp(gam, psi, E);
 
         double lik = 0.0, lik_old = 0.0, converged = 1.0;
         int sweeps = 0;
@@ -147,7 +265,7 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
         while (__any_sync(0xffffffffu, active)) {
             if (active) sweeps++;
             const bool first = (sweeps == 1);   // same for every active group of the warp
-            double acc_lse = 0.0, count_sum = 0.0;
+            double acc_lse = 0.0;
             double acc_psi[TPL];
 #pragma unroll
             for (int t = 0; t < TPL; t++) acc_psi[t] = 0.0;
@@ -156,132 +274,126 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
             // ahead, the rows they select (beta', old phi, lbmax) one word ahead, so neither load
             // latency nor the id -> address dependency sits on the serial update chain.
             // A group that is idle at word n (document shorter than the bundle's longest, or already
-            // converged) still runs the arithmetic, on count = 0 and beta' = 1: every update is then
-            // multiplied by zero and nothing of it is stored.  That keeps the warp converged.
+            // converged) still runs the arithmetic, on count = 0 and the table's spare row (beta' = 1):
+            // every update is then multiplied by zero and nothing of it is stored.  That keeps the
+            // warp converged.
             constexpr int kPhiAhead = ONILDA_PHI_AHEAD;
+            const int live_len = active ? len : 0;
             auto load_ids = [&](int n, int& w, int& c) {
-                const bool on = active && n < len;
-                w = on ? a.words[beg + n] : -1;
-                c = on ? a.counts[beg + n] : 0;
+                w = idle_word;
+                c = 0;
+                if (n < live_len) {
+                    w = doc_words[n];
+                    c = doc_counts[n];
+                }
             };
             auto load_rows = [&](int n, int w, int c, WordItem<TPL>& it) {
-                const bool on = w >= 0;
                 it.word = w;
                 it.count = (double)c;
-                it.lbmax = on ? a.lbmax[w] : 0.0;
-                const double* brow = beta_scaled + (int64_t)w * KS + j;
-                const double* prow = phi + (beg + n) * KS + j;
+                it.lbmax = __ldg(lbmax + w);
+                const double* brow = beta_scaled + (uint64_t)(uint32_t)w * KS;
+                const double* prow = doc_phi + (uint64_t)(uint32_t)n * KS;
+                const bool reread = !first && w != idle_word;
                 // phi is the one stream that comes from HBM (17 GB at cfg 2, re-read every sweep); ask L2 for
                 // the row kPhiAhead words ahead so that the load one word ahead finds it there
-                if (kPhiAhead > 0 && !first && active && n + kPhiAhead < len)
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(prow + (int64_t)kPhiAhead * KS));
+                if (kPhiAhead > 0 && !first && valid[0] && n + kPhiAhead < live_len)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(prow + (uint64_t)kPhiAhead * KS));
 #pragma unroll
                 for (int t = 0; t < TPL; t++) {
-                    it.beta[t] = (on && valid[t]) ? __ldg(brow + t * G) : (valid[t] ? 1.0 : 0.0);
-                    it.old_phi[t] = (first || !on || !valid[t]) ? (valid[t] ? inv_K : 0.0) : prow[t * G];
+                    it.beta[t] = 0.0;
+                    if (valid[t]) it.beta[t] = __ldg(brow + t * G);
+                    it.old_phi[t] = start_phi[t];
+                    if (reread && valid[t]) it.old_phi[t] = prow[t * G];
                 }
             };
 
-            // word n's log(s_n) is also taken one word later (s_prev, with its weight and lbmax)
+            // word n's log(s_n) is taken one word later (s_prev, with its weight and lbmax): it depends only
+            // on values carried into the iteration, so it fills the latency gaps of the serial chain
             double s_prev = 1.0, c_prev = 0.0, lb_prev = 0.0;
 
             // one word of one sweep for every group of the warp
             auto step = [&](const WordItem<TPL>& it, int n) {
-                const bool on = it.word >= 0;
-
-                // The recurrence E -> s -> phi -> gamma -> E (lda-inference.c:52-73) starts here ...
+                // the recurrence E -> s -> phi -> gamma -> E (lda-inference.c:52-73)
                 double x[TPL], part = 0.0;
 #pragma unroll
                 for (int t = 0; t < TPL; t++) {
                     x[t] = E[t] * it.beta[t];
                     part += x[t];
                 }
-                const double s = group_sum<G>(part);
-
-                // ... and, off the recurrence, the two logarithms left over from the previous word.
-                // They depend only on values carried into this iteration, so they fill the latency
-                // gaps of the serial chain (the shuffles above, the reciprocals below).
-                double psi[TPL];
+                // off the chain: gamma - c*old_phi, so that one fma remains after phi is known
+                double gpre[TPL];
 #pragma unroll
-                for (int t = 0; t < TPL; t++) psi[t] = rat[t] + log_of(yy[t]);
-                acc_lse = fma(c_prev, lb_prev + log_of(s_prev), acc_lse);
-                const bool bad = !(s > 1e-290 && s < 1e290);
-                double inv = fast_rcp(s);
+                for (int t = 0; t < TPL; t++) gpre[t] = fma(-it.count, it.old_phi[t], gam[t]);
+                const double s = group_sum<G>(part);
+                acc_lse = fma(c_prev, lb_prev + fast_log_tab(s_prev, tb), acc_lse);
+                // s outside [2^-963, 2^963) (about 1e-290 .. 1e290), zero, negative or NaN: an integer test
+                // on the exponent field, off the FP64 pipe
+                const bool bad = (uint32_t)(double_hi(s) - 0x03C00000) >= (uint32_t)(0x7C200000 - 0x03C00000);
+                // phi = x / s as x*r + (x*r)*e with r the hardware seed (2^-20) and e = d + d*d, d = 1 - s*r:
+                // the cubic step of fast_rcp folded into the product, three dependent operations after the seed
+                double r0 = rcp_seed(s);
+                double e = fma(-s, r0, 1.0);
+                e = fma(e, e, e);
                 s_prev = s;
                 c_prev = it.count;
                 lb_prev = it.lbmax;
-                if (__any_sync(0xffffffffu, bad)) {
-                    // rare: redo this word in log space, as the reference does (lda-inference.c:52-68)
-                    double av[TPL], m = -INFINITY;
+                if (__builtin_expect(__any_sync(0xffffffffu, bad), 0)) {
+                    // rare: redo this word in log space, as the reference does (lda-inference.c:52-68); out of
+                    // line, through a scratch block that only this branch touches
+                    LogSpaceWord<TPL> ls;
 #pragma unroll
                     for (int t = 0; t < TPL; t++) {
-                        av[t] = (valid[t] && it.beta[t] > 0.0) ? (psi[t] - shift) + log(it.beta[t]) : -INFINITY;
-                        m = fmax(m, av[t]);
+                        ls.psi[t] = psi[t];
+                        ls.beta[t] = valid[t] ? it.beta[t] : 0.0;
                     }
-                    m = group_max<G>(m);
-                    double y[TPL], ps = 0.0;
-#pragma unroll
-                    for (int t = 0; t < TPL; t++) {
-                        y[t] = (av[t] > -INFINITY) ? exp(av[t] - m) : 0.0;
-                        ps += y[t];
-                    }
-                    ps = group_sum<G>(ps);
+                    redo_word_in_log_space<G, TPL>(&ls);
                     if (bad) {
 #pragma unroll
-                        for (int t = 0; t < TPL; t++) x[t] = y[t];
-                        inv = 1.0 / ps;
-                        acc_lse = fma(it.count, it.lbmax + m + log(ps), acc_lse);
+                        for (int t = 0; t < TPL; t++) x[t] = ls.y[t];
+                        r0 = ls.inv_sum;
+                        e = 0.0;
+                        acc_lse = fma(it.count, it.lbmax + ls.lse, acc_lse);
                         c_prev = 0.0;      // this word's log-sum is already in
                         s_prev = 1.0;
                     }
                 }
-                double* prow = phi + (beg + n) * KS + j;
+                double* prow = doc_phi + (uint64_t)(uint32_t)n * KS;
+                const bool keep = it.word != idle_word;
 #pragma unroll
                 for (int t = 0; t < TPL; t++) {
-                    const double p = x[t] * inv;
-                    if (on && valid[t]) prow[t * G] = p;
+                    const double xr = x[t] * r0;
+                    const double p = fma(xr, e, xr);
+                    gam[t] = fma(it.count, p, gpre[t]);
+                    if (keep && valid[t]) prow[t * G] = p;
                     acc_psi[t] = fma(it.count * p, psi[t], acc_psi[t]);
-                    gam[t] = gam[t] + it.count * (p - it.old_phi[t]);
-                    const DigammaParts dp = digamma_rational(gam[t]);
-                    // E = exp(psi - shift) = y * exp(rational - shift): no logarithm on the chain.
-                    // Padding topics need no mask here: their beta' is 0, so their E never counts.
-                    E[t] = dp.y * fast_exp(dp.rational - shift);
-                    rat[t] = dp.rational;
-                    yy[t] = dp.y;
                 }
-                count_sum += it.count;
+                // Padding topics need no mask: their beta' is 0, so their E never counts.
+                psi_exp(gam, psi, E);
             };
 
-            // The loop is unrolled by two over a pair of row buffers (A, B) so that prefetched rows
-            // are never copied: a register move of a value still in flight would wait for the load.
-            // Rows for word n+1 are requested before word n is worked on and first touched a whole
-            // step later; ids run one word further ahead.
-            // (The one-document-per-warp instantiation keeps a single-step loop: it is bound by the
-            // latency of its own instruction stream, and doubling the loop body costs it more in
-            // instruction fetch than the copies do.)
-            int wa, ca, wb, cb;
-            WordItem<TPL> A, B;
-            load_ids(0, wa, ca);
-            load_ids(1, wb, cb);
-            load_rows(0, wa, ca, A);
-            if constexpr (G < 32) {
-                for (int n = 0; n < max_len; n += 2) {
-                    load_rows(n + 1, wb, cb, B);
-                    load_ids(n + 2, wa, ca);
-                    step(A, n);
-                    load_rows(n + 2, wa, ca, A);
-                    load_ids(n + 3, wb, cb);
-                    step(B, n + 1);
-                }
-            } else {
-                for (int n = 0; n < max_len; n++) {   // wb, cb hold the ids of word n + 1
-                    load_rows(n + 1, wb, cb, B);
-                    load_ids(n + 2, wb, cb);
-                    step(A, n);
-                    A = B;
+            // The loop is unrolled over a ring of NB row buffers so that prefetched rows are never copied (a
+            // register move of a value still in flight would wait for the load).  Rows for word n + NB - 1 are
+            // requested before word n is worked on; ids run one word further ahead.  NB = 2 where several
+            // documents share the warp (a step is long and registers are short), 3 for the one-document-per-warp
+            // form, whose step is shorter than a round trip to L2 under load.
+            constexpr int NB = (G == 32) ? 3 : 2;
+            WordItem<TPL> ring[NB];
+            int wn, cn;
+#pragma unroll
+            for (int b = 0; b < NB - 1; b++) {
+                load_ids(b, wn, cn);
+                load_rows(b, wn, cn, ring[b]);
+            }
+            load_ids(NB - 1, wn, cn);
+            for (int n = 0; n < max_len; n += NB) {
+#pragma unroll
+                for (int b = 0; b < NB; b++) {
+                    load_rows(n + b + NB - 1, wn, cn, ring[(b + NB - 1) % NB]);
+                    load_ids(n + b + NB, wn, cn);
+                    step(ring[b], n + b);
                 }
             }
-            acc_lse = fma(c_prev, lb_prev + log_of(s_prev), acc_lse);
+            acc_lse = fma(c_prev, lb_prev + fast_log_tab(s_prev, tb), acc_lse);
 
             // likelihood bound of this sweep (lda-inference.c:93-127, see header); computed by every
             // group, used by the active ones
@@ -298,7 +410,7 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
             lg = group_sum<G>(lg);
             ap = group_sum<G>(ap);
             if (active) {
-                lik = a.lik_const - lgamma(gs) + lg - ap + (acc_lse + shift * count_sum);
+                lik = a.lik_const - lgamma(gs) + lg - ap + acc_lse;
                 if (isnan(lik)) *a.error_flag = 1;   // the reference asserts here (lda-inference.c:78)
                 converged = (lik_old - lik) / lik_old;
                 lik_old = lik;
@@ -312,7 +424,7 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
         for (int t = 0; t < TPL; t++) {
             if (valid[t]) {
                 gs += gam[t];
-                ps += rat[t] + fast_log(yy[t]);
+                ps += psi[t];
                 if (has_doc) a.gamma[d * K + t * G + j] = gam[t];
             }
         }
@@ -328,16 +440,16 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
             // four words per trip, all loads issued before the first atomic: the pass is pure
             // memory latency otherwise (phi rows come back from L2/HBM)
             constexpr int U = 4;
+            double* __restrict__ class_word = a.class_word + j;
             for (int n0 = 0; n0 < len; n0 += U) {
                 int w[U];
                 double c[U], p[U][TPL];
 #pragma unroll
                 for (int u = 0; u < U; u++) {
                     const bool in = n0 + u < len;
-                    const int64_t e = beg + n0 + u;
-                    w[u] = in ? a.words[e] : -1;
-                    c[u] = in ? (double)a.counts[e] : 0.0;
-                    const double* prow = phi + e * KS + j;
+                    w[u] = in ? doc_words[n0 + u] : -1;
+                    c[u] = in ? (double)doc_counts[n0 + u] : 0.0;
+                    const double* prow = doc_phi + (uint64_t)(uint32_t)(n0 + u) * KS;
 #pragma unroll
                     for (int t = 0; t < TPL; t++)
                         p[u][t] = (in && valid[t] && sweeps != 0) ? prow[t * G] : inv_K;
@@ -345,7 +457,7 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
 #pragma unroll
                 for (int u = 0; u < U; u++) {
                     if (w[u] >= 0) {
-                        double* crow = a.class_word + (int64_t)w[u] * KS + j;
+                        double* crow = class_word + (uint64_t)(uint32_t)w[u] * KS;
 #pragma unroll
                         for (int t = 0; t < TPL; t++)
                             if (valid[t]) atomicAdd(crow + t * G, c[u] * p[u][t]);
@@ -356,63 +468,76 @@ __global__ void __launch_bounds__(128) estep_kernel(EStepArgs a, unsigned long l
     }
 }
 
+// dynamic shared memory of one block: the psi rows and the 2^(i/64) table
+static constexpr size_t kEstepTableBytes = sizeof(PsiRow) * kPsiRows + sizeof(double) * kExpTabSize;
+
 // Grid for `num_bundles` bundles of one (G, TPL) instantiation: persistent, at most the resident
 // capacity of `sm_count` SMs (or `max_blocks` when the launch shares the device with another).
-template <int G, int TPL>
-static int launch_one(const EStepArgs& args, int sm_count, int block_threads, int reserve_smem, int max_per_sm,
+template <int G, int TPL, int KC>
+static int launch_one(const EStepArgs& args, int sm_count, int block_threads, int extra_smem, int max_per_sm,
                       cudaStream_t stream)
 {
     constexpr int DPW = 32 / G;
     const unsigned long long num_bundles = (unsigned long long)((args.order_count + DPW - 1) / DPW);
     if (num_bundles == 0) return ONILDA_OK;
-    // reserve_smem: dynamic shared memory the kernel never touches, asked for only to cap how many
-    // of these blocks an SM takes (em.cu sets it for the long-document launch: two warps per sub-partition)
-    if (reserve_smem > 0)
-        ONILDA_CUDA(cudaFuncSetAttribute(estep_kernel<G, TPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, reserve_smem));
+    // extra_smem: dynamic shared memory beyond the tables that the kernel never touches, asked for only to
+    // cap how many of these blocks an SM takes
+    if (block_threads > ONILDA_ESTEP_MAX_THREADS || block_threads < 32 || (block_threads & 31))
+        return onilda_fail(ONILDA_EINVAL, "E-step block of %d threads (32..%d, whole warps)", block_threads, ONILDA_ESTEP_MAX_THREADS);
+    const size_t smem = kEstepTableBytes + (size_t)extra_smem;
+    ONILDA_CUDA(cudaFuncSetAttribute(estep_kernel<G, TPL, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
-    ONILDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_kernel<G, TPL>, block_threads, (size_t)reserve_smem));
+    ONILDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_kernel<G, TPL, KC>, block_threads, smem));
     if (per_sm < 1) per_sm = 1;
     if (max_per_sm > 0 && per_sm > max_per_sm) per_sm = max_per_sm;
     const unsigned long long wpb = (unsigned long long)(block_threads / 32);
     unsigned long long want = (num_bundles + wpb - 1) / wpb;
     unsigned long long grid = (unsigned long long)sm_count * per_sm;
     if (grid > want) grid = want;
-    estep_kernel<G, TPL><<<(unsigned)grid, block_threads, (size_t)reserve_smem, stream>>>(args, num_bundles);
+    estep_kernel<G, TPL, KC><<<(unsigned)grid, block_threads, smem, stream>>>(args, num_bundles);
     ONILDA_CUDA(cudaGetLastError());
     return ONILDA_OK;
 }
 
 template <int G>
-static int launch_group(int tpl, const EStepArgs& args, int sm_count, int block_threads, int reserve_smem, int max_per_sm,
+static int launch_group(int tpl, const EStepArgs& args, int sm_count, int block_threads, int extra_smem, int max_per_sm,
                         cudaStream_t stream)
 {
+    // ONI's own topic counts (ml_ops.sh: TOPIC_COUNT=20; the proxy shape of BASELINE.json: 50) get kernels
+    // with the count compiled in
+    if (args.num_topics == 20 && args.kstride == kpad_for(20) && tpl == (20 + G - 1) / G)
+        return launch_one<G, (20 + G - 1) / G, 20>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
+    if (args.num_topics == 50 && args.kstride == kpad_for(50) && tpl == (50 + G - 1) / G) {
+        if constexpr (G >= 8)
+            return launch_one<G, (50 + G - 1) / G, 50>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
+    }
     switch (tpl) {
-        case 1: return launch_one<G, 1>(args, sm_count, block_threads, reserve_smem, max_per_sm, stream);
-        case 2: return launch_one<G, 2>(args, sm_count, block_threads, reserve_smem, max_per_sm, stream);
-        case 3: return launch_one<G, 3>(args, sm_count, block_threads, reserve_smem, max_per_sm, stream);
-        case 4: return launch_one<G, 4>(args, sm_count, block_threads, reserve_smem, max_per_sm, stream);
-        case 5: return launch_one<G, 5>(args, sm_count, block_threads, reserve_smem, max_per_sm, stream);
-        case 6: return launch_one<G, 6>(args, sm_count, block_threads, reserve_smem, max_per_sm, stream);
-        case 7: return launch_one<G, 7>(args, sm_count, block_threads, reserve_smem, max_per_sm, stream);
-        case 8: return launch_one<G, 8>(args, sm_count, block_threads, reserve_smem, max_per_sm, stream);
+        case 1: return launch_one<G, 1, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
+        case 2: return launch_one<G, 2, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
+        case 3: return launch_one<G, 3, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
+        case 4: return launch_one<G, 4, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
+        case 5: return launch_one<G, 5, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
+        case 6: return launch_one<G, 6, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
+        case 7: return launch_one<G, 7, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
+        case 8: return launch_one<G, 8, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
     }
     return onilda_fail(ONILDA_EINVAL, "unsupported topics-per-lane %d", tpl);
 }
 
 // One launch over documents order[order_begin, order_begin + order_count) with `group` lanes per
-// document and `block_threads` (32..128) threads per block.  args.queue must be zero (the caller
+// document and `block_threads` threads per block.  args.queue must be zero (the caller
 // clears it on the same stream).
-int launch_estep(int group, const EStepArgs& args, int sm_count, int block_threads, int reserve_smem, int max_per_sm,
+int launch_estep(int group, const EStepArgs& args, int sm_count, int block_threads, int extra_smem, int max_per_sm,
                  cudaStream_t stream, int* launches)
 {
     if (args.order_count <= 0) return ONILDA_OK;
     const int tpl = (args.num_topics + group - 1) / group;
     int rc;
     switch (group) {
-        case 4: rc = launch_group<4>(tpl, args, sm_count, block_threads, reserve_smem, max_per_sm, stream); break;
-        case 8: rc = launch_group<8>(tpl, args, sm_count, block_threads, reserve_smem, max_per_sm, stream); break;
-        case 16: rc = launch_group<16>(tpl, args, sm_count, block_threads, reserve_smem, max_per_sm, stream); break;
-        case 32: rc = launch_group<32>(tpl, args, sm_count, block_threads, reserve_smem, max_per_sm, stream); break;
+        case 4: rc = launch_group<4>(tpl, args, sm_count, block_threads, extra_smem, max_per_sm, stream); break;
+        case 8: rc = launch_group<8>(tpl, args, sm_count, block_threads, extra_smem, max_per_sm, stream); break;
+        case 16: rc = launch_group<16>(tpl, args, sm_count, block_threads, extra_smem, max_per_sm, stream); break;
+        case 32: rc = launch_group<32>(tpl, args, sm_count, block_threads, extra_smem, max_per_sm, stream); break;
         default: return onilda_fail(ONILDA_EINVAL, "unsupported lane group %d", group);
     }
     if (rc == ONILDA_OK && launches) *launches += 1;

@@ -27,10 +27,13 @@ struct TopicLayout {
 };
 
 // K <= 32 -> 4 lanes, K <= 64 -> 8, K <= 128 -> 16, K <= 256 -> 32.
+__host__ __device__ constexpr int group_for(int K) { return K <= 32 ? 4 : K <= 64 ? 8 : K <= 128 ? 16 : 32; }
+__host__ __device__ constexpr int kpad_for(int K) { return group_for(K) * ((K + group_for(K) - 1) / group_for(K)); }
+
 inline bool choose_layout(int K, TopicLayout* out)
 {
     if (K <= 0 || K > 256) return false;
-    int g = K <= 32 ? 4 : K <= 64 ? 8 : K <= 128 ? 16 : 32;
+    int g = group_for(K);
     out->group = g;
     out->tpl = (K + g - 1) / g;
     out->kpad = out->group * out->tpl;
@@ -52,7 +55,10 @@ struct EStepArgs {
     // model tables, word-major [V][kpad]
     const double* beta_scaled;  // exp(log_beta[w][k] - lbmax[w]); 0 in padding
     const double* lbmax;        // [V] max_k log_beta[w][k]
+    const void* psi_tab;        // device_math.cuh PsiRow[kPsiRows] (hostmath.c builds it)
+    const double* exp_tab;      // 2^(i/64), i < 64
     int num_topics;
+    int num_terms;              // V; row V of beta_scaled / lbmax is the idle row (beta' = 1 for k < K, lbmax = 0)
     int kstride;                // row stride of the tables and of phi, in doubles (TopicLayout::kpad)
     double alpha;
     double lik_const;           // lgamma(alpha*K) - K*lgamma(alpha)
@@ -69,7 +75,7 @@ struct EStepArgs {
     int* error_flag;            // set to 1 on a NaN likelihood
 };
 
-int launch_estep(int group, const EStepArgs& args, int sm_count, int block_threads, int reserve_smem, int max_per_sm,
+int launch_estep(int group, const EStepArgs& args, int sm_count, int block_threads, int extra_smem, int max_per_sm,
                  cudaStream_t stream, int* launches);
 
 // M-step and table kernels (mstep.cu)

@@ -38,6 +38,9 @@ int onilda_fail(int code, const char* fmt, ...);
 double onilda_host_digamma(double x);
 double onilda_host_trigamma(double x);
 double onilda_opt_alpha(double ss, int D, int K);
+/* tables of device_math.cuh's psi_exp_tab: rows[(octaves << mant_bits)][6], tab[n] */
+void onilda_build_psi_table(double* rows, int mant_bits, int octaves);
+void onilda_build_exp_table(double* tab, int n);
 
 /* em.cu */
 void onilda_corpus_unpin(onilda_corpus* c);
