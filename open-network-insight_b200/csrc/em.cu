@@ -22,6 +22,7 @@ struct onilda_em {
     cudaEvent_t ev_long_end, ev_bulk_end;   // ONILDA_TIMING=1: when each of the two concurrent launches ended
     int timing;
     int64_t num_long;           // documents of at least long_len entries: prefix of d_order
+    int64_t long_max_total;     // most tokens in one of them (decides whether the table-only long kernel may run)
     int long_len, long_group, long_smem, long_threads, long_per_sm, bulk_group, bulk_per_sm, bulk_threads;
     // shard
     int64_t doc_begin, doc_end, num_docs, nnz;
@@ -306,6 +307,11 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
         em->num_long = 0;
         if (em->long_len > 0 && em->long_group != lay.group)
             while (em->num_long < D && off[(size_t)order[(size_t)em->num_long] + 1] - off[(size_t)order[(size_t)em->num_long]] >= em->long_len) em->num_long++;
+        em->long_max_total = 0;
+        for (int64_t i = 0; i < em->num_long; i++) {
+            const int64_t t = c->totals[doc_begin + order[(size_t)i]];
+            if (t > em->long_max_total) em->long_max_total = t;
+        }
         TRYCUDA(cudaMemcpyAsync(em->d_offsets, off.data(), sizeof(int64_t) * (size_t)(D + 1), cudaMemcpyHostToDevice, em->stream));
         if (D > 0) {
             TRYCUDA(cudaMemcpyAsync(em->d_totals, c->totals + doc_begin, sizeof(int32_t) * (size_t)D, cudaMemcpyHostToDevice, em->stream));
@@ -384,7 +390,14 @@ static int run_estep(onilda_em* em, bool accumulate)
         ONILDA_CUDA(cudaStreamWaitEvent(em->long_stream, em->ev_fork, 0));
         EStepArgs b = a;
         b.order_begin = 0; b.order_count = em->num_long; b.queue = em->d_queue + 1;
-        rc = launch_estep(em->long_group, b, em->sm_count, em->long_threads, em->long_smem, em->long_per_sm, em->long_stream, &l);
+        // The staged one-document-per-warp kernel reads psi and exp(psi) from the tables only: every gamma of its
+        // documents, within [alpha, alpha + total], must lie inside their range (device_math.cuh).  Otherwise the
+        // general kernel, which has the closed forms, takes the long documents too.
+        const bool tables_cover = em->alpha >= 1e-8 && em->alpha + (double)em->long_max_total + 1.0 < (double)(1 << kPsiOctaves) - 1.0;
+        if (em->long_group == 32 && em->K <= 32 && tables_cover && !getenv("ONILDA_LONG_GENERIC"))
+            rc = launch_estep_long(b, em->sm_count, em->long_threads, em->long_per_sm, em->long_stream, &l);
+        else
+            rc = launch_estep(em->long_group, b, em->sm_count, em->long_threads, em->long_smem, em->long_per_sm, em->long_stream, &l);
         if (rc != ONILDA_OK) return rc;
         if (em->timing) ONILDA_CUDA(cudaEventRecord(em->ev_long_end, em->long_stream));
         ONILDA_CUDA(cudaEventRecord(em->ev_join, em->long_stream));

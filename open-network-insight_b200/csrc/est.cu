@@ -145,6 +145,9 @@ extern "C" int onilda_run_em(const char* start, const char* directory, const oni
         rc = onilda_model_load(start, &model);
     }
     if (rc != ONILDA_OK) { onilda_model_free(model); return rc; }
+    // A loaded model brings its own topic count (the reference saves gamma with model->num_topics too,
+    // lda-estimate.c:313-317); everything below is sized by it, not by the argument.
+    const int K = model->num_topics;
 
     mkdir(directory, S_IRUSR | S_IWUSR | S_IXUSR);   // utils.c:86-89, errors ignored as there
     const std::string dir(directory);
@@ -194,10 +197,10 @@ extern "C" int onilda_run_em(const char* start, const char* directory, const oni
     rc = onilda_em_get_model(set.ems[0], model);
     if (rc == ONILDA_OK) rc = onilda_model_save(model, (dir + "/final").c_str());
     if (rc == ONILDA_OK) {
-        std::vector<double> gamma((size_t)c->num_docs * num_topics + 1);
+        std::vector<double> gamma((size_t)c->num_docs * K + 1);
         for (int r = 0; r < ndev && rc == ONILDA_OK; r++)
-            rc = onilda_em_get_gamma(set.ems[(size_t)r], gamma.data() + (size_t)bounds[(size_t)r] * num_topics);
-        if (rc == ONILDA_OK) rc = onilda_gamma_save((dir + "/final.gamma").c_str(), gamma.data(), c->num_docs, num_topics);
+            rc = onilda_em_get_gamma(set.ems[(size_t)r], gamma.data() + (size_t)bounds[(size_t)r] * K);
+        if (rc == ONILDA_OK) rc = onilda_gamma_save((dir + "/final.gamma").c_str(), gamma.data(), c->num_docs, K);
     }
     if (timing)
         fprintf(stderr, "[timing] device setup %.3f s, %d EM iterations %.3f s, final.* %.3f s\n", secs(t_setup, t_em), iter,

@@ -41,112 +41,22 @@
 //     L = lgamma(alpha K) - K lgamma(alpha) - lgamma(sum gamma) + sum_k lgamma(gamma_k)
 //         - sum_n sum_k c_n phi_nk psi_k(at word n) + sum_n c_n lse_n .
 // tests/ check it against the oracle to ~1e-13 relative per document.
-#include "device_math.cuh"
-#include "kernels.cuh"
+#include "estep_common.cuh"
 
 #ifndef ONILDA_PHI_AHEAD
 #define ONILDA_PHI_AHEAD 8
+#endif
+#ifndef ONILDA_LONG_NB
+#define ONILDA_LONG_NB 3
+#endif
+#ifndef ONILDA_PIN
+#define ONILDA_PIN 1
 #endif
 #ifndef ONILDA_ESTEP_MAX_THREADS
 #define ONILDA_ESTEP_MAX_THREADS 384
 #endif
 
 namespace onilda {
-
-// Sum / max over the G lanes of a group.  Always executed by the whole warp with the full
-// mask (the kernel keeps its warps converged in the hot loop; partial-mask shuffles cost a
-// MATCH/VOTE/branch sequence each).
-template <int G>
-__device__ __forceinline__ double group_sum(double v)
-{
-#pragma unroll
-    for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-}
-
-template <int G>
-__device__ __forceinline__ double group_max(double v)
-{
-#pragma unroll
-    for (int o = G / 2; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
-    return v;
-}
-
-// The math tables in shared memory, addressed through the 32-bit shared window (a generic pointer
-// costs a window-base computation per access).
-struct SmemTables {
-    uint32_t psi, exp2, log;
-    __device__ __forceinline__ static void lds2(uint32_t addr, double& x, double& y)
-    {
-        asm("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(x), "=d"(y) : "r"(addr));
-    }
-    __device__ __forceinline__ void log_entry(int i, double& inv_c, double& log_c) const { lds2(log + (uint32_t)i * 16u, inv_c, log_c); }
-    __device__ __forceinline__ double exp2_frac(int i) const
-    {
-        double v;
-        asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(exp2 + (uint32_t)i * 8u));
-        return v;
-    }
-    __device__ __forceinline__ void psi_row(int row, double (&a)[6]) const
-    {
-        const uint32_t p = psi + (uint32_t)row * (uint32_t)sizeof(PsiRow);
-        lds2(p, a[0], a[1]);
-        lds2(p + 16, a[2], a[3]);
-        lds2(p + 32, a[4], a[5]);
-    }
-};
-
-template <int TPL>
-struct WordItem {
-    int word;            // the sentinel row (num_terms) where this group idles at this word
-    double count;
-    double lbmax;
-    double beta[TPL];
-    double old_phi[TPL];
-};
-
-// The rare paths are kept out of line so that the word loop stays compact in the instruction cache.
-__device__ __noinline__ PsiExp psi_exp_closed(double g)
-{
-    const DigammaParts dp = digamma_rational(g);
-    PsiExp out;
-    out.psi = dp.rational + fast_log(dp.y);
-    out.e = fast_exp(out.psi);
-    return out;
-}
-
-// One word of one document group in log space: phi_k = exp(psi_k + log beta'_k - lse).  Called by the whole
-// warp (the shuffles inside need it converged).
-template <int TPL>
-struct LogSpaceWord {
-    double psi[TPL], beta[TPL];       // in: beta' = 0 marks a padding topic or a true zero
-    double y[TPL], inv_sum, lse;      // out: phi_k = y_k * inv_sum; lse is relative to lbmax
-};
-
-template <int G, int TPL>
-__device__ __noinline__ void redo_word_in_log_space(LogSpaceWord<TPL>* w)
-{
-    double av[TPL], m = -INFINITY;
-#pragma unroll
-    for (int t = 0; t < TPL; t++) {
-        av[t] = (w->beta[t] > 0.0) ? w->psi[t] + log(w->beta[t]) : -INFINITY;
-        m = fmax(m, av[t]);
-    }
-    m = group_max<G>(m);
-    double ps = 0.0;
-#pragma unroll
-    for (int t = 0; t < TPL; t++) {
-        w->y[t] = (av[t] > -INFINITY) ? exp(av[t] - m) : 0.0;
-        ps += w->y[t];
-    }
-    ps = group_sum<G>(ps);
-    w->inv_sum = 1.0 / ps;
-    w->lse = m + log(ps);
-}
-
-// largest gamma the psi table serves (t = gamma + 1 < 2^kPsiOctaves), smallest the table exp takes (psi > -1e9)
-__device__ constexpr double kPsiTableMax = (double)(1 << kPsiOctaves) - 1.0;
-__device__ constexpr double kPsiTableMin = 1e-8;
 
 // KC: the number of topics when known at compile time (0: taken from the arguments).  With it the
 // row stride, the padding tests and every row address are constants or one multiply-add.
@@ -176,7 +86,9 @@ __global__ void __launch_bounds__(ONILDA_ESTEP_MAX_THREADS) estep_kernel(EStepAr
     // has a scoreboard latency that the serial chain would wait for)
     const double* __restrict__ beta_scaled = a.beta_scaled + j;
     const double* __restrict__ lbmax = a.lbmax;
+#if ONILDA_PIN
     asm volatile("" : "+l"(beta_scaled), "+l"(lbmax));
+#endif
 
     // Tables in shared memory, one copy per block: lanes index them divergently (constant memory
     // would serialise, L1 would fetch a sector per lane).
@@ -195,7 +107,9 @@ __global__ void __launch_bounds__(ONILDA_ESTEP_MAX_THREADS) estep_kernel(EStepAr
     SmemTables tb;
     tb.psi = (uint32_t)__cvta_generic_to_shared(smem_raw);
     tb.log = (uint32_t)__cvta_generic_to_shared(logtab);
+#if ONILDA_PIN
     asm volatile("" : "+r"(tb.psi), "+r"(tb.log));
+#endif
     tb.exp2 = tb.psi + (uint32_t)(sizeof(PsiRow) * kPsiRows);
 
     const unsigned int warps_per_block = blockDim.x >> 5;
@@ -376,7 +290,7 @@ __global__ void __launch_bounds__(ONILDA_ESTEP_MAX_THREADS) estep_kernel(EStepAr
             // requested before word n is worked on; ids run one word further ahead.  NB = 2 where several
             // documents share the warp (a step is long and registers are short), 3 for the one-document-per-warp
             // form, whose step is shorter than a round trip to L2 under load.
-            constexpr int NB = (G == 32) ? 3 : 2;
+            constexpr int NB = (G == 32) ? ONILDA_LONG_NB : 2;
             WordItem<TPL> ring[NB];
             int wn, cn;
 #pragma unroll
@@ -467,9 +381,6 @@ __global__ void __launch_bounds__(ONILDA_ESTEP_MAX_THREADS) estep_kernel(EStepAr
         }
     }
 }
-
-// dynamic shared memory of one block: the psi rows and the 2^(i/64) table
-static constexpr size_t kEstepTableBytes = sizeof(PsiRow) * kPsiRows + sizeof(double) * kExpTabSize;
 
 // Grid for `num_bundles` bundles of one (G, TPL) instantiation: persistent, at most the resident
 // capacity of `sm_count` SMs (or `max_blocks` when the launch shares the device with another).

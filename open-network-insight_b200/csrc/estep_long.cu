@@ -1,0 +1,348 @@
+// E-step for LONG documents (K <= 32): one document per warp, one topic per lane, the rows of the
+// words ahead staged through a per-warp ring in shared memory.
+//
+// Why a kernel of its own.  The words of a document are a serial chain (Gauss-Seidel order of
+// lda-inference.c:50-75: gamma and digamma(gamma) change after every word), so the E-step cannot end
+// before the longest document has walked len x sweeps dependent steps.  This kernel is built around the
+// latency of ONE step (measured with ncu, profiles/): nothing that can be known in advance may sit on
+// the chain E -> s -> phi -> gamma -> psi -> E.
+//   * rows (beta' of the word, last sweep's phi, lbmax) are fetched kDepth = 14 words ahead with
+//     cp.async into a ring of kRing = 16 slots per warp and read from shared memory one word ahead:
+//     a step is ~450 cycles, a trip to L2 under load up to ~1000, to HBM more - register prefetch two
+//     words ahead still left 340 cycles of scoreboard stall per word on the first multiply.
+//   * word ids come 32 at a time in one coalesced load per lane, two blocks ahead; a word's id is a
+//     shuffle from the lane that holds it.
+//   * phi = x/s is x*r + (x*r)*e with the hardware reciprocal seed r (three dependent operations),
+//     gamma is updated with one fma (gamma - c*phi_old is formed beside the chain).
+// The arithmetic is that of estep.cu (see its header): psi and exp(psi) from the shared-memory tables,
+// the likelihood bound in the algebraic form, a log-space redo of a word whose sum leaves the safe range.
+#include "estep_common.cuh"
+
+namespace onilda {
+
+namespace {
+
+constexpr int kRing = 16;    // slots of the per-warp ring (power of two)
+constexpr int kDepth = 14;   // words ahead; the slot written at word n was last read at word n - 2
+
+// cp.async under a predicate, without a branch
+__device__ __forceinline__ void cp_async16_if(bool on, uint32_t dst, const void* src)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %0, 0;\n\t@q cp.async.cg.shared.global [%1], [%2], 16;\n\t}" ::"r"((int)on), "r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async8_if(bool on, uint32_t dst, const void* src)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %0, 0;\n\t@q cp.async.ca.shared.global [%1], [%2], 8;\n\t}" ::"r"((int)on), "r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ double lds64(uint32_t addr)
+{
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr) : "memory");
+    return v;
+}
+
+struct LongWord {
+    double count, lbmax, beta, old_phi;
+};
+
+}  // namespace
+
+template <int KC>
+__global__ void __launch_bounds__(256) estep_long_kernel(EStepArgs a, unsigned long long num_docs)
+{
+    constexpr unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int K = KC ? KC : a.num_topics;
+    const uint32_t KS = KC ? (uint32_t)kpad_for(KC) : (uint32_t)a.kstride;
+    const int32_t idle_word = a.num_terms;
+    const bool valid = lane < K;
+    const double inv_K = 1.0 / K;
+
+    const double* __restrict__ beta_scaled = a.beta_scaled;
+    const double* __restrict__ lbmax = a.lbmax;
+    asm volatile("" : "+l"(beta_scaled), "+l"(lbmax));
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ LogTabEntry logtab[128];
+    {
+        const int4* src = reinterpret_cast<const int4*>(a.psi_tab);
+        int4* dst = reinterpret_cast<int4*>(smem_raw);
+        constexpr int chunks = (int)(kEstepTableBytes / sizeof(int4));
+        for (int i = threadIdx.x; i < chunks; i += blockDim.x) dst[i] = src[i];
+        for (int i = threadIdx.x; i < 128; i += blockDim.x) logtab[i] = kLogTab[i];
+        // constants and rings start as zeros (a phantom word may read a slot that was never staged)
+        double* rings = reinterpret_cast<double*>(smem_raw + kEstepTableBytes);
+        const int ring_doubles = 2 + (int)(blockDim.x >> 5) * kRing * (int)(2 * KS + 2);
+        for (int i = threadIdx.x; i < ring_doubles; i += blockDim.x) rings[i] = (i == 1) ? inv_K : 0.0;
+        __syncthreads();
+    }
+    SmemTables tb;
+    tb.psi = (uint32_t)__cvta_generic_to_shared(smem_raw);
+    tb.log = (uint32_t)__cvta_generic_to_shared(logtab);
+    asm volatile("" : "+r"(tb.psi), "+r"(tb.log));
+    tb.exp2 = tb.psi + (uint32_t)(sizeof(PsiRow) * kPsiRows);
+    // slot: beta'[KS] | phi_old[KS] | lbmax | pad
+    const uint32_t slot_bytes = 2u * KS * 8u + 16u;
+    const uint32_t ring_base = tb.psi + (uint32_t)kEstepTableBytes;
+    const uint32_t ring = ring_base + 16u + (uint32_t)(threadIdx.x >> 5) * (uint32_t)kRing * slot_bytes;
+    // two constants in front of the rings, read by address where a lane has nothing of its own to read:
+    // 0.0 (beta' of a lane beyond K) and phi before the first sweep (1/K, lda-inference.c:41; 0 beyond K)
+    const uint32_t zero_word = ring_base;
+    const uint32_t start_word = valid ? ring_base + 8u : ring_base;
+    // this lane's part in staging a word: lanes 0..15 move 16-byte pieces of the beta' row, lanes 16..31 of the phi row
+    const int piece = lane & 15;
+    const bool stages_beta = lane < 16;
+    const bool stages = (uint32_t)piece < KS / 2;
+    const uint32_t stage_dst = (stages_beta ? 0u : KS * 8u) + 16u * (uint32_t)piece;
+
+    const unsigned int warps_per_block = blockDim.x >> 5;
+    const unsigned long long first_doc = (unsigned long long)(threadIdx.x >> 5) * gridDim.x + blockIdx.x;
+    const unsigned long long queue_base = (unsigned long long)gridDim.x * warps_per_block;
+    bool first_claim = true;
+
+    for (;;) {
+        unsigned long long slot_in_order;
+        if (first_claim) {
+            slot_in_order = first_doc;
+            first_claim = false;
+        } else {
+            unsigned int claimed = 0;
+            if (lane == 0) claimed = (unsigned int)atomicAdd(a.queue, 1ull);
+            slot_in_order = queue_base + __reduce_max_sync(FULL, claimed);
+        }
+        if (slot_in_order >= num_docs) break;
+
+        const int64_t d = a.order[a.order_begin + (int64_t)slot_in_order];
+        const int64_t beg = a.offsets[d];
+        const int len = (int)(a.offsets[d + 1] - beg);
+        const int total = a.totals[d];
+        const int32_t* __restrict__ doc_words = a.words + beg;
+        const int32_t* __restrict__ doc_counts = a.counts + beg;
+        double* __restrict__ doc_phi = a.phi + beg * (int64_t)KS;
+        const double* stage_src_phi = doc_phi + 2 * piece;
+
+        // every gamma of a document stays within [alpha, alpha + total]: the caller (em.cu) sends only documents for
+        // which that interval lies inside the tables' range
+        auto psi_exp = [&](double g, double& psi, double& E) {
+            const PsiExp pe = psi_exp_tab<true>(g, tb);
+            psi = pe.psi;
+            E = pe.e;
+        };
+
+        const double gamma0 = a.alpha + (total / ((double)K));
+        double gam = valid ? gamma0 : 1.0, psi, E;
+        psi_exp(gam, psi, E);
+
+        double lik = 0.0, lik_old = 0.0, converged = 1.0;
+        int sweeps = 0;
+        bool active = (converged > a.var_converged) && ((0 < a.var_max_iter) || (a.var_max_iter == -1));
+
+        while (active) {
+            sweeps++;
+            const bool first = (sweeps == 1);
+            double acc_lse = 0.0, acc_psi = 0.0;
+
+            // ids, 32 words per block: the current block, the next one, and the one after (in flight; nothing
+            // reads it until it has moved up, 32 words later)
+            int blk = 0;
+            int w0, c0, w1, c1, w2, c2;
+            auto load_block = [&](int b, int& w, int& c) {
+                const int m = b * 32 + lane;
+                w = idle_word;
+                c = 0;
+                if (m < len) {
+                    w = doc_words[m];
+                    c = doc_counts[m];
+                }
+            };
+            load_block(0, w0, c0);
+            load_block(1, w1, c1);
+            load_block(2, w2, c2);
+
+            // Everything below up to the rare-path test at the end of a word is ONE basic block (predicated
+            // copies, no branches), so that the compiler can place the staging work of later words into the
+            // latency gaps of the chain of the current one.
+            // rows of word m -> slot m % kRing (m is warp-uniform); always one commit group per call
+            auto stage = [&](int m) {
+                const int w = __shfl_sync(FULL, ((m >> 5) == blk) ? w0 : w1, m & 31);
+                const uint32_t slot = ring + (uint32_t)(m & (kRing - 1)) * slot_bytes;
+                const double* src = stages_beta ? beta_scaled + (uint64_t)(uint32_t)w * KS + 2 * piece
+                                                : stage_src_phi + (uint64_t)(uint32_t)m * KS;
+                // past the end of the document the id is the table's idle row (beta' = 1, lbmax = 0): a phantom word
+                // then finds a harmless slot; phi rows past the end belong to other documents and are not touched
+                cp_async16_if(stages && (stages_beta || (!first && m < len)), slot + stage_dst, src);
+                cp_async8_if(lane == 31, slot + 2u * KS * 8u, lbmax + w);
+                cp_async_commit();
+            };
+            // the staged rows of word m into registers (m's group has landed and the warp has synchronised)
+            auto fetch = [&](int m, LongWord& it) {
+                const uint32_t slot = ring + (uint32_t)(m & (kRing - 1)) * slot_bytes;
+                it.count = (double)__shfl_sync(FULL, ((m >> 5) == blk) ? c0 : c1, m & 31);
+                it.lbmax = lds64(slot + 2u * KS * 8u);
+                // lanes beyond K read the slot's zero word: beta' = 0 keeps them inert
+                it.beta = lds64(valid ? slot + 8u * (uint32_t)lane : zero_word);
+                it.old_phi = lds64((valid && !first) ? slot + KS * 8u + 8u * (uint32_t)lane : start_word);
+            };
+
+            double s_prev = 1.0, c_prev = 0.0, lb_prev = 0.0;
+            auto step = [&](const LongWord& it, int n) {
+                const double gam_in = gam, psi_in = psi, acc_psi_in = acc_psi;
+                const double x = E * it.beta;
+                double s = x;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(FULL, s, o);
+                const double gpre = fma(-it.count, it.old_phi, gam);      // beside the chain
+                acc_lse = fma(c_prev, lb_prev + fast_log_tab(s_prev, tb), acc_lse);
+                const double r0 = rcp_seed(s);
+                double e = fma(-s, r0, 1.0);
+                e = fma(e, e, e);
+                s_prev = s;
+                c_prev = it.count;
+                lb_prev = it.lbmax;
+                const double xr = x * r0;
+                const double p = fma(xr, e, xr);
+                gam = fma(it.count, p, gpre);
+                const bool keep = valid && n < len;
+                double* const prow = doc_phi + (uint64_t)(uint32_t)n * KS + lane;
+                if (keep) *prow = p;
+                acc_psi = fma(it.count * p, psi, acc_psi);
+                const PsiExp pe = psi_exp_tab<true>(gam, tb);
+                psi = pe.psi;
+                E = pe.e;
+                // s outside [2^-963, 2^963), zero, negative or NaN (an integer test on the exponent field; s is the
+                // same in every lane): the word is done again in log space, as the reference does
+                // (lda-inference.c:52-68), from the state saved above.  Rare; kept out of line.
+                if (__builtin_expect((uint32_t)(double_hi(s) - 0x03C00000) >= (uint32_t)(0x7C200000 - 0x03C00000), 0)) {
+                    LogSpaceWord<1> ls;
+                    ls.psi[0] = psi_in;
+                    ls.beta[0] = it.beta;
+                    redo_word_in_log_space<32, 1>(&ls);
+                    const double p2 = ls.y[0] * ls.inv_sum;
+                    gam = fma(it.count, p2, fma(-it.count, it.old_phi, gam_in));
+                    if (keep) *prow = p2;
+                    acc_psi = fma(it.count * p2, psi_in, acc_psi_in);
+                    acc_lse = fma(it.count, it.lbmax + ls.lse, acc_lse);
+                    c_prev = 0.0;      // this word's log-sum is already in
+                    s_prev = 1.0;
+                    const PsiExp pe2 = psi_exp_tab<true>(gam, tb);
+                    psi = pe2.psi;
+                    E = pe2.e;
+                }
+            };
+
+            for (int m = 0; m < kDepth; m++) stage(m);
+            cp_async_wait<kDepth - 1>();
+            __syncwarp();
+            LongWord A, B;
+            fetch(0, A);
+            auto advance = [&](int n, LongWord& now, LongWord& next) {
+                stage(n + kDepth);
+                cp_async_wait<kDepth - 1>();      // word n + 1 has landed
+                __syncwarp();
+                fetch(n + 1, next);
+                step(now, n);
+            };
+            // words in pairs (an odd document ends on a phantom word: count 0, nothing stored), 32 to a block of ids
+            for (int n0 = 0; n0 < len; n0 += 32) {
+                const int n1 = (n0 + 32 < len) ? n0 + 32 : len;
+                for (int n = n0; n < n1; n += 2) {
+                    advance(n, A, B);
+                    advance(n + 1, B, A);
+                }
+                blk++;
+                w0 = w1; c0 = c1;
+                w1 = w2; c1 = c2;
+                load_block(blk + 2, w2, c2);
+            }
+            cp_async_wait<0>();
+            __syncwarp();
+            acc_lse = fma(c_prev, lb_prev + fast_log_tab(s_prev, tb), acc_lse);
+
+            // likelihood bound of this sweep (lda-inference.c:93-127; estep.cu header)
+            double gs = valid ? gam : 0.0, lg = valid ? lgamma(gam) : 0.0, ap = acc_psi;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                gs += __shfl_xor_sync(FULL, gs, o);
+                lg += __shfl_xor_sync(FULL, lg, o);
+                ap += __shfl_xor_sync(FULL, ap, o);
+            }
+            lik = a.lik_const - lgamma(gs) + lg - ap + acc_lse;
+            if (isnan(lik)) *a.error_flag = 1;   // the reference asserts here (lda-inference.c:78)
+            converged = (lik_old - lik) / lik_old;
+            lik_old = lik;
+            active = (converged > a.var_converged) && ((sweeps < a.var_max_iter) || (a.var_max_iter == -1));
+        }
+
+        // doc_e_step (lda-estimate.c:40-46)
+        double gs = valid ? gam : 0.0, ps = valid ? psi : 0.0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            gs += __shfl_xor_sync(FULL, gs, o);
+            ps += __shfl_xor_sync(FULL, ps, o);
+        }
+        if (valid) a.gamma[d * K + lane] = gam;
+        if (lane == 0) {
+            a.doc_lik[d] = lik;
+            a.doc_alpha_ss[d] = ps - K * digamma(gs);
+            a.doc_sweeps[d] = sweeps;
+        }
+        // class_word[k][w] += c_n phi_nk (lda-estimate.c:48-55)
+        if (a.class_word != nullptr) {
+            constexpr int U = 8;
+            double* __restrict__ class_word = a.class_word + lane;
+            for (int n0 = 0; n0 < len; n0 += U) {
+                int w[U];
+                double c[U], p[U];
+#pragma unroll
+                for (int u = 0; u < U; u++) {
+                    const bool in = n0 + u < len;
+                    w[u] = in ? doc_words[n0 + u] : -1;
+                    c[u] = in ? (double)doc_counts[n0 + u] : 0.0;
+                    p[u] = (in && valid && sweeps != 0) ? doc_phi[(uint64_t)(uint32_t)(n0 + u) * KS + lane] : inv_K;
+                }
+#pragma unroll
+                for (int u = 0; u < U; u++)
+                    if (w[u] >= 0 && valid) atomicAdd(class_word + (uint64_t)(uint32_t)w[u] * KS, c[u] * p[u]);
+            }
+        }
+    }
+}
+
+template <int KC>
+static int launch_long_one(const EStepArgs& args, int sm_count, int block_threads, int max_per_sm, cudaStream_t stream)
+{
+    if (block_threads > 256 || block_threads < 32 || (block_threads & 31))
+        return onilda_fail(ONILDA_EINVAL, "long-document E-step block of %d threads (32..256, whole warps)", block_threads);
+    const size_t slot_bytes = 2 * (size_t)args.kstride * 8 + 16;
+    const size_t smem = kEstepTableBytes + 16 + (size_t)(block_threads / 32) * kRing * slot_bytes;
+    ONILDA_CUDA(cudaFuncSetAttribute(estep_long_kernel<KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    ONILDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_long_kernel<KC>, block_threads, smem));
+    if (per_sm < 1) per_sm = 1;
+    if (max_per_sm > 0 && per_sm > max_per_sm) per_sm = max_per_sm;
+    const unsigned long long wpb = (unsigned long long)(block_threads / 32);
+    const unsigned long long docs = (unsigned long long)args.order_count;
+    unsigned long long grid = (unsigned long long)sm_count * per_sm;
+    if (grid > (docs + wpb - 1) / wpb) grid = (docs + wpb - 1) / wpb;
+    estep_long_kernel<KC><<<(unsigned)grid, block_threads, smem, stream>>>(args, docs);
+    ONILDA_CUDA(cudaGetLastError());
+    return ONILDA_OK;
+}
+
+// The documents order[order_begin, order_begin + order_count), one per warp.  K <= 32 and an even row stride <= 32.
+int launch_estep_long(const EStepArgs& args, int sm_count, int block_threads, int max_per_sm, cudaStream_t stream, int* launches)
+{
+    if (args.order_count <= 0) return ONILDA_OK;
+    if (args.num_topics > 32 || args.kstride > 32 || (args.kstride & 1))
+        return onilda_fail(ONILDA_EINVAL, "long-document E-step: %d topics with row stride %d unsupported", args.num_topics, args.kstride);
+    int rc;
+    if (args.num_topics == 20 && args.kstride == kpad_for(20)) rc = launch_long_one<20>(args, sm_count, block_threads, max_per_sm, stream);
+    else rc = launch_long_one<0>(args, sm_count, block_threads, max_per_sm, stream);
+    if (rc == ONILDA_OK && launches) *launches += 1;
+    return rc;
+}
+
+}  // namespace onilda

@@ -78,6 +78,9 @@ struct EStepArgs {
 int launch_estep(int group, const EStepArgs& args, int sm_count, int block_threads, int extra_smem, int max_per_sm,
                  cudaStream_t stream, int* launches);
 
+// estep_long.cu: documents one per warp with staged rows (K <= 32)
+int launch_estep_long(const EStepArgs& args, int sm_count, int block_threads, int max_per_sm, cudaStream_t stream, int* launches);
+
 // M-step and table kernels (mstep.cu)
 int launch_tables_from_log_beta(const double* log_beta_kv, int K, int V, const TopicLayout& lay, double* log_beta_wk,
                                 double* beta_scaled, double* lbmax, cudaStream_t stream, int* launches);

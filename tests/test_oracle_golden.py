@@ -271,3 +271,20 @@ def test_country_codes_match_reference(oracle):
         text = ref.read_text()
         listed = set(re.findall(r'"([a-z]*)"', text[text.index("val countryCodes = Set("):text.index("def dnsWordCreation")]))
         assert listed == oracle.COUNTRY_CODES
+
+
+def test_oracle_first_iteration_of_cfg1_fixture(oracle, tmp_path):
+    """The C restatement's first E-step from tests/golden/cfg1/000 (10,000 documents, V = 5,000, K = 20) gives the
+    first line of the likelihood.dat the unmodified reference wrote (tests/golden/make_golden_cfg1.py)."""
+    import gzip
+    import shutil
+    d = GOLD / "cfg1"
+    for name in ("c.dat", "000.beta"):
+        with gzip.open(d / (name + ".gz"), "rb") as f, open(tmp_path / name, "wb") as g:
+            shutil.copyfileobj(f, g)
+    shutil.copy(d / "000.other", tmp_path / "000.other")
+    off, w, cn, tot, V = oracle.read_dat(tmp_path / "c.dat")
+    alpha, lb = oracle.load_model(tmp_path / "000")
+    ref = oracle.e_step(off, w, cn, V, alpha, lb, 20, float(np.float32(1e-6)))
+    want = float((d / "likelihood.dat").read_text().split()[0])
+    assert abs(ref["lik"] - want) <= 1e-9 * abs(want)
