@@ -53,7 +53,7 @@
 #define ONILDA_PIN 1
 #endif
 #ifndef ONILDA_ESTEP_MAX_THREADS
-#define ONILDA_ESTEP_MAX_THREADS 384
+#define ONILDA_ESTEP_MAX_THREADS 512
 #endif
 
 namespace onilda {
