@@ -262,10 +262,10 @@ int onilda_em_estep(onilda_em* em);
 /* The shard's sufficient statistics as ONE packed fp64 device buffer, the
  * operand of the per-iteration sum over shards (replaces the 2K+3 MPI_Allreduce
  * calls at lda-estimate.c:211-252):
- *    [ class_word, word-major, V x kpad | likelihood | alpha_suffstats | num_docs | 0 ]
- * Single shard: skip this.  Several shards: all-reduce (SUM) `count` doubles in
- * place across the shards' buffers (NCCL or onilda_em_allreduce_peer), then
- * call onilda_em_mstep on every shard. */
+ *    [ class_word, word-major, (V + 16) x kpad (the last 16 rows zero) | likelihood | alpha_suffstats | num_docs | 0 ]
+ * Single shard: skip this.  Several shards WITHOUT a communicator attached (see below): all-reduce (SUM)
+ * `count` doubles in place across the shards' buffers (onilda_em_allreduce_peer, or the caller's own
+ * collective), then call onilda_em_mstep on every shard. */
 int onilda_em_suffstats_device(onilda_em* em, double** dev_ptr, int64_t* count);
 /* M-step + convergence bookkeeping: lda_mle (lda-model.c:27-54, log-normalise
  * on device; opt_alpha's scalar Newton on the host, lda-alpha.c:42-68), then
@@ -284,8 +284,39 @@ int onilda_em_reload(onilda_em* em, const onilda_model* m);
 int onilda_em_iterate(onilda_em* em, double* likelihood, double* converged, int* keep_going);
 /* In-process sum of the packed statistics of `n` handles (one per device, same
  * process) over NVLink peer memory; each device reduces its slice of the buffer
- * from all peers and writes the sum back to every peer. */
+ * from all peers, always in rank order, and writes the sum back to every peer:
+ * the alternative to the communicator below when identical bits from run to run
+ * matter more than the replicated M-step it leaves to every device. */
 int onilda_em_allreduce_peer(onilda_em** ems, int n);
+
+/* Several shards, one communicator (NCCL over NVLink / NVSwitch).  Replaces the MPI calls of
+ * lda-estimate.c:211-252 - MPI_Barrier, then MPI_Allreduce of alpha_suffstats, num_docs, K rows of
+ * class_word, K class_total values and the likelihood - and the lda_mle every rank then repeats (:256).
+ * With a communicator attached, onilda_em_mstep / onilda_em_mstep_group run on the handles' streams, with no
+ * host synchronisation before the final read-back of four scalars:
+ *     reduce-scatter of class_word (rank r receives the sums of rows [r*ceil(V/P), (r+1)*ceil(V/P)))
+ *     -> class_total partial sums of those rows -> all-reduce of [likelihood, alpha_suffstats, num_docs, class_total]
+ *     -> lda_mle of the own rows -> all-gather of log_beta, the E-step's beta' table and its row maxima.
+ * The caller does NOT all-reduce onilda_em_suffstats_device itself in this mode.
+ *   one process per GPU (torchrun, mpiexec): rank 0 calls onilda_comm_unique_id, ships the 128 bytes to the
+ *     others by its own means, every rank calls onilda_em_comm_attach (collective, like ncclCommInitRank);
+ *   one process, n devices: onilda_em_comm_attach_local on the n handles, then onilda_em_mstep_group on all of them.
+ * At most 16 ranks.  Every rank must hold the same V and K. */
+#define ONILDA_COMM_ID_BYTES 128
+int onilda_comm_unique_id(unsigned char* id /* [ONILDA_COMM_ID_BYTES] */);
+int onilda_em_comm_attach(onilda_em* em, const unsigned char* id, int nranks, int rank);
+int onilda_em_comm_attach_local(onilda_em** ems, int n);
+/* onilda_em_mstep for all handles of this process at once (NCCL calls of several devices issued by one thread
+ * must sit in one group).  likelihood / converged / keep_going are those of the whole corpus. */
+int onilda_em_mstep_group(onilda_em** ems, int n, double* likelihood, double* converged, int* keep_going);
+/* What the last mstep's exchange took on this handle's stream, in ms (CUDA events; includes the wait for the
+ * slowest rank's E-step), and the communicator's shape. */
+int onilda_em_comm_stats(onilda_em* em, int* nranks, int* rank, double* reduce_scatter_ms, double* all_gather_ms);
+/* The exchange by itself, for bus-bandwidth figures: `repeats` reduce-scatters of the statistics table, then as
+ * many rounds of the three all-gathers, each set started together on all ranks; per-call ms (max over the
+ * handles given) and the table bytes one call reduces / gathers.  Collective.  Leaves the statistics buffer
+ * undefined until the next onilda_em_estep; the model is unchanged. */
+int onilda_em_collective_time(onilda_em** ems, int n, int repeats, double* rs_ms, double* ag_ms, int64_t* bytes);
 
 /* Current model (after the last mstep) and the variational gamma of the
  * shard's documents from the last estep ([doc_end-doc_begin][K], row i is

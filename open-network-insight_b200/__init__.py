@@ -115,6 +115,12 @@ def lib():
     L.onilda_em_mstep.argtypes = [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int)]
     L.onilda_em_iterate.argtypes = [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int)]
     L.onilda_em_allreduce_peer.argtypes = [C.POINTER(_vp), C.c_int]
+    L.onilda_comm_unique_id.argtypes = [C.c_char_p]
+    L.onilda_em_comm_attach.argtypes = [_vp, C.c_char_p, C.c_int, C.c_int]
+    L.onilda_em_comm_attach_local.argtypes = [C.POINTER(_vp), C.c_int]
+    L.onilda_em_mstep_group.argtypes = [C.POINTER(_vp), C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int)]
+    L.onilda_em_comm_stats.argtypes = [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.onilda_em_collective_time.argtypes = [C.POINTER(_vp), C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int64)]
     L.onilda_em_get_model.argtypes = [_vp, _vp]
     L.onilda_em_get_gamma.argtypes = [_vp, _f64p]
     L.onilda_em_get_doc_likelihood.argtypes = [_vp, _f64p]
@@ -480,6 +486,63 @@ class EM:
 def allreduce_peer(ems):
     arr = (_vp * len(ems))(*[e._h for e in ems])
     _check(lib().onilda_em_allreduce_peer(arr, len(ems)))
+
+
+COMM_ID_BYTES = 128
+
+
+def _nccl_of_this_process():
+    """libonilda binds NCCL at the first communicator call (csrc/nccl_dyn.h) and takes the libnccl.so.2 the process
+    already holds.  A Python process that will also import PyTorch must hold PyTorch's own NCCL by then - the
+    system library is older, and loading it first makes a later `import torch` fail on missing symbols - so
+    PyTorch, where installed, is imported before the first such call."""
+    try:
+        import torch  # noqa: F401
+    except ImportError:
+        pass
+
+
+def comm_unique_id() -> bytes:
+    """The 128 bytes rank 0 ships to every other rank before comm_attach (ncclGetUniqueId)."""
+    _nccl_of_this_process()
+    buf = C.create_string_buffer(COMM_ID_BYTES)
+    _check(lib().onilda_comm_unique_id(buf))
+    return buf.raw
+
+
+def comm_attach(em: "EM", comm_id: bytes, nranks: int, rank: int):
+    """One process per GPU: collective over all ranks."""
+    assert len(comm_id) == COMM_ID_BYTES
+    _nccl_of_this_process()
+    _check(lib().onilda_em_comm_attach(em._h, comm_id, nranks, rank))
+
+
+def comm_attach_local(ems):
+    """One process, several devices."""
+    _nccl_of_this_process()
+    arr = (_vp * len(ems))(*[e._h for e in ems])
+    _check(lib().onilda_em_comm_attach_local(arr, len(ems)))
+
+
+def mstep_group(ems):
+    arr = (_vp * len(ems))(*[e._h for e in ems])
+    lik, conv, keep = C.c_double(), C.c_double(), C.c_int()
+    _check(lib().onilda_em_mstep_group(arr, len(ems), C.byref(lik), C.byref(conv), C.byref(keep)))
+    return lik.value, conv.value, bool(keep.value)
+
+
+def comm_stats(em: "EM"):
+    n, r, rs, ag = C.c_int(), C.c_int(), C.c_double(), C.c_double()
+    _check(lib().onilda_em_comm_stats(em._h, C.byref(n), C.byref(r), C.byref(rs), C.byref(ag)))
+    return dict(nranks=n.value, rank=r.value, reduce_scatter_ms=rs.value, all_gather_ms=ag.value)
+
+
+def collective_time(ems, repeats=10):
+    """Per-call ms of the M-step's reduce-scatter and of its three all-gathers, and the table bytes of one call."""
+    arr = (_vp * len(ems))(*[e._h for e in ems])
+    rs, ag, nb = C.c_double(), C.c_double(), C.c_int64()
+    _check(lib().onilda_em_collective_time(arr, len(ems), repeats, C.byref(rs), C.byref(ag), C.byref(nb)))
+    return dict(reduce_scatter_ms=rs.value, all_gather_ms=ag.value, table_bytes=nb.value)
 
 
 def run_em(start, directory, corpus: Corpus, num_topics, initial_alpha, settings: Settings, ndev=1, seed=0):

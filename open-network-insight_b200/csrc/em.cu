@@ -7,8 +7,10 @@
 
 #include <vector>
 
+
 #include "device_math.cuh"
 #include "kernels.cuh"
+#include "nccl_dyn.h"
 
 using namespace onilda;
 
@@ -39,8 +41,7 @@ struct onilda_em {
     int64_t* d_offsets;
     int32_t *d_words, *d_counts, *d_totals, *d_order;
     double *d_log_beta_wk, *d_beta_scaled, *d_lbmax;
-    double* d_ss;               // [V*kpad + SS_TAIL]
-    double* d_class_total;      // [kpad]
+    double* d_ss;               // [(V + kTablePadRows)*kpad statistics | SS_TAIL scalars | kpad class_total]
     double* d_partial;
     double* d_phi;              // [nnz][kpad]
     double *d_gamma, *d_doc_lik, *d_doc_ass;
@@ -54,6 +55,11 @@ struct onilda_em {
     int64_t launches;
     int64_t sweeps;
     int estep_done;
+    // sufficient statistics across shards (NCCL); nranks == 1: none
+    ncclComm_t comm;
+    int nranks, rank;
+    cudaEvent_t ev_c0, ev_c1, ev_c2, ev_c3;   // around the reduce-scatter and the all-gathers
+    double rs_ms, ag_ms;
 };
 
 namespace {
@@ -90,6 +96,9 @@ void order_by_length(const int64_t* offsets, int64_t D, int32_t max_len, std::ve
     order.resize((size_t)D);
     for (int64_t d = 0; d < D; d++) order[(size_t)start[(size_t)(max_len - (offsets[d + 1] - offsets[d]))]++] = (int32_t)d;
 }
+
+// doubles of the padded statistics / model tables; the scalar tail and class_total follow in d_ss
+size_t table_doubles(const onilda_em* em) { return ((size_t)em->V + kTablePadRows) * em->lay.kpad; }
 
 int upload_model(onilda_em* em, const double* log_beta_kv)
 {
@@ -161,7 +170,7 @@ extern "C" void onilda_em_destroy(onilda_em* em)
     DeviceGuard g(em->device);
     cudaFree(em->d_offsets); cudaFree(em->d_words); cudaFree(em->d_counts); cudaFree(em->d_totals); cudaFree(em->d_order);
     cudaFree(em->d_log_beta_wk); cudaFree(em->d_beta_scaled); cudaFree(em->d_lbmax); cudaFree(em->d_ss);
-    cudaFree(em->d_class_total); cudaFree(em->d_partial); cudaFree(em->d_phi); cudaFree(em->d_gamma);
+    cudaFree(em->d_partial); cudaFree(em->d_phi); cudaFree(em->d_gamma);
     cudaFree(em->d_doc_lik); cudaFree(em->d_doc_ass); cudaFree(em->d_doc_sweeps); cudaFree(em->d_queue);
     cudaFree(em->d_error); cudaFree(em->d_kv); cudaFree(em->d_math_tab);
     if (em->ev0) cudaEventDestroy(em->ev0);
@@ -173,6 +182,11 @@ extern "C" void onilda_em_destroy(onilda_em* em)
     if (em->ev_forked) cudaEventDestroy(em->ev_forked);
     if (em->ev_long_end) cudaEventDestroy(em->ev_long_end);
     if (em->ev_bulk_end) cudaEventDestroy(em->ev_bulk_end);
+    if (em->comm) { const NcclApi* nccl = nccl_api(); if (nccl) nccl->CommDestroy(em->comm); }
+    if (em->ev_c0) cudaEventDestroy(em->ev_c0);
+    if (em->ev_c1) cudaEventDestroy(em->ev_c1);
+    if (em->ev_c2) cudaEventDestroy(em->ev_c2);
+    if (em->ev_c3) cudaEventDestroy(em->ev_c3);
     if (em->long_stream) cudaStreamDestroy(em->long_stream);
     if (em->stream) cudaStreamDestroy(em->stream);
     free(em);
@@ -243,11 +257,20 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
     TRY(dev_alloc(&em->d_counts, (size_t)N));
     TRY(dev_alloc(&em->d_totals, (size_t)D));
     TRY(dev_alloc(&em->d_order, (size_t)D));
-    TRY(dev_alloc(&em->d_log_beta_wk, table));
-    TRY(dev_alloc(&em->d_beta_scaled, table + lay.kpad));       // + the idle row (kernels.cuh: EStepArgs)
-    TRY(dev_alloc(&em->d_lbmax, (size_t)em->V + 1));
-    TRY(dev_alloc(&em->d_ss, table + SS_TAIL));
-    TRY(dev_alloc(&em->d_class_total, (size_t)lay.kpad));
+    // every table has kTablePadRows spare rows (kernels.cuh); beta_scaled and lbmax one more, the idle row
+    const size_t table_pad = table + (size_t)kTablePadRows * lay.kpad;
+    TRY(dev_alloc(&em->d_log_beta_wk, table_pad));
+    TRY(dev_alloc(&em->d_beta_scaled, table_pad + lay.kpad));
+    TRY(dev_alloc(&em->d_lbmax, (size_t)em->V + kTablePadRows + 1));
+    TRY(dev_alloc(&em->d_ss, table_pad + SS_TAIL + lay.kpad));
+    em->nranks = 1;
+    TRYCUDA(cudaEventCreate(&em->ev_c0));
+    TRYCUDA(cudaEventCreate(&em->ev_c1));
+    TRYCUDA(cudaEventCreate(&em->ev_c2));
+    TRYCUDA(cudaEventCreate(&em->ev_c3));
+    TRYCUDA(cudaMemset(em->d_log_beta_wk, 0, sizeof(double) * table_pad));
+    TRYCUDA(cudaMemset(em->d_beta_scaled, 0, sizeof(double) * table_pad));
+    TRYCUDA(cudaMemset(em->d_lbmax, 0, sizeof(double) * ((size_t)em->V + kTablePadRows)));
     TRY(dev_alloc(&em->d_partial, (size_t)mstep_partial_doubles(em->V, lay, D)));
     TRY(dev_alloc(&em->d_phi, (size_t)N * lay.kpad));
     TRY(dev_alloc(&em->d_gamma, (size_t)D * em->K));
@@ -265,8 +288,8 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
         TRYCUDA(cudaMemcpy(em->d_math_tab, tab.data(), sizeof(double) * tab.size(), cudaMemcpyHostToDevice));
         std::vector<double> idle((size_t)lay.kpad + 1, 0.0);     // beta' = 1 for the real topics, then lbmax = 0
         for (int k = 0; k < em->K; k++) idle[(size_t)k] = 1.0;
-        TRYCUDA(cudaMemcpy(em->d_beta_scaled + table, idle.data(), sizeof(double) * lay.kpad, cudaMemcpyHostToDevice));
-        TRYCUDA(cudaMemcpy(em->d_lbmax + em->V, idle.data() + lay.kpad, sizeof(double), cudaMemcpyHostToDevice));
+        TRYCUDA(cudaMemcpy(em->d_beta_scaled + table_pad, idle.data(), sizeof(double) * lay.kpad, cudaMemcpyHostToDevice));
+        TRYCUDA(cudaMemcpy(em->d_lbmax + em->V + kTablePadRows, idle.data() + lay.kpad, sizeof(double), cudaMemcpyHostToDevice));
     }
 
     // shard-local CSR
@@ -325,7 +348,7 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
         }
         TRYCUDA(cudaStreamSynchronize(em->stream));   // the host vectors go out of scope
     }
-    TRYCUDA(cudaMemsetAsync(em->d_ss, 0, sizeof(double) * (table + SS_TAIL), em->stream));
+    TRYCUDA(cudaMemsetAsync(em->d_ss, 0, sizeof(double) * (table_pad + SS_TAIL + lay.kpad), em->stream));
     TRYCUDA(cudaMemsetAsync(em->d_error, 0, sizeof(int), em->stream));
     TRY(upload_model(em, start->log_beta));
     TRYCUDA(cudaStreamSynchronize(em->stream));
@@ -364,17 +387,17 @@ extern "C" int onilda_em_reload(onilda_em* em, const onilda_model* m)
 
 static int run_estep(onilda_em* em, bool accumulate)
 {
-    const size_t table = (size_t)em->V * em->lay.kpad;
+    const size_t table = table_doubles(em);
     int l = 0;
     ONILDA_CUDA(cudaEventRecord(em->ev0, em->stream));
     if (accumulate) {
-        ONILDA_CUDA(cudaMemsetAsync(em->d_ss, 0, sizeof(double) * (table + SS_TAIL), em->stream));   // zero_initialize_ss
+        ONILDA_CUDA(cudaMemsetAsync(em->d_ss, 0, sizeof(double) * (table + SS_TAIL + em->lay.kpad), em->stream));   // zero_initialize_ss
     }
     EStepArgs a;
     a.offsets = em->d_offsets; a.words = em->d_words; a.counts = em->d_counts; a.totals = em->d_totals;
     a.order = em->d_order;
     a.psi_tab = em->d_math_tab; a.exp_tab = em->d_math_tab + (size_t)6 * kPsiRows;
-    a.beta_scaled = em->d_beta_scaled; a.lbmax = em->d_lbmax; a.num_topics = em->K; a.num_terms = em->V; a.kstride = em->lay.kpad;
+    a.beta_scaled = em->d_beta_scaled; a.lbmax = em->d_lbmax; a.num_topics = em->K; a.num_terms = em->V; a.idle_row = em->V + kTablePadRows; a.kstride = em->lay.kpad;
     a.alpha = em->alpha;
     a.lik_const = lgamma(em->alpha * em->K) - em->K * lgamma(em->alpha);
     a.var_max_iter = em->var_max_iter;
@@ -434,57 +457,289 @@ extern "C" int onilda_em_suffstats_device(onilda_em* em, double** dev_ptr, int64
 {
     if (!em || !dev_ptr || !count) return onilda_fail(ONILDA_EINVAL, "em_suffstats_device: null argument");
     *dev_ptr = em->d_ss;
-    *count = (int64_t)em->V * em->lay.kpad + SS_TAIL;
+    *count = (int64_t)table_doubles(em) + SS_TAIL;
     return ONILDA_OK;
 }
 
 extern "C" void* onilda_em_stream(onilda_em* em) { return em ? (void*)em->stream : nullptr; }
 
+// The M-step over all shards of one process (n handles; one per process under torchrun).
+//
+// One shard: column sums -> lda_mle rows (lda-model.c:27-44) on the device.
+// P shards (a communicator attached): what the reference does with 2K + 3 MPI_Allreduce calls and a replicated
+// lda_mle on every rank (lda-estimate.c:211-256) becomes, stream-ordered and without a host synchronisation,
+//     ncclReduceScatter of class_word      each rank receives the sums of its own ceil(V/P) rows
+//     column sums of the own rows          partial class_total
+//     ncclAllReduce of 4 + kpad doubles    likelihood, alpha statistic, document count, class_total
+//     lda_mle on the own rows              log(cw) - log(ct) | -100, beta', lbmax
+//     ncclAllGather x 3                    log_beta, beta', lbmax: every rank has the whole model again
+// which moves the same bytes as an all-reduce of K x V doubles and normalises each row once instead of P times.
+static int mstep_group(onilda_em** ems, int n, double* likelihood, double* converged, int* keep_going)
+{
+    for (int i = 0; i < n; i++) {
+        if (!ems[i]) return onilda_fail(ONILDA_EINVAL, "em_mstep: null handle");
+        if (!ems[i]->estep_done) return onilda_fail(ONILDA_EINVAL, "em_mstep: call onilda_em_estep first");
+        if (ems[i]->nranks != ems[0]->nranks || ems[i]->V != ems[0]->V || ems[i]->K != ems[0]->K)
+            return onilda_fail(ONILDA_EINVAL, "em_mstep: handles of different shapes in one group");
+    }
+    const int P = ems[0]->nranks;
+    if (P > 1 && !ems[0]->comm) return onilda_fail(ONILDA_EINVAL, "em_mstep: no communicator attached");
+    const NcclApi* nccl = P > 1 ? nccl_api() : nullptr;
+    if (P > 1 && !nccl) return ONILDA_ECUDA;
+    int prev = 0;
+    ONILDA_CUDA(cudaGetDevice(&prev));
+    struct Restore { int d; ~Restore() { cudaSetDevice(d); } } restore{prev};
+    const int kpad = ems[0]->lay.kpad;
+    const size_t table = table_doubles(ems[0]);
+    const int64_t rows_per_rank = P > 1 ? ((int64_t)ems[0]->V + P - 1) / P : (int64_t)ems[0]->V;
+    std::vector<int> launches((size_t)n, 0);
+#define NCCL_TRY(call)                                                                                              \
+    do {                                                                                                            \
+        ncclResult_t r__ = (call);                                                                                  \
+        if (r__ != ncclSuccess) return onilda_fail(ONILDA_ECUDA, "%s failed: %s", #call, nccl->GetErrorString(r__)); \
+    } while (0)
+
+    for (int i = 0; i < n; i++) {
+        ONILDA_CUDA(cudaSetDevice(ems[i]->device));
+        ONILDA_CUDA(cudaEventRecord(ems[i]->ev2, ems[i]->stream));
+        ONILDA_CUDA(cudaEventRecord(ems[i]->ev_c0, ems[i]->stream));
+    }
+    if (P > 1) {
+        NCCL_TRY(nccl->GroupStart());
+        for (int i = 0; i < n; i++) {
+            onilda_em* em = ems[i];
+            const size_t cnt = (size_t)rows_per_rank * kpad;
+            NCCL_TRY(nccl->ReduceScatter(em->d_ss, em->d_ss + (size_t)em->rank * cnt, cnt, ncclDouble, ncclSum, em->comm, em->stream));
+        }
+        NCCL_TRY(nccl->GroupEnd());
+    }
+    for (int i = 0; i < n; i++) {
+        onilda_em* em = ems[i];
+        ONILDA_CUDA(cudaSetDevice(em->device));
+        ONILDA_CUDA(cudaEventRecord(em->ev_c1, em->stream));
+        const size_t lo = P > 1 ? (size_t)em->rank * rows_per_rank : 0;
+        int rc = launch_column_sums(em->d_ss + lo * kpad, (int)rows_per_rank, em->lay, em->sm_count, em->d_partial,
+                                    em->d_ss + table + SS_TAIL, em->stream, &launches[(size_t)i]);
+        if (rc != ONILDA_OK) return rc;
+    }
+    if (P > 1) {
+        NCCL_TRY(nccl->GroupStart());
+        for (int i = 0; i < n; i++)
+            NCCL_TRY(nccl->AllReduce(ems[i]->d_ss + table, ems[i]->d_ss + table, (size_t)SS_TAIL + kpad, ncclDouble, ncclSum,
+                                   ems[i]->comm, ems[i]->stream));
+        NCCL_TRY(nccl->GroupEnd());
+    }
+    for (int i = 0; i < n; i++) {
+        onilda_em* em = ems[i];
+        ONILDA_CUDA(cudaSetDevice(em->device));
+        const size_t lo = P > 1 ? (size_t)em->rank * rows_per_rank : 0;
+        int rc = launch_normalise(em->d_ss + lo * kpad, em->d_ss + table + SS_TAIL, em->K, (int)rows_per_rank, em->lay,
+                                  em->d_log_beta_wk + lo * kpad, em->d_beta_scaled + lo * kpad, em->d_lbmax + lo, em->stream,
+                                  &launches[(size_t)i]);
+        if (rc != ONILDA_OK) return rc;
+        ONILDA_CUDA(cudaEventRecord(em->ev_c2, em->stream));
+    }
+    if (P > 1) {
+        NCCL_TRY(nccl->GroupStart());
+        for (int i = 0; i < n; i++) {
+            onilda_em* em = ems[i];
+            const size_t cnt = (size_t)rows_per_rank * kpad, lo = (size_t)em->rank * rows_per_rank;
+            NCCL_TRY(nccl->AllGather(em->d_log_beta_wk + lo * kpad, em->d_log_beta_wk, cnt, ncclDouble, em->comm, em->stream));
+            NCCL_TRY(nccl->AllGather(em->d_beta_scaled + lo * kpad, em->d_beta_scaled, cnt, ncclDouble, em->comm, em->stream));
+            NCCL_TRY(nccl->AllGather(em->d_lbmax + lo, em->d_lbmax, (size_t)rows_per_rank, ncclDouble, em->comm, em->stream));
+        }
+        NCCL_TRY(nccl->GroupEnd());
+    }
+#undef NCCL_TRY
+    std::vector<double> tails((size_t)n * SS_TAIL);
+    std::vector<int> errs((size_t)n, 0);
+    for (int i = 0; i < n; i++) {
+        onilda_em* em = ems[i];
+        ONILDA_CUDA(cudaSetDevice(em->device));
+        ONILDA_CUDA(cudaEventRecord(em->ev_c3, em->stream));
+        ONILDA_CUDA(cudaMemcpyAsync(&tails[(size_t)i * SS_TAIL], em->d_ss + table, sizeof(double) * SS_TAIL, cudaMemcpyDeviceToHost, em->stream));
+        ONILDA_CUDA(cudaMemcpyAsync(&errs[(size_t)i], em->d_error, sizeof(int), cudaMemcpyDeviceToHost, em->stream));
+        ONILDA_CUDA(cudaEventRecord(em->ev3, em->stream));
+    }
+    for (int i = 0; i < n; i++) {
+        onilda_em* em = ems[i];
+        ONILDA_CUDA(cudaSetDevice(em->device));
+        ONILDA_CUDA(cudaStreamSynchronize(em->stream));
+        em->launches += launches[(size_t)i];
+        em->estep_done = 0;
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, em->ev0, em->ev1) == cudaSuccess) em->estep_ms = ms;
+        if (em->timing) {
+            float tl = 0, tb = 0;
+            if (em->num_long > 0) cudaEventElapsedTime(&tl, em->ev0, em->ev_long_end);
+            cudaEventElapsedTime(&tb, em->ev0, em->ev_bulk_end);
+            fprintf(stderr, "[onilda] E-step %.2f ms: long-document launch ended at %.2f ms, bulk launch at %.2f ms\n",
+                    em->estep_ms, tl, tb);
+        }
+        if (cudaEventElapsedTime(&ms, em->ev2, em->ev3) == cudaSuccess) em->mstep_ms = ms;
+        if (cudaEventElapsedTime(&ms, em->ev_c0, em->ev_c1) == cudaSuccess) em->rs_ms = ms;
+        if (cudaEventElapsedTime(&ms, em->ev_c2, em->ev_c3) == cudaSuccess) em->ag_ms = ms;
+        cudaGetLastError();
+    }
+    for (int i = 0; i < n; i++)
+        if (errs[(size_t)i] || isnan(tails[(size_t)i * SS_TAIL + SS_LIK]))
+            return onilda_fail(ONILDA_ENAN, "NaN likelihood in the E-step (the reference asserts at lda-inference.c:78)");
+
+    // every shard holds the same reduced scalars; the host part of lda_mle and run_em's bookkeeping
+    // (lda-model.c:45-53, lda-estimate.c:186-188, 260-262) runs once and is copied to each handle
+    const double* tail = tails.data();
+    const double lik = tail[SS_LIK];
+    onilda_em* e0 = ems[0];
+    double alpha = e0->alpha;
+    if (e0->settings.estimate_alpha == 1) alpha = onilda_opt_alpha(tail[SS_ALPHA], (int)llround(tail[SS_NDOCS]), e0->K);
+    const double conv = (e0->likelihood_old - lik) / (e0->likelihood_old);
+    for (int i = 0; i < n; i++) {
+        onilda_em* em = ems[i];
+        em->alpha = alpha;
+        em->iteration++;
+        em->converged = conv;
+        if (em->converged < 0) em->var_max_iter = em->var_max_iter * 2;
+        em->likelihood_old = lik;
+    }
+    if (likelihood) *likelihood = lik;
+    if (converged) *converged = conv;
+    if (keep_going)
+        *keep_going = ((e0->converged < 0) || (e0->converged > e0->settings.em_converged) || (e0->iteration <= 2)) &&
+                      (e0->iteration <= e0->settings.em_max_iter);
+    return ONILDA_OK;
+}
+
 extern "C" int onilda_em_mstep(onilda_em* em, double* likelihood, double* converged, int* keep_going)
 {
-    if (!em) return onilda_fail(ONILDA_EINVAL, "em_mstep: null handle");
-    if (!em->estep_done) return onilda_fail(ONILDA_EINVAL, "em_mstep: call onilda_em_estep first");
-    DeviceGuard g(em->device);
-    const size_t table = (size_t)em->V * em->lay.kpad;
-    int l = 0;
-    ONILDA_CUDA(cudaEventRecord(em->ev2, em->stream));
-    int rc = launch_mstep(em->d_ss, em->K, em->V, em->lay, em->d_partial, em->d_class_total, em->d_log_beta_wk,
-                          em->d_beta_scaled, em->d_lbmax, em->stream, &l);
-    if (rc != ONILDA_OK) return rc;
-    double tail[SS_TAIL];
-    int err = 0;
-    ONILDA_CUDA(cudaMemcpyAsync(tail, em->d_ss + table, sizeof tail, cudaMemcpyDeviceToHost, em->stream));
-    ONILDA_CUDA(cudaMemcpyAsync(&err, em->d_error, sizeof err, cudaMemcpyDeviceToHost, em->stream));
-    ONILDA_CUDA(cudaEventRecord(em->ev3, em->stream));
-    ONILDA_CUDA(cudaStreamSynchronize(em->stream));
-    em->launches += l;
-    em->estep_done = 0;
-    float ms = 0;
-    if (cudaEventElapsedTime(&ms, em->ev0, em->ev1) == cudaSuccess) em->estep_ms = ms;
-    if (em->timing) {
-        float tl = 0, tb = 0;
-        if (em->num_long > 0) cudaEventElapsedTime(&tl, em->ev0, em->ev_long_end);
-        cudaEventElapsedTime(&tb, em->ev0, em->ev_bulk_end);
-        fprintf(stderr, "[onilda] E-step %.2f ms: long-document launch ended at %.2f ms, bulk launch at %.2f ms\n",
-                em->estep_ms, tl, tb);
-    }
-    if (cudaEventElapsedTime(&ms, em->ev2, em->ev3) == cudaSuccess) em->mstep_ms = ms;
-    cudaGetLastError();
-    if (err || isnan(tail[SS_LIK])) return onilda_fail(ONILDA_ENAN, "NaN likelihood in the E-step (the reference asserts at lda-inference.c:78)");
+    return mstep_group(&em, 1, likelihood, converged, keep_going);
+}
 
-    const double lik = tail[SS_LIK];
-    // lda_mle's alpha part (lda-model.c:45-53): Newton on the host, D as int
-    if (em->settings.estimate_alpha == 1) em->alpha = onilda_opt_alpha(tail[SS_ALPHA], (int)llround(tail[SS_NDOCS]), em->K);
-    // lda-estimate.c:186-188, 260-262
-    em->iteration++;
-    em->converged = (em->likelihood_old - lik) / (em->likelihood_old);
-    if (em->converged < 0) em->var_max_iter = em->var_max_iter * 2;
-    em->likelihood_old = lik;
-    if (likelihood) *likelihood = lik;
-    if (converged) *converged = em->converged;
-    if (keep_going)
-        *keep_going = ((em->converged < 0) || (em->converged > em->settings.em_converged) || (em->iteration <= 2)) &&
-                      (em->iteration <= em->settings.em_max_iter);
+extern "C" int onilda_em_mstep_group(onilda_em** ems, int n, double* likelihood, double* converged, int* keep_going)
+{
+    if (!ems || n <= 0) return onilda_fail(ONILDA_EINVAL, "em_mstep_group: no handles");
+    return mstep_group(ems, n, likelihood, converged, keep_going);
+}
+
+extern "C" int onilda_comm_unique_id(unsigned char* id)
+{
+    if (!id) return onilda_fail(ONILDA_EINVAL, "comm_unique_id: null argument");
+    static_assert(sizeof(ncclUniqueId) == ONILDA_COMM_ID_BYTES, "ONILDA_COMM_ID_BYTES must be NCCL's unique-id size");
+    const NcclApi* nccl = nccl_api();
+    if (!nccl) return ONILDA_ECUDA;
+    ncclUniqueId u;
+    ncclResult_t r = nccl->GetUniqueId(&u);
+    if (r != ncclSuccess) return onilda_fail(ONILDA_ECUDA, "ncclGetUniqueId: %s", nccl->GetErrorString(r));
+    memcpy(id, &u, sizeof u);
+    return ONILDA_OK;
+}
+
+extern "C" int onilda_em_comm_attach(onilda_em* em, const unsigned char* id, int nranks, int rank)
+{
+    if (!em || !id) return onilda_fail(ONILDA_EINVAL, "em_comm_attach: null argument");
+    if (nranks < 1 || nranks > kTablePadRows || rank < 0 || rank >= nranks)
+        return onilda_fail(ONILDA_EINVAL, "em_comm_attach: rank %d of %d (1..%d ranks)", rank, nranks, (int)kTablePadRows);
+    if (em->comm) return onilda_fail(ONILDA_EINVAL, "em_comm_attach: the handle already has a communicator");
+    if (nranks == 1) return ONILDA_OK;
+    const NcclApi* nccl = nccl_api();
+    if (!nccl) return ONILDA_ECUDA;
+    DeviceGuard g(em->device);
+    ncclUniqueId u;
+    memcpy(&u, id, sizeof u);
+    ncclResult_t r = nccl->CommInitRank(&em->comm, nranks, u, rank);
+    if (r != ncclSuccess) { em->comm = nullptr; return onilda_fail(ONILDA_ECUDA, "ncclCommInitRank: %s", nccl->GetErrorString(r)); }
+    em->nranks = nranks;
+    em->rank = rank;
+    return ONILDA_OK;
+}
+
+extern "C" int onilda_em_comm_attach_local(onilda_em** ems, int n)
+{
+    if (!ems || n < 1 || n > kTablePadRows) return onilda_fail(ONILDA_EINVAL, "em_comm_attach_local: 1..%d handles", (int)kTablePadRows);
+    if (n == 1) return ONILDA_OK;
+    std::vector<int> devs((size_t)n);
+    for (int i = 0; i < n; i++) {
+        if (!ems[i] || ems[i]->comm) return onilda_fail(ONILDA_EINVAL, "em_comm_attach_local: null handle or communicator present");
+        devs[(size_t)i] = ems[i]->device;
+    }
+    const NcclApi* nccl = nccl_api();
+    if (!nccl) return ONILDA_ECUDA;
+    std::vector<ncclComm_t> comms((size_t)n);
+    ncclResult_t r = nccl->CommInitAll(comms.data(), n, devs.data());
+    if (r != ncclSuccess) return onilda_fail(ONILDA_ECUDA, "ncclCommInitAll: %s", nccl->GetErrorString(r));
+    for (int i = 0; i < n; i++) {
+        ems[i]->comm = comms[(size_t)i];
+        ems[i]->nranks = n;
+        ems[i]->rank = i;
+    }
+    return ONILDA_OK;
+}
+
+// The exchange of one M-step by itself: `repeats` reduce-scatters of the statistics table and as many rounds of the
+// three all-gathers, each set behind a barrier-like small all-reduce and timed with events on the handle's stream.
+// The statistics buffer is left undefined (the next E-step clears it); the model tables are gathered onto themselves.
+extern "C" int onilda_em_collective_time(onilda_em** ems, int n, int repeats, double* rs_ms, double* ag_ms, int64_t* bytes)
+{
+    if (!ems || n <= 0 || repeats <= 0) return onilda_fail(ONILDA_EINVAL, "em_collective_time: bad argument");
+    const int P = ems[0]->nranks;
+    if (P < 2 || !ems[0]->comm) return onilda_fail(ONILDA_EINVAL, "em_collective_time: no communicator attached");
+    const NcclApi* nccl = nccl_api();
+    if (!nccl) return ONILDA_ECUDA;
+    int prev = 0;
+    ONILDA_CUDA(cudaGetDevice(&prev));
+    struct Restore { int d; ~Restore() { cudaSetDevice(d); } } restore{prev};
+    const int kpad = ems[0]->lay.kpad;
+    const size_t table = table_doubles(ems[0]);
+    const size_t rows = (size_t)(((int64_t)ems[0]->V + P - 1) / P), cnt = rows * kpad;
+#define NCCL_TRY(call)                                                                                              \
+    do {                                                                                                            \
+        ncclResult_t r__ = (call);                                                                                  \
+        if (r__ != ncclSuccess) return onilda_fail(ONILDA_ECUDA, "%s failed: %s", #call, nccl->GetErrorString(r__)); \
+    } while (0)
+    for (int phase = 0; phase < 2; phase++) {
+        NCCL_TRY(nccl->GroupStart());
+        for (int i = 0; i < n; i++)
+            NCCL_TRY(nccl->AllReduce(ems[i]->d_ss + table, ems[i]->d_ss + table, 1, ncclDouble, ncclSum, ems[i]->comm, ems[i]->stream));
+        NCCL_TRY(nccl->GroupEnd());
+        for (int i = 0; i < n; i++) { ONILDA_CUDA(cudaSetDevice(ems[i]->device)); ONILDA_CUDA(cudaEventRecord(ems[i]->ev_c0, ems[i]->stream)); }
+        for (int it = 0; it < repeats; it++) {
+            NCCL_TRY(nccl->GroupStart());
+            for (int i = 0; i < n; i++) {
+                onilda_em* em = ems[i];
+                const size_t lo = (size_t)em->rank * rows;
+                if (phase == 0) {
+                    NCCL_TRY(nccl->ReduceScatter(em->d_ss, em->d_ss + lo * kpad, cnt, ncclDouble, ncclSum, em->comm, em->stream));
+                } else {
+                    NCCL_TRY(nccl->AllGather(em->d_log_beta_wk + lo * kpad, em->d_log_beta_wk, cnt, ncclDouble, em->comm, em->stream));
+                    NCCL_TRY(nccl->AllGather(em->d_beta_scaled + lo * kpad, em->d_beta_scaled, cnt, ncclDouble, em->comm, em->stream));
+                    NCCL_TRY(nccl->AllGather(em->d_lbmax + lo, em->d_lbmax, rows, ncclDouble, em->comm, em->stream));
+                }
+            }
+            NCCL_TRY(nccl->GroupEnd());
+        }
+        double worst = 0;
+        for (int i = 0; i < n; i++) {
+            ONILDA_CUDA(cudaSetDevice(ems[i]->device));
+            ONILDA_CUDA(cudaEventRecord(ems[i]->ev_c1, ems[i]->stream));
+            ONILDA_CUDA(cudaStreamSynchronize(ems[i]->stream));
+            float ms = 0;
+            ONILDA_CUDA(cudaEventElapsedTime(&ms, ems[i]->ev_c0, ems[i]->ev_c1));
+            if (ms > worst) worst = ms;
+        }
+        if (phase == 0 && rs_ms) *rs_ms = worst / repeats;
+        if (phase == 1 && ag_ms) *ag_ms = worst / repeats;
+    }
+#undef NCCL_TRY
+    if (bytes) *bytes = (int64_t)(cnt * P * sizeof(double));
+    return ONILDA_OK;
+}
+
+extern "C" int onilda_em_comm_stats(onilda_em* em, int* nranks, int* rank, double* reduce_scatter_ms, double* all_gather_ms)
+{
+    if (!em) return onilda_fail(ONILDA_EINVAL, "em_comm_stats: null handle");
+    if (nranks) *nranks = em->nranks;
+    if (rank) *rank = em->rank;
+    if (reduce_scatter_ms) *reduce_scatter_ms = em->rs_ms;
+    if (all_gather_ms) *all_gather_ms = em->ag_ms;
     return ONILDA_OK;
 }
 

@@ -86,8 +86,9 @@ extern "C" int onilda_em_allreduce_peer(onilda_em** ems, int n)
         if (hi > count) hi = count;
         if (lo >= hi) continue;
         ONILDA_CUDA(cudaSetDevice(dev[r]));
-        int blocks = (int)((hi - lo + 255) / 256);
-        if (blocks > 148 * 8) blocks = 148 * 8;
+        int blocks = (int)((hi - lo + 255) / 256), sms = 0;
+        ONILDA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev[r]));
+        if (blocks > sms * 8) blocks = sms * 8;
         peer_sum_kernel<<<blocks, 256, 0, st[r]>>>(p, lo, hi);
         ONILDA_CUDA(cudaGetLastError());
     }
@@ -170,6 +171,14 @@ extern "C" int onilda_run_em(const char* start, const char* directory, const oni
         set.ems.push_back(em);
     }
 
+    // several devices: NCCL reduce-scatter -> lda_mle of the own rows -> all-gather (em.cu), unless
+    // ONILDA_ALLREDUCE=peer asks for the fixed-order peer-memory sum
+    const char* env_ar = getenv("ONILDA_ALLREDUCE");
+    const bool peer_sum = env_ar && strcmp(env_ar, "peer") == 0;
+    if (ndev > 1 && !peer_sum) {
+        rc = onilda_em_comm_attach_local(set.ems.data(), ndev);
+        if (rc != ONILDA_OK) { onilda_model_free(model); return rc; }
+    }
     FILE* lf = fopen((dir + "/likelihood.dat").c_str(), "w");
     if (!lf) { onilda_model_free(model); return onilda_fail(ONILDA_EIO, "cannot write %s/likelihood.dat", directory); }
 
@@ -181,10 +190,15 @@ extern "C" int onilda_run_em(const char* start, const char* directory, const oni
         iter++;
         printf("**** em iteration %d ****\n", iter);
         for (onilda_em* em : set.ems) { rc = onilda_em_estep(em); if (rc != ONILDA_OK) break; }
-        if (rc == ONILDA_OK && ndev > 1) rc = onilda_em_allreduce_peer(set.ems.data(), ndev);
         double lik = 0, conv = 0;
-        if (rc == ONILDA_OK)
-            for (onilda_em* em : set.ems) { rc = onilda_em_mstep(em, &lik, &conv, &keep); if (rc != ONILDA_OK) break; }
+        if (rc == ONILDA_OK && peer_sum) {
+            // the deterministic alternative: fixed-order sums over peer memory, then the whole M-step on every device
+            if (ndev > 1) rc = onilda_em_allreduce_peer(set.ems.data(), ndev);
+            if (rc == ONILDA_OK)
+                for (onilda_em* em : set.ems) { rc = onilda_em_mstep(em, &lik, &conv, &keep); if (rc != ONILDA_OK) break; }
+        } else if (rc == ONILDA_OK) {
+            rc = onilda_em_mstep_group(set.ems.data(), ndev, &lik, &conv, &keep);
+        }
         if (rc != ONILDA_OK) break;
         fprintf(lf, "%10.10f\t%5.5e\n", lik, conv);   // lda-estimate.c:266
         fflush(lf);

@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(ONILDA_ESTEP_MAX_THREADS) estep_kernel(EStepAr
     const int j = lane % G;
     const int K = KC ? KC : a.num_topics;
     const uint32_t KS = KC ? (uint32_t)kpad_for(KC) : (uint32_t)a.kstride;
-    const int32_t idle_word = a.num_terms;     // table row V: beta' = 1, lbmax = 0
+    const int32_t idle_word = a.idle_row;      // beta' = 1, lbmax = 0
     const double inv_K = 1.0 / K;
     bool valid[TPL];
     double start_phi[TPL];                     // phi before the first sweep: 1/K (lda-inference.c:41)

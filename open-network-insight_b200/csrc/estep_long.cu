@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
     const int lane = threadIdx.x & 31;
     const int K = KC ? KC : a.num_topics;
     const uint32_t KS = KC ? (uint32_t)kpad_for(KC) : (uint32_t)a.kstride;
-    const int32_t idle_word = a.num_terms;
+    const int32_t idle_word = a.idle_row;
     const bool valid = lane < K;
     const double inv_K = 1.0 / K;
 

@@ -42,6 +42,9 @@ inline bool choose_layout(int K, TopicLayout* out)
 
 // Tail of the packed sufficient-statistics buffer, after the V*kpad table.
 enum { SS_LIK = 0, SS_ALPHA = 1, SS_NDOCS = 2, SS_SPARE = 3, SS_TAIL = 4 };
+// The tables carry kTablePadRows spare rows after row V: with P <= 16 ranks each owning ceil(V/P) rows, the
+// reduce-scatter / all-gather of the distributed M-step covers at most V + 15 rows; the idle row sits behind them.
+enum { kTablePadRows = 16 };
 
 struct EStepArgs {
     // corpus shard, CSR, offsets local to the shard (offsets[0] == 0)
@@ -58,7 +61,8 @@ struct EStepArgs {
     const void* psi_tab;        // device_math.cuh PsiRow[kPsiRows] (hostmath.c builds it)
     const double* exp_tab;      // 2^(i/64), i < 64
     int num_topics;
-    int num_terms;              // V; row V of beta_scaled / lbmax is the idle row (beta' = 1 for k < K, lbmax = 0)
+    int num_terms;              // V
+    int idle_row;               // row of beta_scaled / lbmax with beta' = 1 for k < K and lbmax = 0: what an idle group reads
     int kstride;                // row stride of the tables and of phi, in doubles (TopicLayout::kpad)
     double alpha;
     double lik_const;           // lgamma(alpha*K) - K*lgamma(alpha)
@@ -86,8 +90,10 @@ int launch_tables_from_log_beta(const double* log_beta_kv, int K, int V, const T
                                 double* beta_scaled, double* lbmax, cudaStream_t stream, int* launches);
 int launch_reduce_doc_stats(const double* doc_lik, const double* doc_alpha_ss, int64_t num_docs, double* partial,
                             double* ss_tail, cudaStream_t stream, int* launches);
-int launch_mstep(const double* class_word, int K, int V, const TopicLayout& lay, double* partial, double* class_total,
-                 double* log_beta_wk, double* beta_scaled, double* lbmax, cudaStream_t stream, int* launches);
+int launch_column_sums(const double* table, int rows, const TopicLayout& lay, int sm_count, double* partial, double* total,
+                       cudaStream_t stream, int* launches);
+int launch_normalise(const double* class_word, const double* class_total, int K, int rows, const TopicLayout& lay,
+                     double* log_beta_wk, double* beta_scaled, double* lbmax, cudaStream_t stream, int* launches);
 int launch_export_log_beta(const double* log_beta_wk, int K, int V, const TopicLayout& lay, double* log_beta_kv,
                            cudaStream_t stream, int* launches);
 int mstep_partial_doubles(int V, const TopicLayout& lay, int64_t num_docs);

@@ -13,7 +13,7 @@
 
 namespace onilda {
 
-static constexpr int kColBlocks = 592;   // 4 x 148 SMs
+static constexpr int kMaxColBlocks = 1024;   // partial[] is sized for this many; launches use 4 x the SM count
 static constexpr int kColThreads = 256;
 
 // partial[b][k] = sum over this block's words of table[w][k]
@@ -141,7 +141,7 @@ __global__ void doc_final_kernel(const double* __restrict__ partial, int nblocks
 int mstep_partial_doubles(int V, const TopicLayout& lay, int64_t num_docs)
 {
     (void)V; (void)num_docs;
-    int a = kColBlocks * lay.kpad, b = 2 * kDocBlocks;
+    int a = kMaxColBlocks * lay.kpad, b = 2 * kDocBlocks;
     return a > b ? a : b;
 }
 
@@ -178,19 +178,35 @@ int launch_reduce_doc_stats(const double* doc_lik, const double* doc_alpha_ss, i
     return ONILDA_OK;
 }
 
-int launch_mstep(const double* class_word, int K, int V, const TopicLayout& lay, double* partial, double* class_total,
-                 double* log_beta_wk, double* beta_scaled, double* lbmax, cudaStream_t stream, int* launches)
+static int col_blocks(int sm_count)
 {
-    if (V == 0) return ONILDA_OK;
+    int b = 4 * (sm_count > 0 ? sm_count : 1);
+    return b > kMaxColBlocks ? kMaxColBlocks : b;
+}
+
+// class_total[k] = sum over `rows` table rows of column k, in a fixed order (two stages)
+int launch_column_sums(const double* table, int rows, const TopicLayout& lay, int sm_count, double* partial, double* total,
+                       cudaStream_t stream, int* launches)
+{
+    const int blocks = col_blocks(sm_count);
     const size_t shmem = sizeof(double) * (size_t)(kColThreads / lay.kpad) * lay.kpad;
-    column_partial_kernel<<<kColBlocks, kColThreads, shmem, stream>>>(class_word, V, lay.kpad, partial);
+    column_partial_kernel<<<blocks, kColThreads, shmem, stream>>>(table, rows, lay.kpad, partial);
     ONILDA_CUDA(cudaGetLastError());
-    column_final_kernel<<<blocks_for(lay.kpad, 64), 64, 0, stream>>>(partial, kColBlocks, lay.kpad, class_total);
+    column_final_kernel<<<blocks_for(lay.kpad, 64), 64, 0, stream>>>(partial, blocks, lay.kpad, total);
     ONILDA_CUDA(cudaGetLastError());
-    normalise_kernel<<<blocks_for(V, 256), 256, 0, stream>>>(class_word, class_total, K, V, lay.kpad, log_beta_wk,
-                                                             beta_scaled, lbmax);
+    if (launches) *launches += 2;
+    return ONILDA_OK;
+}
+
+// lda_mle over `rows` rows (all pointers already at the first of them)
+int launch_normalise(const double* class_word, const double* class_total, int K, int rows, const TopicLayout& lay,
+                     double* log_beta_wk, double* beta_scaled, double* lbmax, cudaStream_t stream, int* launches)
+{
+    if (rows <= 0) return ONILDA_OK;
+    normalise_kernel<<<blocks_for(rows, 256), 256, 0, stream>>>(class_word, class_total, K, rows, lay.kpad, log_beta_wk,
+                                                                beta_scaled, lbmax);
     ONILDA_CUDA(cudaGetLastError());
-    if (launches) *launches += 3;
+    if (launches) *launches += 1;
     return ONILDA_OK;
 }
 

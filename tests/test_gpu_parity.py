@@ -397,17 +397,21 @@ def test_top1000_overlap_after_em(oni, oracle, corpusgen):
     em.close()
 
 
-def test_two_gpu_lda_est_matches_one_gpu(oni, tmp_path):
-    """`lda est ... 2 ...`: documents sharded over two devices, statistics summed over NVLink peer memory
-    (replaces the MPI_Allreduce calls of lda-estimate.c:211-252); results must not depend on the GPU count."""
+@pytest.mark.parametrize("exchange", ["nccl", "peer"])
+def test_two_gpu_lda_est_matches_one_gpu(oni, tmp_path, exchange):
+    """`lda est ... 2 ...`: documents sharded over two devices; the statistics go through NCCL (reduce-scatter ->
+    lda_mle of the own rows -> all-gather) or, with ONILDA_ALLREDUCE=peer, through the fixed-order sum over peer
+    memory (both replace the MPI_Allreduce calls of lda-estimate.c:211-252); results must not depend on the GPU count."""
     if oni.device_count() < 2:
         pytest.skip("needs two GPUs")
+    import os
     d = GOLD / "k20"
     outs = []
+    env = dict(os.environ, ONILDA_ALLREDUCE=exchange)
     for ndev in (1, 2):
         out = tmp_path / f"out{ndev}"
         r = subprocess.run([str(oni.LDA_BIN), "est", "2.5", "20", str(d / "settings.txt"), str(ndev), str(d / "c.dat"),
-                            str(d / "000"), str(out)], capture_output=True, text=True)
+                            str(d / "000"), str(out)], capture_output=True, text=True, env=env)
         assert r.returncode == 0, r.stderr
         outs.append(out)
     l1, l2 = np.loadtxt(outs[0] / "likelihood.dat", ndmin=2), np.loadtxt(outs[1] / "likelihood.dat", ndmin=2)
@@ -417,6 +421,43 @@ def test_two_gpu_lda_est_matches_one_gpu(oni, tmp_path):
     assert np.max(np.abs(l2[:, 0] - l1[:, 0]) / np.abs(l1[:, 0])) < 1e-12
     assert rel_err(read_matrix(outs[1] / "final.beta"), read_matrix(d / "final.beta"), 1e-2) < MODEL_RTOL
     assert rel_err(read_matrix(outs[1] / "final.gamma"), read_matrix(d / "final.gamma"), 1e-3) < MODEL_RTOL
+
+
+def test_two_gpu_fused_mstep_in_process(oni, corpusgen):
+    """Two shards on two devices with a communicator: estep on both, then ONE grouped M-step (reduce-scatter,
+    lda_mle of the own rows, all-gather) against the single-device run; vocabulary not a multiple of the rank
+    count, so the padding rows of the scatter are exercised; then the exchange timed by itself."""
+    if oni.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    g = corpusgen.generate(3000, 40, 801, 20, seed=8, hub_tokens=3000)
+    c = oni.Corpus.from_csr(g.offsets, g.words, g.counts, num_terms=801)
+    m = oni.Model.new(20, c.num_terms)
+    m.init_random(4)
+    m.alpha = 2.5
+    st = oni.Settings(20, 1e-6, 3, 1e-6, 1)
+    one = oni.EM(c, m, st, device=0)
+    a = oni.EM(c, m, st, device=0, doc_begin=0, doc_end=1300)
+    b = oni.EM(c, m, st, device=1, doc_begin=1300, doc_end=3000)
+    oni.comm_attach_local([a, b])
+    for _ in range(3):
+        l1, c1, k1 = one.iterate()
+        a.estep()
+        b.estep()
+        lg, cg, kg = oni.mstep_group([a, b])
+        assert kg == k1 and abs(lg - l1) / abs(l1) < 1e-12
+    for e in (a, b):
+        assert rel_err(e.model().log_beta, one.model().log_beta, 1e-6) < 1e-9
+        assert abs(e.model().alpha - one.model().alpha) < 1e-12
+    assert rel_err(np.vstack([a.gamma(), b.gamma()]), one.gamma(), 1e-9) < 1e-9
+    t = oni.collective_time([a, b], repeats=3)
+    assert t["reduce_scatter_ms"] > 0 and t["all_gather_ms"] > 0 and t["table_bytes"] == 2 * 401 * 20 * 8
+    assert oni.comm_stats(a)["nranks"] == 2 and oni.comm_stats(b)["rank"] == 1
+    # the handles still work after the timing exchange (the next E-step clears the statistics)
+    a.estep()
+    b.estep()
+    oni.mstep_group([a, b])
+    for e in (one, a, b):
+        e.close()
 
 
 def test_degenerate_shapes(oni, oracle):
