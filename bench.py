@@ -3,25 +3,29 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
-A "step" is one EM iteration (E-step + sufficient-statistics sum + M-step) over
-the synthetic one-day netflow corpus of BASELINE.json configs[1]: 1M IP
-documents, ~100M tokens, V = 100k flow words, K = 20, lda-c's default settings.
-At N > 1 (torchrun, one rank per GPU) every rank holds its own 1M-document
-shard (weak scaling) and the packed statistics are summed with one NCCL
-all-reduce per iteration.
+A "step" is one EM iteration (E-step + sufficient-statistics exchange + M-step) over the synthetic one-day
+netflow corpus of BASELINE.json configs[1]: 1M IP documents, ~100M tokens, V = 100k flow words, K = 20, lda-c's
+default settings.  At N > 1 (torchrun, one rank per GPU) the headline `value` keeps round 1's meaning - every rank
+holds its own 1M-document corpus (weak scaling) - and the statistics go through the library's own NCCL exchange
+(reduce-scatter -> lda_mle of the own rows -> all-gather, csrc/em.cu).  North_star's split - ONE corpus sharded over
+the N GPUs - is measured beside it in `strong`, with the exchange timed by itself (bus GB/s), the longest document
+and its lone-warp time; `strong_dns` does the same for configs[2]; `scoring.sharded` shards configs[4]'s events.
 
-Prints ONE JSON line (see the contract in the task statement).  `value` is
-measured with the corpus resident in HBM; `e2e` runs the same iterations through
-the C ABI with HOST buffers (corpus + model copied host->device and model + gamma
-device->host inside every timed step).  `roofline` is for the E-step kernel;
-`cpu_baseline` is the unmodified reference lda-c (oracle/_ref/lda) timed on this
-box's host cores on a bounded sample of the same corpus.
+Prints ONE JSON line (contract in the task statement).  `value` is measured with the corpus resident in HBM;
+`e2e` runs the same iterations through the C ABI with HOST buffers (corpus + model host->device and model + gamma
+device->host inside every timed step).  `roofline` is for the E-step; `cpu_baseline` is the unmodified reference
+lda-c (oracle/_ref/lda) on this box's host cores on a bounded document prefix, `parity` compares that very run's
+likelihood.dat / final.gamma / final.beta / top-1000 events with the GPU path on the same documents.
 
-PyTorch is plumbing here (synthetic-data generation on the GPU, pinned host
-buffers, torch.distributed/NCCL); every timed kernel is libonilda's.
+`--impl reference` times the unmodified reference only: that process never loads libonilda (its inputs are written
+with numpy); PyTorch generates the synthetic corpus there as here.
+
+PyTorch is plumbing (synthetic data on the GPU, pinned host buffers, torch.distributed for rendezvous and for the
+arithmetic of the max-over-ranks timing); every timed kernel is libonilda's.
 """
 import argparse
 import importlib
+import importlib.util
 import json
 import os
 import subprocess
@@ -164,21 +168,66 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def time_reference(oni, corpus, model0, n_docs, n_iters, nproc, workdir):
-    """Runs the UNMODIFIED reference (oracle/_ref/lda; fork-based MPI stand-in with `nproc`
-    ranks) for n_iters EM iterations on the first n_docs documents, from the same start
-    model, and returns the per-iteration seconds read off its own progress lines."""
+def start_model_numpy(K, V, seed):
+    """A random start as random_initialize_ss + lda_mle make it (lda-model.c:104-116, 27-44): class_word =
+    1/V + U[0,1), log-normalised per topic.  numpy's generator, so both arms can write it without libonilda."""
+    rng = np.random.default_rng(seed)
+    cw = 1.0 / V + rng.random((K, V))
+    return ALPHA0, np.log(cw) - np.log(cw.sum(axis=1, keepdims=True))
+
+
+def write_model_text(root, alpha, log_beta):
+    """<root>.beta / <root>.other in save_lda_model's format (lda-model.c:193-217)."""
+    K, V = log_beta.shape
+    np.savetxt(str(root) + ".beta", log_beta, fmt=" %5.10f", delimiter="")
+    Path(str(root) + ".other").write_text(f"num_topics {K}\nnum_terms {V}\nalpha {alpha:5.10f}\n")
+
+
+def write_dat_numpy(path, offsets, words, counts, n_docs):
+    """The first n_docs documents as a .dat file, built with numpy only.  read_data is token based and takes
+    "%10d" fields (lda-data.c:22-59): numbers are written zero-padded to a fixed width so that the whole file is
+    one vectorised byte fill: "\\n<7-digit length>" per document, " <7-digit word>:<6-digit count>" per entry."""
+    off = np.asarray(offsets[:n_docs + 1], np.int64)
+    n = int(off[-1])
+    w = np.asarray(words[:n], np.int64)
+    c = np.asarray(counts[:n], np.int64)
+    assert n_docs == 0 or (np.diff(off).max() < 10 ** 7 and (n == 0 or (w.max() < 10 ** 7 and c.max() < 10 ** 6)))
+
+    def digits(v, width):
+        return ((v[:, None] // (10 ** np.arange(width - 1, -1, -1, dtype=np.int64))) % 10 + 48).astype(np.uint8)
+    HW, EW = 8, 15
+    head = np.empty((n_docs, HW), np.uint8)
+    head[:, 0] = 10
+    head[:, 1:] = digits(np.diff(off), 7)
+    ent = np.empty((n, EW), np.uint8)
+    ent[:, 0] = 32
+    ent[:, 1:8] = digits(w, 7)
+    ent[:, 8] = 58
+    ent[:, 9:] = digits(c, 6)
+    out = np.empty(n_docs * HW + n * EW + 1, np.uint8)
+    doc_of = np.repeat(np.arange(n_docs, dtype=np.int64), np.diff(off))
+    out[(np.arange(n_docs, dtype=np.int64) * HW + off[:-1] * EW)[:, None] + np.arange(HW)] = head
+    out[(np.arange(n, dtype=np.int64) * EW + (doc_of + 1) * HW)[:, None] + np.arange(EW)] = ent
+    out[-1] = 10
+    out.tofile(str(path))
+
+
+def run_reference(workdir, offsets, words, counts, n_docs, K, V, n_iters, nproc, start):
+    """Runs the UNMODIFIED reference (oracle/_ref/lda; fork-based MPI stand-in with `nproc` ranks) for n_iters EM
+    iterations on the first n_docs documents from the start model `start` = (alpha, log_beta).  Inputs are written
+    with numpy.  Returns (seconds per iteration read off its own progress lines, output directory) or None."""
     ref_bin = ROOT / "oracle" / "_ref" / "lda"
     if not ref_bin.exists():
         return None
     work = Path(workdir)
-    corpus.save_dat(work / "sample.dat", 0, n_docs)
-    model0.save(work / "000")
+    write_dat_numpy(work / "sample.dat", offsets, words, counts, n_docs)
+    write_model_text(work / "000", *start)
     (work / "settings.txt").write_text(
         f"var max iter 20\nvar convergence 1e-6\nem max iter {n_iters - 1}\nem convergence 1e-6\nalpha estimate\n")
-    env = dict(os.environ, ONI_MPI_STUB_NP=str(nproc), ONI_MPI_STUB_MAXCOUNT=str(max(model0.num_terms, 1 << 16)))
-    cmd = ["stdbuf", "-oL", str(ref_bin), "est", str(ALPHA0), str(model0.num_topics), "settings.txt", str(nproc),
-           "sample.dat", "000", "out"]
+    env = dict(os.environ, ONI_MPI_STUB_NP=str(nproc), ONI_MPI_STUB_MAXCOUNT=str(max(V, 1 << 16)))
+    if nproc <= 1:
+        env.pop("ONI_MPI_STUB_NP")
+    cmd = ["stdbuf", "-oL", str(ref_bin), "est", str(ALPHA0), str(K), "settings.txt", str(nproc), "sample.dat", "000", "out"]
     starts, ends = [], []
     p = subprocess.Popen(cmd, cwd=work, env=env, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
     for line in p.stdout:
@@ -190,7 +239,7 @@ def time_reference(oni, corpus, model0, n_docs, n_iters, nproc, workdir):
     p.wait()
     if p.returncode != 0 or not starts or len(ends) < len(starts):
         return None
-    return [e - s for s, e in zip(starts, ends)]
+    return [e - s for s, e in zip(starts, ends)], work / "out"
 
 
 def reference_sample_docs(corpus_offsets, cores, target_seconds=8.0, nnz_per_core_second=120_000):
@@ -372,6 +421,313 @@ def grouping_leg(oni, torch, device, offsets, words, counts, steps, peak, cpu=Tr
     return res
 
 
+# ----------------------------------------------------------------- parity against the reference on the same documents
+
+def _rel(a, b, floor):
+    return np.abs(a - b) / np.maximum(np.abs(b), floor)
+
+
+def theta_phi_numpy(gamma, log_beta):
+    """OniLDACWrapper.scala:121-144, 170-195 in numpy (fp64): theta rows = gamma / sum (zeros if the sum is not
+    positive), phi[w][k] = exp(log_beta[k][w]) / sum_w exp(log_beta[k][w])."""
+    s = gamma.sum(axis=1, keepdims=True)
+    theta = np.where(s > 0, gamma / np.where(s > 0, s, 1.0), 0.0)
+    p = np.exp(log_beta)
+    return theta, np.ascontiguousarray((p / p.sum(axis=1, keepdims=True)).T)
+
+
+def flow_min_numpy(ev, theta, phi):
+    """score = min over the two sides of sum_k theta[ip][k] phi[word][k] (SuspiciousConnectsScoreFunction.scala:11-23,
+    FlowPostLDA.scala:99-125): unknown word -> uniform 1/K; unknown ip -> the inner join drops the event (:94), here +inf."""
+    K = theta.shape[1]
+    out = np.full(len(ev[0]), np.inf)
+    for doc, word in ((ev[0], ev[1]), (ev[2], ev[3])):
+        known_d = (doc >= 0) & (doc < theta.shape[0])
+        known_w = (word >= 0) & (word < phi.shape[0])
+        t = theta[np.where(known_d, doc, 0)]
+        p = np.where(known_w[:, None], phi[np.where(known_w, word, 0)], 1.0 / K)
+        s = np.zeros(len(doc))
+        for k in range(K):                      # left to right, as Scala's zip/map/sum
+            s += t[:, k] * p[:, k]
+        s[~known_d] = np.inf
+        out = s if doc is ev[0] else np.where(np.isinf(out) | np.isinf(s), np.inf, np.minimum(out, s))
+    return out
+
+
+def parity_leg(oni, torch, device, offsets, words, counts, K, V, cores, local_rank, n_iters=3, target_seconds=6.0):
+    """The unmodified reference on a document prefix (all host cores), the GPU path on the SAME documents from the
+    SAME 000 files, and what the two wrote compared with north_star's bars: likelihood.dat per iteration (1e-6),
+    final.gamma / final.beta (1e-4 max relative), the 1000 most suspicious of 2M flow events (99 % overlap).
+    Also the timing baselines: the reference on all cores and as a single process, the GPU on the same prefix."""
+    n_docs = reference_sample_docs(offsets, cores, target_seconds=target_seconds)
+    start = start_model_numpy(K, V, 20161102)
+    out = {"cpu_baseline": None, "parity": None}
+    with tempfile.TemporaryDirectory() as td:
+        td = Path(td)
+        ref = run_reference(td, offsets, words, counts, n_docs, K, V, n_iters, cores, start)
+        nnz = int(offsets[n_docs])
+        tok = int(np.asarray(counts[:nnz], np.int64).sum())
+        if ref is None:
+            out["cpu_baseline"] = {"value": None, "unit": "tokens/s", "cores": cores, "kind": "reference",
+                                   "sample": "oracle/_ref/lda missing or failed on this box"}
+            return out
+        secs, ref_out = ref
+        sample = (f"unmodified lda-c (oracle/_ref/lda, {cores} forked ranks), first {n_docs} docs ({nnz} nnz, {tok} tokens), "
+                  f"EM iterations 1-{n_iters} from a 000 model both sides load")
+        cb = {"value": tok / float(np.mean(secs)), "unit": "tokens/s", "cores": cores, "kind": "reference", "sample": sample,
+              "nnz_per_sec": nnz / float(np.mean(secs)), "sec_per_iter": [round(x, 3) for x in secs]}
+        # the GPU path on the same documents, same files, same iterations
+        c = oni.Corpus.from_csr(np.asarray(offsets[:n_docs + 1]), np.asarray(words[:nnz]), np.asarray(counts[:nnz]), num_terms=V)
+        m = oni.Model.load(td / "000")
+        st = oni.Settings.default()
+        st.em_max_iter = n_iters - 1
+        em = oni.EM(c, m, st, device=local_rank)
+        liks, ms, sweeps, keep = [], [], [], True
+        while keep:
+            t0 = time.perf_counter()
+            lik, _, keep = em.iterate()
+            ms.append(1e3 * (time.perf_counter() - t0))
+            liks.append(lik)
+            sweeps.append(int(em.stats(with_sweeps=True)["sweeps"]))
+        gamma, model = em.gamma(), em.model()
+        em.close()
+        cb["gpu_same_sample"] = {"value": tok / (np.mean(ms) * 1e-3), "unit": "tokens/s", "ms_per_iter": [round(x, 3) for x in ms],
+                                 "variational_sweeps_per_iter": sweeps,
+                                 "note": "same documents, same start files, same EM iterations as the reference run above; "
+                                         "wall time of onilda_em_iterate, corpus resident"}
+        out["cpu_baseline"] = cb
+        ref_lik = np.loadtxt(ref_out / "likelihood.dat", ndmin=2)[:, 0]
+        g_ref = np.loadtxt(ref_out / "final.gamma", ndmin=2)
+        b_ref = np.loadtxt(ref_out / "final.beta", ndmin=2)
+        a_ref = float((ref_out / "final.other").read_text().split()[-1])
+        par = {"documents": n_docs, "iterations_reference": int(len(ref_lik)), "iterations_gpu": len(liks),
+               "iterations_equal": len(ref_lik) == len(liks)}
+        if par["iterations_equal"]:
+            lik_err = np.abs(np.array(liks) - ref_lik) / np.abs(ref_lik)
+            g_err = _rel(gamma, g_ref, 1e-3).max(axis=1)
+            par.update({"lik_rel_err_per_iter": [float(x) for x in lik_err], "lik_rel_err_max": float(lik_err.max()),
+                        "gamma_max_rel": float(g_err.max()), "gamma_docs_beyond_1e-4": int((g_err >= 1e-4).sum()),
+                        "beta_max_rel": float(_rel(np.array(model.log_beta), b_ref, 1e-2).max()),
+                        "alpha_rel": abs(model.alpha - a_ref) / a_ref,
+                        "floors": "relative error with an absolute floor of 1e-3 (gamma) / 1e-2 (log beta), as in tests/test_gpu_parity.py; "
+                                  "the reference's values carry the 10 decimals of its %5.10f files"})
+            # top-1000 most suspicious flow events under each side's own theta / phi
+            th_r, ph_r = theta_phi_numpy(g_ref, b_ref)
+            th_g, ph_g = oni.theta_from_gamma(gamma, device=local_rank), oni.phi_from_log_beta(np.array(model.log_beta), device=local_rank)
+            th_t = torch.from_numpy(th_r).to(device)
+            pc = torch.cumsum(torch.from_numpy(ph_r).to(device).t().contiguous(), 1)
+            pc = pc / pc[:, -1:]
+            flat = (pc + torch.arange(K, device=device, dtype=torch.float64)[:, None]).reshape(-1)
+            ev = [e.cpu().numpy() for e in gen_flow_events_torch(2_000_000, th_t, flat, n_docs, V, K, device)]
+            del th_t, pc, flat
+            want = flow_min_numpy(ev, th_r, ph_r)
+            sc = oni.Scorer(th_g, ph_g, device=local_rank)
+            mine = sc.score_flow_min(*ev)
+            idx, _ = sc.topk(mine, 1.0, 1000)
+            sc.close()
+            order = np.lexsort((np.arange(len(want)), want))[:1000]
+            cut = want[order[-1]] * (1 + 1e-9)
+            finite = np.isfinite(want)
+            par.update({"top1000_overlap": float(np.mean(want[idx] <= cut)),
+                        "score_max_rel": float(np.max(np.abs(mine[finite] - want[finite]) / np.maximum(want[finite], 1e-12))),
+                        "top1000_note": "tie-aware: share of the GPU's 1000 that the reference's own scores place at or below its "
+                                        "1000th score; 2M flow events drawn from the reference's theta/phi"})
+            par["within_bars"] = bool(par["lik_rel_err_max"] < 1e-6 and par["gamma_max_rel"] < 1e-4 and par["beta_max_rel"] < 1e-4
+                                      and par["top1000_overlap"] >= 0.99)
+        out["parity"] = par
+    # north_star: "single process and mpiexec across all host cores": the single-process rate on a smaller prefix
+    n1 = reference_sample_docs(offsets, 1, target_seconds=4.0)
+    with tempfile.TemporaryDirectory() as td:
+        one = run_reference(td, offsets, words, counts, n1, K, V, 2, 1, start)
+    if one is not None:
+        tok1 = int(np.asarray(counts[:int(offsets[n1])], np.int64).sum())
+        out["cpu_baseline"]["single_process"] = {"value": tok1 / float(np.mean(one[0])), "unit": "tokens/s", "cores": 1,
+                                                 "sample": f"first {n1} docs ({int(offsets[n1])} nnz, {tok1} tokens), EM iterations 1-2",
+                                                 "sec_per_iter": [round(x, 3) for x in one[0]]}
+    return out
+
+
+def cfg1_leg(oni, local_rank):
+    """BASELINE.json configs[0] (tests/golden/cfg1: 10k documents, V = 5k, K = 20, all 21 iterations, files written by
+    the unmodified reference): the drop-in `lda est` on the GPU, wall time and the likelihood.dat it writes."""
+    import gzip
+    import shutil
+    gold = ROOT / "tests" / "golden" / "cfg1"
+    if not (gold / "c.dat.gz").exists():
+        return None
+    with tempfile.TemporaryDirectory() as td:
+        td = Path(td)
+        for name in ("c.dat", "000.beta"):
+            with gzip.open(gold / (name + ".gz"), "rb") as f, open(td / name, "wb") as g:
+                shutil.copyfileobj(f, g)
+        shutil.copy(gold / "000.other", td / "000.other")
+        shutil.copy(gold / "settings.txt", td / "settings.txt")
+        env = dict(os.environ, CUDA_VISIBLE_DEVICES=os.environ.get("CUDA_VISIBLE_DEVICES", str(local_rank)))
+        t0 = time.perf_counter()
+        r = subprocess.run([str(oni.LDA_BIN), "est", "2.5", "20", "settings.txt", "1", "c.dat", "000", "out"], cwd=td, env=env,
+                           capture_output=True, text=True)
+        wall = time.perf_counter() - t0
+        if r.returncode != 0:
+            return {"error": r.stderr[-300:]}
+        mine = np.loadtxt(td / "out" / "likelihood.dat", ndmin=2)[:, 0]
+    ref = np.loadtxt(gold / "likelihood.dat", ndmin=2)[:, 0]
+    res = {"workload": "10k docs, 1.1M tokens, V=5k, K=20, settings.txt defaults, from the fixture's 000", "iterations": int(len(mine)),
+           "lda_est_wall_s": wall, "iterations_equal": len(mine) == len(ref),
+           "reference_recorded": (gold / "README").read_text().strip()}
+    if len(mine) == len(ref):
+        res["lik_rel_err_max"] = float(np.max(np.abs(mine - ref) / np.abs(ref)))
+    return res
+
+
+# ----------------------------------------------------------------- north_star's split: one corpus over N GPUs
+
+def strong_leg(oni, torch, dist, device, local_rank, rank, world, workload, steps, warmup, comm_id_fn, scale=1.0):
+    """ONE corpus (the same on every rank: same seeds), contiguous document ranges balanced by entries
+    (csrc/est.cu split_by_nnz, lda-estimate.c:201), E-step on the shard, the library's NCCL exchange + fused M-step.
+    Timed on the device per iteration, max over ranks."""
+    cfg = dict(WORKLOADS[workload])
+    cfg["num_docs"] = max(1000, int(cfg["num_docs"] * scale))
+    K, V = cfg["num_topics"], cfg["num_terms"]
+    offsets, words, counts = gen_corpus_torch(device=device, doc_seed=cfg["seed"], **cfg)
+    torch.cuda.empty_cache()
+    corpus = oni.Corpus.from_csr(offsets, words, counts, num_terms=V)
+    D, N, T = corpus.num_docs, corpus.nnz, corpus.tokens
+    want = (N + D) * np.arange(world + 1) / world
+    bounds = np.searchsorted(offsets + np.arange(D + 1), want).clip(0, D)
+    bounds[0], bounds[-1] = 0, D
+    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+    model0 = oni.Model.new(K, V)
+    model0.init_random(20161102)
+    model0.alpha = float(np.float32(ALPHA0))
+    st = oni.Settings.default()
+    st.em_max_iter = steps + warmup + 8
+    em = oni.EM(corpus, model0, st, device=local_rank, doc_begin=lo, doc_end=hi)
+    oni.comm_attach(em, comm_id_fn(), world, rank)
+    liks, ms, est, rs, ag = [], [], [], [], []
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stream = torch.cuda.ExternalStream(em.stream(), device=device)
+    for it in range(warmup + steps):
+        dist.barrier()
+        torch.cuda.synchronize()
+        ev0.record(stream)
+        em.estep()
+        lik = em.mstep()[0]
+        ev1.record(stream)
+        torch.cuda.synchronize()
+        if it >= warmup:
+            ms.append(ev0.elapsed_time(ev1))
+            est.append(em.stats()["estep_ms"])
+            cs = oni.comm_stats(em)
+            rs.append(cs["reduce_scatter_ms"])
+            ag.append(cs["all_gather_ms"])
+        liks.append(lik)
+    t = torch.tensor([float(np.mean(ms)), float(np.mean(est))], device=device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max, est_max = (float(x) for x in t.tolist())
+    coll = oni.collective_time([em], repeats=10)
+    # the longest document of the corpus, by itself on one warp (its serial word chain bounds any split)
+    lens = np.diff(offsets)
+    dmax = int(np.argmax(lens))
+    lone = None
+    if rank == 0:
+        one = oni.EM(corpus, em.model(), st, device=local_rank, doc_begin=dmax, doc_end=dmax + 1)
+        for _ in range(3):
+            one.estep()
+            one.mstep()
+        lone = one.stats()["estep_ms"]
+        lone_sweeps = int(one.stats(with_sweeps=True)["sweeps"])
+        one.close()
+    em.close()
+    del corpus
+    if rank != 0:
+        return None
+    P = world
+    nb = coll["table_bytes"]
+    b_em = algorithmic_bytes(N, D, K)
+    return {"workload": workload, "num_docs": D, "nnz": N, "tokens": T, "num_terms": V, "num_topics": K, "n_gpus": P,
+            "split": "contiguous document ranges balanced by entries (+1 per document)", "steps": steps, "warmup": warmup,
+            "ms_per_iter": ms_max, "estep_ms_max_over_ranks": est_max, "tokens_per_sec": T / (ms_max * 1e-3),
+            "nnz_per_sec": N / (ms_max * 1e-3), "likelihood_last": liks[-1],
+            "roofline_frac": b_em / (ms_max * 1e-3) / 1e9 / (P * peak_hbm()[0]),
+            "in_step_exchange_ms": {"reduce_scatter": float(np.mean(rs)), "all_gather_x3": float(np.mean(ag)),
+                                    "note": "rank 0, CUDA events on the EM stream; includes waiting for the slowest rank's E-step"},
+            "exchange_alone": {"reduce_scatter_ms": coll["reduce_scatter_ms"], "all_gather_x3_ms": coll["all_gather_ms"],
+                               "table_bytes": nb,
+                               "reduce_scatter_bus_gbs": (P - 1) / P * nb / (coll["reduce_scatter_ms"] * 1e-3) / 1e9,
+                               "all_gather_bus_gbs": (P - 1) / P * (2 * nb + nb // (corpus_kpad(K))) / (coll["all_gather_ms"] * 1e-3) / 1e9,
+                               "allreduce_equivalent_bus_gbs": 2 * (P - 1) / P * nb / ((coll["reduce_scatter_ms"] + coll["all_gather_ms"] / 2) * 1e-3) / 1e9,
+                               "note": "NCCL over NVLink/NVSwitch, 10 back-to-back calls behind a barrier; bus bandwidth = (P-1)/P x bytes / time "
+                                       "(reduce-scatter of the K x V fp64 statistics; all-gather of log_beta + beta' + row maxima); the "
+                                       "all-reduce equivalent pairs the reduce-scatter with ONE table's all-gather"},
+            "longest_document": {"entries": int(lens[dmax]), "sweeps": lone_sweeps, "lone_warp_estep_ms": lone,
+                                 "note": "the document alone in an E-step: one warp, nothing else on the GPU; no split of the corpus "
+                                         "over more GPUs ends an iteration earlier than this"}}
+
+
+def corpus_kpad(K):
+    g = 4 if K <= 32 else 8 if K <= 64 else 16 if K <= 128 else 32
+    return g * ((K + g - 1) // g)
+
+
+def peak_hbm():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        return json.loads(p.read_text())["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def sharded_scoring_leg(oni, torch, dist, device, local_rank, rank, world, gamma0, log_beta0, n_events, steps):
+    """configs[4] at N GPUs: theta / phi replicated (rank 0's documents and the common model), the events sharded
+    contiguously, each rank's 1000 most suspicious merged on rank 0 (no collective on the data path)."""
+    D, K = gamma0.shape
+    V = log_beta0.shape[1]
+    theta = oni.theta_from_gamma(gamma0, device=local_rank)
+    phi = oni.phi_from_log_beta(log_beta0, device=local_rank)
+    per = n_events // world
+    theta_t = torch.from_numpy(theta).to(device)
+    pc = torch.cumsum(torch.from_numpy(phi).to(device).t().contiguous(), 1)
+    pc = pc / pc[:, -1:]
+    flat = (pc + torch.arange(K, device=device, dtype=torch.float64)[:, None]).reshape(-1)
+    torch.manual_seed(20161105 + rank)
+    ev = gen_flow_events_torch(per, theta_t, flat, D, V, K, device)
+    del theta_t, pc, flat
+    torch.cuda.empty_cache()
+    sc = oni.Scorer(theta, phi, device=local_rank)
+    scores = torch.empty(per, dtype=torch.float64, device=device)
+    ts = []
+    for it in range(2 + steps):
+        dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        idx, val = sc.score_flow_topk_device(ev[0].data_ptr(), ev[1].data_ptr(), ev[2].data_ptr(), ev[3].data_ptr(), per, 1.0,
+                                             1000, scores.data_ptr())
+        pad = 1000 - len(idx)
+        mine = torch.tensor(np.concatenate([val, np.full(pad, np.inf)]), device=device)
+        mine_i = torch.tensor(np.concatenate([idx + rank * per, np.full(pad, -1)]), device=device)
+        allv = [torch.empty_like(mine) for _ in range(world)]
+        alli = [torch.empty_like(mine_i) for _ in range(world)]
+        dist.all_gather(allv, mine)
+        dist.all_gather(alli, mine_i)
+        if rank == 0:
+            v, i = torch.cat(allv).cpu().numpy(), torch.cat(alli).cpu().numpy()
+            order = np.lexsort((i, v))[:1000]
+            top = (i[order], v[order])
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if it >= 2:
+            ts.append(dt)
+    t = torch.tensor([float(np.mean(ts)), sc.stats()["kernel_ms"]], device=device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    sc.close()
+    if rank != 0:
+        return None
+    sec, kms = float(t[0]), float(t[1])
+    return {"events": per * world, "n_gpus": world, "events_per_sec": per * world / sec, "unit": "flow events/s",
+            "ms": 1e3 * sec, "score_kernel_ms_max_over_ranks": kms, "most_suspicious_score": float(top[1][0]),
+            "note": "events sharded contiguously, theta/phi replicated, per-rank top-1000 gathered and merged on rank 0; "
+                    "wall time from barrier to merged rows, max over ranks"}
+
+
 # ----------------------------------------------------------------- main
 
 def algorithmic_bytes(nnz, num_docs, K):
@@ -407,6 +763,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-scoring", action="store_true")
     ap.add_argument("--no-grouping", action="store_true")
+    ap.add_argument("--no-strong", action="store_true", help="skip the one-corpus-over-N-GPUs legs at N > 1")
     ap.add_argument("--events", type=int, default=1_000_000_000, help="flow events of the scoring leg (configs[4])")
     args = ap.parse_args()
     if args.warmup < 3:
@@ -420,28 +777,70 @@ def main():
         return 0
 
     import torch
-    oni = importlib.import_module("open-network-insight_b200")
     cfg = dict(WORKLOADS[args.workload])
     cfg["num_docs"] = max(1000, int(cfg["num_docs"] * args.scale))
     K, V = cfg["num_topics"], cfg["num_terms"]
     if args.hub_frac is not None:
         cfg["hub_frac"] = args.hub_frac
-
-    if not torch.cuda.is_available() or oni.device_count() < 1:
-        raise SystemExit("bench.py needs a CUDA device: libonilda has no CPU path")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (the synthetic corpus is generated there; libonilda has no CPU path)")
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
+
+    # ------------------------------------------------------------ reference arm: never loads libonilda
+    if args.impl == "reference":
+        t0 = time.time()
+        offsets, words, counts = gen_corpus_torch(device=device, doc_seed=cfg["seed"], **cfg)
+        log(f"corpus: D={len(offsets) - 1} N={int(offsets[-1])} ({time.time() - t0:.1f}s)")
+        cores = host_cores()
+        n_docs = reference_sample_docs(offsets, cores)
+        n_iters = args.steps + args.warmup
+        with tempfile.TemporaryDirectory() as td:
+            ref = run_reference(td, offsets, words, counts, n_docs, K, V, n_iters, cores, start_model_numpy(K, V, 20161102))
+        if ref is None:
+            emit({"impl": "reference", "unavailable": "oracle/_ref/lda missing or failed on this box"})
+            return 0
+        secs = ref[0]
+        timed = secs[args.warmup:] if len(secs) > args.warmup else secs
+        nnz = int(offsets[n_docs])
+        tok = int(np.asarray(counts[:nnz], np.int64).sum())
+        val = tok / float(np.mean(timed))
+        sample = (f"first {n_docs} docs ({nnz} nnz, {tok} tokens) of the workload, EM iterations {len(secs) - len(timed) + 1}-{len(secs)} "
+                  f"timed ({len(timed)}), {cores} forked ranks of the unmodified lda-c")
+        emit({"metric": "lda_em_tokens_per_sec_per_iter", "value": val, "unit": "tokens/s", "n_gpus": 0,
+              "steps": len(timed), "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(timed)),
+              "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+              "impl": "reference",
+              "config": {"workload": args.workload, "sample": sample, "nnz_per_sec": nnz / float(np.mean(timed)),
+                         "inputs": "sample.dat and 000.* written with numpy; libonilda is not loaded by this process; the "
+                                   "synthetic corpus is generated with PyTorch on the GPU, as in the other arm",
+                         "sec_per_iter": [round(x, 3) for x in secs]},
+              "cpu_baseline": {"value": val, "unit": "tokens/s", "cores": cores, "kind": "reference", "sample": sample},
+              "e2e": {"value": val, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+              "gpu_launches": 0})
+        return 0
+
+    oni = importlib.import_module("open-network-insight_b200")
+    if oni.device_count() < 1:
+        raise SystemExit("bench.py needs a CUDA device: libonilda has no CPU path")
     dist = None
-    if world > 1 and args.impl == "ours":
+    if world > 1:
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")    # stdout carries the one JSON line only
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=device)
+
+    def comm_id():
+        """128 bytes of NCCL unique id from rank 0 to everyone (torch.distributed is the messenger only)."""
+        buf = torch.zeros(oni.COMM_ID_BYTES, dtype=torch.uint8, device=device)
+        if rank == 0:
+            buf.copy_(torch.frombuffer(bytearray(oni.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(buf, 0)
+        return buf.cpu().numpy().tobytes()
 
     t0 = time.time()
     offsets, words, counts = gen_corpus_torch(device=device, doc_seed=cfg["seed"] + 1000 * rank, **cfg)
     torch.cuda.empty_cache()
     corpus = oni.Corpus.from_csr(offsets, words, counts, num_terms=V)
-    del words, counts
     D, N, T = corpus.num_docs, corpus.nnz, corpus.tokens
     log(f"[rank {rank}] corpus: D={D} N={N} T={T} V={corpus.num_terms} max_len={corpus.max_len} ({time.time() - t0:.1f}s)")
     model0 = oni.Model.new(K, V)
@@ -450,47 +849,13 @@ def main():
     settings = oni.Settings.default()
     settings.em_max_iter = max(settings.em_max_iter, args.steps + args.warmup)
 
-    # ------------------------------------------------------------ reference arm
-    if args.impl == "reference":
-        cores = host_cores()
-        n_docs = reference_sample_docs(offsets, cores)
-        n_iters = args.steps + args.warmup
-        with tempfile.TemporaryDirectory() as td:
-            secs = time_reference(oni, corpus, model0, n_docs, n_iters, cores, td)
-        if secs is None:
-            emit({"impl": "reference", "unavailable": "oracle/_ref/lda missing or failed on this box"})
-            return 0
-        timed = secs[args.warmup:] if len(secs) > args.warmup else secs
-        tok = int(np.asarray(corpus.csr()[2][:offsets[n_docs]], np.int64).sum())
-        val = tok / float(np.mean(timed))
-        sample = f"first {n_docs} docs ({int(offsets[n_docs])} nnz, {tok} tokens) of the workload, {len(timed)} timed EM iterations"
-        line = {"metric": "lda_em_tokens_per_sec_per_iter", "value": val, "unit": "tokens/s", "n_gpus": 0,
-                "steps": len(timed), "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(timed)),
-                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "impl": "reference",
-                "config": {"workload": args.workload, "sample": sample, "nnz_per_sec": offsets[n_docs] / float(np.mean(timed))},
-                "cpu_baseline": {"value": val, "unit": "tokens/s", "cores": cores, "kind": "reference", "sample": sample},
-                "e2e": {"value": val, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                "gpu_launches": 0}
-        emit(line)
-        return 0
-
-    # ------------------------------------------------------------ our arm: resident-in-HBM leg
+    # ------------------------------------------------------------ resident-in-HBM leg
     em = oni.EM(corpus, model0, settings, device=local_rank)
-    ss_tensor = None
     if dist is not None:
-        ptr, cnt = em.suffstats_device()
-
-        class _Buf:
-            __cuda_array_interface__ = {"shape": (cnt,), "typestr": "<f8", "data": (ptr, False), "version": 3}
-        ss_tensor = torch.as_tensor(_Buf(), device=device)
+        oni.comm_attach(em, comm_id(), world, rank)      # the exchange is the library's: reduce-scatter, lda_mle, all-gather
 
     def em_step():
         em.estep()
-        if dist is not None:
-            torch.cuda.synchronize()          # the library runs on its own stream
-            dist.all_reduce(ss_tensor)
-            torch.cuda.synchronize()
         return em.mstep()
 
     def barrier():
@@ -541,16 +906,11 @@ def main():
     def e2e_step():
         em.reload(cur)                        # H2D: CSR words+counts+totals, model
         em.estep()
-        if dist is not None:
-            torch.cuda.synchronize()
-            dist.all_reduce(ss_tensor)
-            torch.cuda.synchronize()
-        out = em.mstep()                      # D2H: likelihood + statistics tail
+        out = em.mstep()                      # exchange (N > 1), M-step; D2H: likelihood + statistics tail
         oni._check(lib.onilda_em_get_model(em._h, cur._h))      # D2H: new model
         oni._check(lib.onilda_em_get_gamma(em._h, g_host))      # D2H: gamma
         return out
 
-    # the EM loop state must follow the iterations, not restart: reload() resets it, so carry it here
     e2e_liks = [float("nan")]
     e2e_elapsed = float("nan")
     if not args.no_e2e:
@@ -571,75 +931,81 @@ def main():
     e2e = {"value": T_all / (e2e_elapsed / args.steps), "unit": "tokens/s", "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * e2e_elapsed / args.steps}
 
+    gamma = em.gamma()
+    log_beta = np.array(em.model().log_beta)
+    exchange = oni.comm_stats(em) if dist is not None else None
+    em.close()
+    torch.cuda.empty_cache()
+
+    # ------------------------------------------------------------ N > 1: north_star's split and the sharded scoring sweep
+    strong = strong_dns = sharded = None
+    if dist is not None and not args.no_strong:
+        try:
+            strong = strong_leg(oni, torch, dist, device, local_rank, rank, world, DEFAULT_WORKLOAD, 8, 3, comm_id, args.scale)
+            strong_dns = strong_leg(oni, torch, dist, device, local_rank, rank, world, "dns-2M-docs-200M-tokens-V50k-K20", 6, 3,
+                                    comm_id, args.scale)
+        except Exception as e:          # the headline line must still be printed
+            log(f"[rank {rank}] strong leg failed: {e!r}")
+            strong = strong or {"error": repr(e)}
+        if not args.no_scoring:
+            try:
+                g0 = torch.from_numpy(gamma).to(device)
+                b0 = torch.from_numpy(log_beta).to(device)
+                dist.broadcast(g0, 0)
+                dist.broadcast(b0, 0)
+                sharded = sharded_scoring_leg(oni, torch, dist, device, local_rank, rank, world, g0.cpu().numpy(), b0.cpu().numpy(),
+                                              max(1_000_000, int(args.events * args.scale)), 5)
+                del g0, b0
+            except Exception as e:
+                log(f"[rank {rank}] sharded scoring failed: {e!r}")
+                sharded = {"error": repr(e)}
+
     if rank != 0:
         if dist is not None:
             dist.barrier()
             dist.destroy_process_group()
         return 0
 
-    # ------------------------------------------------------------ roofline of the E-step kernel
-    peaks_path = ROOT / "MEASURED_PEAKS.json"
-    if peaks_path.exists():
-        peak, peak_src = json.loads(peaks_path.read_text())["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs"
-    else:
-        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    # ------------------------------------------------------------ roofline of the E-step
+    peak, peak_src = peak_hbm()
     b_em = algorithmic_bytes(N, D, K)
     achieved = b_em / (np.mean(estep_ms) * 1e-3) / 1e9
-    traffic = None
+    traffic = fp64 = None
     prof = ROOT / "profiles" / "estep_traffic.json"
     if prof.exists():
         try:
-            traffic = json.loads(prof.read_text()).get("dram_bytes_per_launch")
+            pj = json.loads(prof.read_text())
+            traffic, fp64 = pj.get("dram_bytes_per_launch"), pj.get("fp64_pipe_pct_of_active_cycles")
         except ValueError:
-            traffic = None
+            pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": "E-step = estep_kernel<32,1> (documents >= 1024 entries) || estep_kernel<4,5> "
-                                              "(the rest), two concurrent launches timed as one",
+                "traffic": traffic, "kernel": "E-step = estep_long_kernel<20> (documents >= 1024 entries, one per warp) || "
+                                              "estep_kernel<4,5,20> (the rest, eight per warp), two concurrent launches timed as one",
                 "algorithmic_bytes_per_launch": b_em, "kernel_ms": float(np.mean(estep_ms)), "peak_source": peak_src,
-                "fp64_pipe_pct_of_active_cycles": {"estep_kernel<4,5>": 62.6, "estep_kernel<32,1>": 43.9,
-                                                   "source": "profiles/ncu_r1_*_summary.txt"},
-                "note": "nominally an HBM gather; measured bound is FP64 issue + the serial per-word dependency chain "
-                        "(Gauss-Seidel order of lda-inference.c:50-75), so frac against HBM is small by construction: DESIGN.md 4.1"}
+                "fp64_pipe_pct_of_active_cycles": fp64,
+                "note": "nominally an HBM gather; measured bound is instruction issue on the serial per-word dependency chain "
+                        "(Gauss-Seidel order of lda-inference.c:50-75) of the long documents, so frac against HBM is small by "
+                        "construction: DESIGN.md 4.1"}
 
-    # ------------------------------------------------------------ scoring leg (rank 0, one GPU)
-    scoring = None
-    if not args.no_scoring:
-        gamma = em.gamma()
-        log_beta = np.array(em.model().log_beta)
-        em.close()
+    # ------------------------------------------------------------ single-GPU side legs (rank 0 at N = 1)
+    scoring = grouping = cfg1 = None
+    cpu_baseline = parity = None
+    if world == 1:
+        if not args.no_scoring:
+            n_events = max(1_000_000, int(args.events * args.scale))
+            scoring = scoring_leg(oni, torch, device, gamma, log_beta, n_events, 1 << 28, 5, peak,
+                                  cpu_cores=0 if args.no_cpu_baseline else host_cores())
         torch.cuda.empty_cache()
-        n_events = max(1_000_000, int(args.events * args.scale))
-        scoring = scoring_leg(oni, torch, device, gamma, log_beta, n_events, 1 << 28, 5, peak,
-                              cpu_cores=0 if args.no_cpu_baseline else host_cores())
-        del gamma, log_beta
-
-    # ------------------------------------------------------------ grouping leg (rank 0, one GPU)
-    grouping = None
-    if not args.no_grouping:
-        if args.no_scoring:
-            em.close()
-        torch.cuda.empty_cache()
-        _, w_all, c_all, _ = corpus.csr()
-        grouping = grouping_leg(oni, torch, device, np.asarray(offsets), w_all, c_all, 5, peak,
-                                cpu=not args.no_cpu_baseline)
-
-    # ------------------------------------------------------------ CPU baseline (reference lda-c on this box)
-    cpu_baseline = None
-    if not args.no_cpu_baseline:
-        cores = host_cores()
-        n_docs = reference_sample_docs(offsets, cores, target_seconds=6.0)
-        with tempfile.TemporaryDirectory() as td:
-            secs = time_reference(oni, corpus, model0, n_docs, 3, cores, td)
-        if secs:
-            tok = int(np.asarray(corpus.csr()[2][:offsets[n_docs]], np.int64).sum())
-            cpu_baseline = {"value": tok / float(np.mean(secs)), "unit": "tokens/s", "cores": cores, "kind": "reference",
-                            "sample": f"unmodified lda-c (oracle/_ref/lda, {cores} forked ranks), first {n_docs} docs "
-                                      f"({int(offsets[n_docs])} nnz, {tok} tokens), 3 EM iterations from the same start model",
-                            "nnz_per_sec": int(offsets[n_docs]) / float(np.mean(secs)),
-                            "sec_per_iter": [round(x, 3) for x in secs]}
-        else:
-            cpu_baseline = {"value": None, "unit": "tokens/s", "cores": cores, "kind": "reference",
-                            "sample": "oracle/_ref/lda missing or failed on this box"}
+        if not args.no_grouping:
+            _, w_all, c_all, _ = corpus.csr()
+            grouping = grouping_leg(oni, torch, device, np.asarray(offsets), w_all, c_all, 5, peak, cpu=not args.no_cpu_baseline)
+        if not args.no_cpu_baseline:
+            pl = parity_leg(oni, torch, device, offsets, words, counts, K, V, host_cores(), local_rank)
+            cpu_baseline, parity = pl["cpu_baseline"], pl["parity"]
+            cfg1 = cfg1_leg(oni, local_rank)
+    else:
+        scoring = {"sharded": sharded} if sharded is not None else None
+    del gamma, log_beta
 
     line = {"metric": "lda_em_tokens_per_sec_per_iter", "value": value, "unit": "tokens/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
@@ -648,13 +1014,17 @@ def main():
                        "num_topics": K, "docs_per_gpu": D, "settings": "var 20/1e-6, em 20/1e-6, alpha estimate",
                        "start": "random (MT19937 seed 20161102), alpha 2.5",
                        "l2": "inputs larger than L2 (CSR 0.7 GB + phi scratch 14 GB per GPU)",
-                       "parallelism": f"dp{world} over documents", "scale": args.scale},
+                       "parallelism": f"dp{world} over documents; statistics: NCCL reduce-scatter -> lda_mle of the own rows -> all-gather "
+                                      "inside libonilda" if world > 1 else "one GPU", "scale": args.scale},
             "nnz_per_sec": N_all / (elapsed / args.steps),
             "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
-            "cpu_baseline": cpu_baseline, "scoring": scoring, "grouping": grouping,
+            "cpu_baseline": cpu_baseline, "parity": parity, "cfg1": cfg1, "scoring": scoring, "grouping": grouping,
+            "strong": strong, "strong_dns": strong_dns, "exchange_in_step": exchange,
             "em": {"estep_ms": [round(x, 3) for x in estep_ms], "mstep_ms_mean": float(np.mean(mstep_ms)),
                    "likelihood_first": liks[0], "likelihood_last": liks[-1], "sweeps_last_iter": int(sweeps),
-                   "e2e_likelihood_last": e2e_liks[-1]}}
+                   "e2e_likelihood_last": e2e_liks[-1],
+                   "estep_ms_note": "EM iterations warmup+1 .. warmup+steps of one run: later iterations take more variational "
+                                    "sweeps per document as the topics sharpen (sweeps_last_iter), so estep_ms rises within the run"}}
     emit(line)
     if dist is not None:
         dist.barrier()

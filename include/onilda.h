@@ -377,7 +377,13 @@ void onilda_scorer_destroy(onilda_scorer* s);
  * takes the uniform 1/K row.  Host buffers; copies are pipelined inside. */
 int onilda_score(onilda_scorer* s, const int32_t* doc, const int32_t* word, int64_t n, double* out);
 /* replaces FlowPostLDA.score x2 + minimumScore (netflow/FlowPostLDA.scala:94-125):
- * min(score(sdoc, sword), score(ddoc, dword)) per flow event. */
+ * min(score(sdoc, sword), score(ddoc, dword)) per flow event.
+ * Unknown ids: a word id outside the table scores against the uniform row (:100, Array.fill(20)(0.05)).
+ * An ip (document id) outside the table is different for flow: the reference inner-joins the events with the
+ * document table (:94), once per side, so such an event is absent from its results.  out[] keeps one slot per
+ * event, so that event's slot holds +infinity; onilda_topk / onilda_flow_results / onilda_score_flow_topk_device
+ * never return a +infinity row, whatever the threshold.  (onilda_score - dns, proxy - gives an unknown ip the
+ * uniform row, as SuspiciousConnectsScoreFunction.scala:17 does.) */
 int onilda_score_flow_min(onilda_scorer* s, const int32_t* sdoc, const int32_t* sword, const int32_t* ddoc,
                           const int32_t* dword, int64_t n, double* out);
 /* replaces filter(score <= threshold) + orderBy/takeOrdered(k)
@@ -408,8 +414,8 @@ int onilda_scorer_stats(onilda_scorer* s, double* kernel_ms, int64_t* launches);
  * Who that is: code running inside a process that has already given all of the GPU's memory to
  * a pooling allocator - a Spark executor with a GPU memory pool, which is where ONI's post-LDA
  * scoring lives - so that a cudaMalloc made by this library would fail; and latency-bound
- * streaming scorers, because cudaMalloc / cudaFree stall the whole device and cannot be issued
- * while a stream is being captured.  onilda_topk and onilda_score_flow_topk_device both allocate.
+ * streaming scorers, because cudaMalloc / cudaFree stall the whole device.
+ * onilda_topk and onilda_score_flow_topk_device both allocate.
  *
  * This one makes no cudaMalloc / cudaFree / host-heap call.  Same result as onilda_topk (the k
  * smallest scores that are <= threshold, ascending, ties by event index), with
@@ -424,8 +430,13 @@ int onilda_scorer_stats(onilda_scorer* s, double* kernel_ms, int64_t* launches);
  *     work of its own still running that reads the results) race on that array: serialise them.
  *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress);
  *     make that first call before starting any stream capture.
- *   - work is issued to the legacy default stream and the call returns when the rows are in
- *     the host arrays. */
+ *   - the scores must be COMPLETE before the call: synchronise the stream that produced them.
+ *     The work here goes to the legacy default stream, which does not wait for streams created
+ *     with cudaStreamNonBlocking - the scorer's own streams are of that kind.
+ *   - the call is synchronous: it reads small results back with blocking copies between its
+ *     passes and returns when the rows are in the host arrays.
+ *   - about 80 KB of the CALLER'S STACK are used (one histogram and the k rows): mind threads
+ *     with small stacks, e.g. JVM threads that come in through JNI. */
 #define ONILDA_NOALLOC_MAX_K 4096
 int onilda_topk_device_noalloc(const double* score_dev, int64_t n, double threshold, int64_t k,
                                int64_t* idx_out, double* score_out, int64_t* n_out);

@@ -15,6 +15,7 @@
 // tile, then each lane forms its own event's dot product from the tile with the
 // products rounded and added left to right - the order of Scala's
 // zip/map/sum - so the result is bit-identical to a sequential CPU evaluation.
+#include <float.h>
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
@@ -107,7 +108,11 @@ __global__ void __launch_bounds__(kScoreThreads) score_kernel(const double* __re
         const int64_t i = tile * 32 + lane;
         const bool live = i < n;
         int32_t d0 = live ? sdoc[i] : -1, w0 = live ? sword[i] : -1;
-        // ids outside the tables (e.g. -1) take the uniform row (SuspiciousConnectsScoreFunction.scala:13-18)
+        // ids outside the tables (e.g. -1) take the uniform row (SuspiciousConnectsScoreFunction.scala:13-18).
+        // Flow is the exception for the ip: FlowPostLDA joins the events with the document table (an inner join,
+        // FlowPostLDA.scala:94), so an event whose source or destination ip has no theta row is gone from its
+        // results.  Here such an event keeps its slot and gets +infinity: no threshold keeps it, no top-k takes it.
+        bool dropped = FLOW && !(d0 >= 0 && d0 < D);
         int64_t drow = (d0 >= 0 && d0 < D) ? d0 : D;
         int64_t wrow = (w0 >= 0 && w0 < V) ? w0 : V;
         stage_rows(theta, drow, K, stride, tile_t, lane);
@@ -117,6 +122,7 @@ __global__ void __launch_bounds__(kScoreThreads) score_kernel(const double* __re
         __syncwarp();
         if (FLOW) {
             int32_t d1 = live ? ddoc[i] : -1, w1 = live ? dword[i] : -1;
+            dropped = dropped || !(d1 >= 0 && d1 < D);
             drow = (d1 >= 0 && d1 < D) ? d1 : D;
             wrow = (w1 >= 0 && w1 < V) ? w1 : V;
             stage_rows(theta, drow, K, stride, tile_t, lane);
@@ -126,7 +132,7 @@ __global__ void __launch_bounds__(kScoreThreads) score_kernel(const double* __re
             __syncwarp();
             s = (s <= s2) ? s : s2;   // scala.math.min (FlowPostLDA.scala:117-119)
         }
-        if (live) out[i] = s;
+        if (live) out[i] = dropped ? INFINITY : s;
     }
 }
 
@@ -166,11 +172,13 @@ __global__ void __launch_bounds__(kScoreThreads) score_pairs_kernel(const double
         const int64_t i = tile_id * 32 + lane;
         const bool live = i < n;
         double result = 0.0;
+        bool dropped = false;     // flow only: an ip without a theta row (the inner join of FlowPostLDA.scala:94; see score_kernel)
 #pragma unroll
         for (int side = 0; side < (FLOW ? 2 : 1); side++) {
             const int32_t d0 = live ? (side ? ddoc[i] : sdoc[i]) : -1;
             const int32_t w0 = live ? (side ? dword[i] : sword[i]) : -1;
             // ids outside the tables (e.g. -1) take the uniform row (SuspiciousConnectsScoreFunction.scala:13-18)
+            if (FLOW) dropped = dropped || !(d0 >= 0 && d0 < D);
             rows_t[lane] = (d0 >= 0 && d0 < D) ? d0 : (int)D;
             rows_p[lane] = (w0 >= 0 && w0 < V) ? w0 : (int)V;
             __syncwarp();
@@ -197,7 +205,7 @@ __global__ void __launch_bounds__(kScoreThreads) score_pairs_kernel(const double
             __syncwarp();
             result = (side == 0) ? s : ((result <= s) ? result : s);   // scala.math.min (FlowPostLDA.scala:117-119)
         }
-        if (live) out[i] = result;
+        if (live) out[i] = dropped ? INFINITY : result;
     }
 }
 
@@ -419,7 +427,8 @@ int select_topk_device(onilda_scorer* s, const double* score_dev, int64_t n, dou
                        int64_t* idx_out, double* score_out, int64_t* n_out)
 {
     cudaStream_t st = s->stream[0];
-    const unsigned long long max_key = isnan(threshold) ? 0ull : host_order_key(threshold);
+    // +infinity marks an event the flow join dropped (score_kernel): no threshold, however large, keeps it
+    const unsigned long long max_key = isnan(threshold) ? 0ull : host_order_key(threshold > DBL_MAX ? DBL_MAX : threshold);
     const int blocks = s->sm_count * 4;
     std::vector<unsigned long long> hist(kBins);
     // the array the digit passes read: all n scores at first, the compacted candidates later
@@ -935,7 +944,8 @@ extern "C" int onilda_topk_device_noalloc(const double* score_dev, int64_t n, do
     TopkScratch* sc = g_topk_scratch_addr[dev];
     ONILDA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     const int blocks = sms * 4;
-    const unsigned long long max_key = isnan(threshold) ? 0ull : host_order_key(threshold);
+    // +infinity marks an event the flow join dropped (score_kernel): no threshold, however large, keeps it
+    const unsigned long long max_key = isnan(threshold) ? 0ull : host_order_key(threshold > DBL_MAX ? DBL_MAX : threshold);
     unsigned long long hist[kBins];          // 16 KB on the stack
     *n_out = 0;
     if (n == 0 || k == 0) return ONILDA_OK;

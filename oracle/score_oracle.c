@@ -72,6 +72,10 @@ static void* score_range(void* arg)
         if (j->ddoc) {
             double b = score_one(j->ddoc[i], j->dword[i], j->D, j->V, j->K, j->theta, j->phi_wk);
             j->out[i] = (a <= b) ? a : b;      /* scala.math.min */
+            /* netflow/FlowPostLDA.scala:94: the events are inner-joined with the document table on the ip, for the
+             * source and again for the destination, so an event with an ip that has no theta row leaves the result
+             * set.  Per-event output has to keep the slot: +infinity, which no threshold keeps and no top-k takes. */
+            if (!(j->sdoc[i] >= 0 && j->sdoc[i] < j->D) || !(j->ddoc[i] >= 0 && j->ddoc[i] < j->D)) j->out[i] = INFINITY;
         } else {
             j->out[i] = a;
         }
@@ -131,7 +135,7 @@ int64_t oracle_topk(int64_t n, const double* score, double threshold, int64_t k,
     scored* kept = malloc(sizeof(scored) * (size_t)(n > 0 ? n : 1));
     int64_t m = 0;
     for (int64_t i = 0; i < n; i++)
-        if (score[i] <= threshold) { kept[m].s = score[i]; kept[m].i = i; m++; }
+        if (score[i] <= threshold && !isinf(score[i])) { kept[m].s = score[i]; kept[m].i = i; m++; }   /* +inf: a row the flow join dropped */
     qsort(kept, (size_t)m, sizeof(scored), by_score_then_index);
     int64_t take = (k == -1 || m < k) ? m : k;
     for (int64_t j = 0; j < take; j++) { idx_out[j] = kept[j].i; score_out[j] = kept[j].s; }

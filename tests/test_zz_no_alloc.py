@@ -44,3 +44,22 @@ def test_limits_are_refused_with_a_clear_message(oni):
     assert len(idx) == 0
     idx, val = oni.topk_device_noalloc(dev.data_ptr(), 10, -1.0, 5)      # nothing under the threshold
     assert len(idx) == 0
+
+
+def test_second_device_has_its_own_scratch(oni):
+    """Every GPU that loads the library holds its own copy of the scratch array; the entry point looks the
+    address up once per device, with that device current."""
+    import torch
+    if oni.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    rng = np.random.default_rng(12)
+    scores = rng.random(200_000) ** 3
+    sc = oni.Scorer(np.ones((1, 2)) / 2, np.ones((1, 2)) / 2, device=0)
+    ridx, rval = sc.topk(scores, 0.5, 777)
+    sc.close()
+    for dev_id in (1, 0, 1):
+        with torch.cuda.device(dev_id):
+            dev = torch.tensor(scores, dtype=torch.float64, device=f"cuda:{dev_id}")
+            torch.cuda.synchronize()
+            idx, val = oni.topk_device_noalloc(dev.data_ptr(), len(scores), 0.5, 777)
+        assert np.array_equal(idx, ridx) and np.array_equal(val, rval), dev_id
