@@ -328,6 +328,9 @@ int onilda_em_get_doc_likelihood(onilda_em* em, double* out);
 /* Variational sweeps each document took in the last estep (lda_inference's var_iter,
  * lda-inference.c:48): [doc_end-doc_begin]. */
 int onilda_em_get_doc_sweeps(onilda_em* em, int32_t* out);
+/* How many (document, word) steps of the last estep were redone in log space because their sum over topics left
+ * the range of the product form (a diagnostic; the reference computes every word that way, lda-inference.c:52-68). */
+int onilda_em_log_space_words(onilda_em* em, int64_t* count);
 /* Counters of the last estep: kernel time in ms (CUDA events on the handle's
  * stream), number of kernel launches issued by the last estep+mstep pair, and
  * total variational sweeps summed over documents. */
@@ -400,6 +403,28 @@ int onilda_topk(onilda_scorer* s, const double* score, int64_t n, double thresho
 int onilda_flow_results(onilda_scorer* s, const int32_t* sdoc, const int32_t* sword, const int32_t* ddoc,
                         const int32_t* dword, int64_t n, double threshold, int64_t k, int64_t* idx_out,
                         double* src_score_out, double* dst_score_out, int64_t* n_out);
+/* The rows of dns_results.csv / proxy_results.csv in one call: score per event (one side: client ip x word), keep
+ * score <= threshold, the k smallest in ascending order; k == -1 keeps all (replaces DNSPostLDA.scala:44-70 - filter,
+ * count, takeOrdered(takeCount), sortBy - ProxySuspiciousConnectsAnalysis.scala:45-51 and
+ * DataFrameUtils.dfTakeOrdered, utilities/DataFrameUtils.scala:21-38).  idx_out: event indices of the kept rows (join
+ * the event's own columns on the caller's side), score_out: the Score column.  Equal scores come out by event
+ * index (Spark leaves them in no particular order).  Outputs need room for min(k, n) entries, n when k == -1. */
+int onilda_results_rows(onilda_scorer* s, const int32_t* doc, const int32_t* word, int64_t n, double threshold,
+                        int64_t k, int64_t* idx_out, double* score_out, int64_t* n_out);
+/* Writes <type>_results.csv: line i = rows[i] + delimiter + score_a[i] [+ delimiter + score_b[i]] (replaces the
+ * `_.mkString(outputDelimiter)` + saveAsTextFile of netflow/FlowPostLDA.scala:80, dns/DNSPostLDA.scala:69,
+ * proxy/ProxySuspiciousConnectsAnalysis.scala:51; the part files ml_ops.sh merges are one file here).
+ *   rows[i]  : the kept event's own columns and word column(s), already joined with the delimiter by the caller,
+ *              in the order onilda_flow_results / onilda_results_rows returned them;
+ *   flow     : score_a = SourceScore, score_b = DestinationScore (columns 35 / 36 for oni-oa, oa/flow/flow_conf.json);
+ *   dns, proxy: score_a = Score, score_b = NULL.
+ * Doubles are printed in Java's Double.toString layout (see onilda_format_java_double).  Temporary file + rename. */
+int onilda_results_write(const char* path, const char* const* rows, int64_t m, const double* score_a, const double* score_b,
+                         const char* delimiter);
+/* v as Java's Double.toString lays it out, with the shortest digits that read back as v ("0.05", "1.0E-4",
+ * "6.379973716629045E-4", "1.2345678E7").  out: at least 32 bytes; returns the length, no NUL.  JDK 19+ prints
+ * exactly this; the JDK 7/8 that Spark 1.6 ran on prints one more digit for a small share of values. */
+int onilda_format_java_double(double v, char* out);
 /* Fused form for data already on the device (no host copies): scores the
  * events, keeps the running top-k, returns only the k rows.  Device pointers. */
 int onilda_score_flow_topk_device(onilda_scorer* s, const int32_t* sdoc_dev, const int32_t* sword_dev,

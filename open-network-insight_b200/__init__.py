@@ -127,6 +127,7 @@ def lib():
     L.onilda_em_get_doc_sweeps.argtypes = [_vp, _i32p]
     L.onilda_em_stats.argtypes = [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int64),
                                   C.POINTER(C.c_int64)]
+    L.onilda_em_log_space_words.argtypes = [_vp, C.POINTER(C.c_int64)]
     L.onilda_em_stream.argtypes = [_vp]
     L.onilda_em_stream.restype = _vp
     L.onilda_run_em.argtypes = [C.c_char_p, C.c_char_p, _vp, C.c_int, C.c_double, C.POINTER(Settings), C.c_int,
@@ -138,6 +139,9 @@ def lib():
     L.onilda_scorer_create.argtypes = [_vp, C.c_int64, _vp, C.c_int32, C.c_int, C.c_int, C.POINTER(_vp)]
     L.onilda_scorer_create_from_em.argtypes = [_vp, C.POINTER(_vp)]
     L.onilda_scorer_destroy.argtypes = [_vp]
+    L.onilda_results_rows.argtypes = [_vp, _vp, _vp, C.c_int64, C.c_double, C.c_int64, _vp, _vp, C.POINTER(C.c_int64)]
+    L.onilda_results_write.argtypes = [C.c_char_p, C.POINTER(C.c_char_p), C.c_int64, _vp, _vp, C.c_char_p]
+    L.onilda_format_java_double.argtypes = [C.c_double, C.c_char_p]
     L.onilda_scorer_destroy.restype = None
     L.onilda_score.argtypes = [_vp, _vp, _vp, C.c_int64, _vp]
     L.onilda_score_flow_min.argtypes = [_vp, _vp, _vp, _vp, _vp, C.c_int64, _vp]
@@ -470,6 +474,11 @@ class EM:
         _check(lib().onilda_em_get_doc_sweeps(self._h, out))
         return out
 
+    def log_space_words(self):
+        n = C.c_int64()
+        _check(lib().onilda_em_log_space_words(self._h, C.byref(n)))
+        return n.value
+
     def stats(self, with_sweeps=False):
         e, m, l, s = C.c_double(), C.c_double(), C.c_int64(), C.c_int64()
         _check(lib().onilda_em_stats(self._h, C.byref(e), C.byref(m), C.byref(l), C.byref(s) if with_sweeps else None))
@@ -624,6 +633,16 @@ class Scorer:
                                          _ptr(idx), _ptr(ss), _ptr(ds), C.byref(m)))
         return idx[:m.value].copy(), ss[:m.value].copy(), ds[:m.value].copy()
 
+    def results_rows(self, doc, word, threshold, k):
+        """dns / proxy: (event index, Score) of the kept rows, most suspicious first (DNSPostLDA.scala:44-70)."""
+        a = [np.ascontiguousarray(x, np.int32) for x in (doc, word)]
+        n = len(a[0])
+        cap = max(1, n if k == -1 else min(k, n))
+        idx, sc = np.zeros(cap, np.int64), np.zeros(cap)
+        m = C.c_int64()
+        _check(lib().onilda_results_rows(self._h, _ptr(a[0]), _ptr(a[1]), n, threshold, k, _ptr(idx), _ptr(sc), C.byref(m)))
+        return idx[:m.value].copy(), sc[:m.value].copy()
+
     def score_raw(self, sdoc_ptr, sword_ptr, ddoc_ptr, dword_ptr, n, out_ptr):
         """Host pointers given as integers (e.g. pinned torch tensors' data_ptr())."""
         if ddoc_ptr:
@@ -658,6 +677,22 @@ class Scorer:
             self._h = None
 
     __del__ = close
+
+
+def java_double(v: float) -> str:
+    buf = C.create_string_buffer(40)
+    n = lib().onilda_format_java_double(float(v), buf)
+    return buf.raw[:n].decode()
+
+
+def results_write(path, rows, score_a, score_b=None, delimiter=","):
+    """<type>_results.csv: rows[i] + delimiter + score_a[i] [+ delimiter + score_b[i]]."""
+    rows = [r.encode() if isinstance(r, str) else r for r in rows]
+    arr = (C.c_char_p * max(len(rows), 1))(*rows)
+    a = np.ascontiguousarray(score_a, np.float64)
+    b = None if score_b is None else np.ascontiguousarray(score_b, np.float64)
+    _check(lib().onilda_results_write(str(path).encode(), arr, len(rows), _ptr(a), _ptr(b) if b is not None else None,
+                                      delimiter.encode()))
 
 
 NOALLOC_MAX_K = 4096

@@ -47,7 +47,7 @@ struct onilda_em {
     double *d_gamma, *d_doc_lik, *d_doc_ass;
     int32_t* d_doc_sweeps;
     unsigned long long* d_queue;   // [2]: bulk, long
-    int* d_error;
+    int* d_error;               // [0] NaN likelihood seen; [1] words redone in log space in the last E-step
     double* d_kv;               // [K][V] staging for import / export
     double* d_math_tab;         // psi rows, then the 2^(i/64) table (device_math.cuh)
     // stats
@@ -278,7 +278,7 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
     TRY(dev_alloc(&em->d_doc_ass, (size_t)D));
     TRY(dev_alloc(&em->d_doc_sweeps, (size_t)D));
     TRY(dev_alloc(&em->d_queue, 2));
-    TRY(dev_alloc(&em->d_error, 1));
+    TRY(dev_alloc(&em->d_error, 2));
     TRY(dev_alloc(&em->d_kv, (size_t)em->K * em->V));
     TRY(dev_alloc(&em->d_math_tab, (size_t)6 * kPsiRows + kExpTabSize));
     {
@@ -349,7 +349,7 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
         TRYCUDA(cudaStreamSynchronize(em->stream));   // the host vectors go out of scope
     }
     TRYCUDA(cudaMemsetAsync(em->d_ss, 0, sizeof(double) * (table_pad + SS_TAIL + lay.kpad), em->stream));
-    TRYCUDA(cudaMemsetAsync(em->d_error, 0, sizeof(int), em->stream));
+    TRYCUDA(cudaMemsetAsync(em->d_error, 0, 2 * sizeof(int), em->stream));
     TRY(upload_model(em, start->log_beta));
     TRYCUDA(cudaStreamSynchronize(em->stream));
 #undef TRY
@@ -407,6 +407,7 @@ static int run_estep(onilda_em* em, bool accumulate)
     a.class_word = accumulate ? em->d_ss : nullptr;
     a.error_flag = em->d_error;
     ONILDA_CUDA(cudaMemsetAsync(em->d_queue, 0, 2 * sizeof(unsigned long long), em->stream));
+    ONILDA_CUDA(cudaMemsetAsync(em->d_error + 1, 0, sizeof(int), em->stream));
     int rc;
     if (em->num_long > 0) {
         // fork: long documents first, on their own stream, one warp per block so that the block
@@ -805,6 +806,20 @@ extern "C" int onilda_em_get_doc_sweeps(onilda_em* em, int32_t* out)
     if (em->num_docs > 0)
         ONILDA_CUDA(cudaMemcpyAsync(out, em->d_doc_sweeps, sizeof(int32_t) * (size_t)em->num_docs, cudaMemcpyDeviceToHost, em->stream));
     ONILDA_CUDA(cudaStreamSynchronize(em->stream));
+    return ONILDA_OK;
+}
+
+// Words of the last E-step whose sum over topics left the range of the product form and were redone in log space
+// (estep.cu header; the reference works in log space throughout, lda-inference.c:52-68).  A diagnostic: the tests
+// use it to know that a constructed case really took that path.
+extern "C" int onilda_em_log_space_words(onilda_em* em, int64_t* count)
+{
+    if (!em || !count) return onilda_fail(ONILDA_EINVAL, "em_log_space_words: null argument");
+    DeviceGuard g(em->device);
+    int v = 0;
+    ONILDA_CUDA(cudaMemcpyAsync(&v, em->d_error + 1, sizeof v, cudaMemcpyDeviceToHost, em->stream));
+    ONILDA_CUDA(cudaStreamSynchronize(em->stream));
+    *count = v;
     return ONILDA_OK;
 }
 

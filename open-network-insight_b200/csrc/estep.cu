@@ -254,6 +254,7 @@ __global__ void __launch_bounds__(ONILDA_ESTEP_MAX_THREADS) estep_kernel(EStepAr
                 if (__builtin_expect(__any_sync(0xffffffffu, bad), 0)) {
                     // rare: redo this word in log space, as the reference does (lda-inference.c:52-68); out of
                     // line, through a scratch block that only this branch touches
+                    if (bad && j == 0) atomicAdd(a.error_flag + 1, 1);
                     LogSpaceWord<TPL> ls;
 #pragma unroll
                     for (int t = 0; t < TPL; t++) {

@@ -234,6 +234,7 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
                 // same in every lane): the word is done again in log space, as the reference does
                 // (lda-inference.c:52-68), from the state saved above.  Rare; kept out of line.
                 if (__builtin_expect((uint32_t)(double_hi(s) - 0x03C00000) >= (uint32_t)(0x7C200000 - 0x03C00000), 0)) {
+                    if (lane == 0) atomicAdd(a.error_flag + 1, 1);
                     LogSpaceWord<1> ls;
                     ls.psi[0] = psi_in;
                     ls.beta[0] = it.beta;

@@ -820,6 +820,35 @@ extern "C" int onilda_flow_results(onilda_scorer* s, const int32_t* sdoc, const 
     return rc;
 }
 
+// dns / proxy: one score per event (DNSPostLDA.scala:44, 75-92; ProxySuspiciousConnectsModel.scala:41-71), then
+// filter(score <= threshold), takeOrdered(k) with k == -1 meaning all, ascending (DNSPostLDA.scala:49-70,
+// ProxySuspiciousConnectsAnalysis.scala:45-51, DataFrameUtils.scala:21-38) in one call.  Ties, which Spark leaves in
+// no particular order, come out by event index.
+extern "C" int onilda_results_rows(onilda_scorer* s, const int32_t* doc, const int32_t* word, int64_t n, double threshold,
+                                   int64_t k, int64_t* idx_out, double* score_out, int64_t* n_out)
+{
+    if (!s || n < 0 || !n_out || k < -1 || (n > 0 && (!doc || !word)))
+        return onilda_fail(ONILDA_EINVAL, "results_rows: bad argument");
+    *n_out = 0;
+    if (n == 0 || k == 0) return ONILDA_OK;
+    if (!idx_out || !score_out) return onilda_fail(ONILDA_EINVAL, "results_rows: null output");
+    DeviceGuard g(s->device);
+    int32_t* d_ids = nullptr;
+    double* d_score = nullptr;
+    const size_t b = (sizeof(int32_t) * (size_t)n + 255) & ~(size_t)255;
+    if (cudaMalloc((void**)&d_ids, 2 * b) != cudaSuccess || cudaMalloc((void**)&d_score, sizeof(double) * (size_t)n) != cudaSuccess) {
+        cudaGetLastError();
+        cudaFree(d_ids);
+        return onilda_fail(ONILDA_ENOMEM, "results_rows: device memory for %lld events not available", (long long)n);
+    }
+    struct Free { void *a, *b; ~Free() { cudaFree(a); cudaFree(b); } } fr{d_ids, d_score};
+    int32_t* d_doc = d_ids;
+    int32_t* d_word = (int32_t*)((char*)d_ids + b);
+    ONILDA_CUDA(cudaMemcpyAsync(d_doc, doc, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, s->stream[0]));
+    ONILDA_CUDA(cudaMemcpyAsync(d_word, word, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, s->stream[0]));
+    return onilda_score_flow_topk_device(s, d_doc, d_word, nullptr, nullptr, n, threshold, k, idx_out, score_out, n_out, d_score);
+}
+
 extern "C" int onilda_scorer_stats(onilda_scorer* s, double* kernel_ms, int64_t* launches)
 {
     if (!s) return onilda_fail(ONILDA_EINVAL, "scorer_stats: null handle");

@@ -744,3 +744,92 @@ out:
     free(tmpname); free(line);
     return rc;
 }
+
+
+/*
+ * The results file.  The reference ends each analysis with
+ *     rows.map(_.mkString(outputDelimiter)).saveAsTextFile(path)
+ * (netflow/FlowPostLDA.scala:80, dns/DNSPostLDA.scala:69, proxy/ProxySuspiciousConnectsAnalysis.scala:51) and ml_ops.sh
+ * merges the parts into <type>_results.csv, which oni-oa reads (oa/flow/flow_oa.py:101).  A row is the event's own
+ * columns, then its word column(s), then the score column(s): SourceScore, DestinationScore for flow (the minimum is
+ * dropped, :80), Score for dns and proxy.  mkString prints a Double with Java's Double.toString.
+ */
+
+/* Java's Double.toString layout with the shortest digits that read back as the same double: plain decimal for
+ * 1e-3 <= |v| < 1e7 (at least one digit after the point), otherwise d.dddE[-]n.  JDK 19+ prints exactly this; older
+ * JDKs (Spark 1.6 ran on 7/8) print one digit more for a small share of values - the same double when parsed, which
+ * is how oni-oa reads the column.  Returns the length (no NUL); out needs 32 bytes. */
+int onilda_format_java_double(double v, char* out)
+{
+    if (isnan(v)) { memcpy(out, "NaN", 3); return 3; }
+    int n = 0;
+    if (signbit(v)) { out[n++] = '-'; v = -v; }
+    if (isinf(v)) { memcpy(out + n, "Infinity", 8); return n + 8; }
+    if (v == 0.0) { memcpy(out + n, "0.0", 3); return n + 3; }
+    char buf[40];
+    int prec;
+    for (prec = 2; prec <= 17; prec++) {            /* shortest digit string (two digits at least, as Java) that round-trips */
+        snprintf(buf, sizeof buf, "%.*e", prec - 1, v);
+        if (strtod(buf, NULL) == v) break;
+    }
+    /* buf = d[.ddd]e[+-]xx */
+    char digits[20];
+    int nd = 0;
+    const char* p = buf;
+    for (; *p && *p != 'e'; p++) if (*p >= '0' && *p <= '9') digits[nd++] = *p;
+    int e10 = atoi(p + 1);
+    while (nd > 1 && digits[nd - 1] == '0') nd--;
+    if (v >= 1e-3 && v < 1e7) {
+        if (e10 >= 0) {
+            for (int i = 0; i <= e10; i++) out[n++] = i < nd ? digits[i] : '0';
+            out[n++] = '.';
+            if (nd > e10 + 1) for (int i = e10 + 1; i < nd; i++) out[n++] = digits[i];
+            else out[n++] = '0';
+        } else {
+            out[n++] = '0';
+            out[n++] = '.';
+            for (int i = 0; i < -e10 - 1; i++) out[n++] = '0';
+            for (int i = 0; i < nd; i++) out[n++] = digits[i];
+        }
+    } else {
+        out[n++] = digits[0];
+        out[n++] = '.';
+        if (nd > 1) for (int i = 1; i < nd; i++) out[n++] = digits[i];
+        else out[n++] = '0';
+        out[n++] = 'E';
+        n += sprintf(out + n, "%d", e10);
+    }
+    return n;
+}
+
+/* rows[i] + delimiter + score_a[i] (+ delimiter + score_b[i] when score_b is given), one line per kept row, in the
+ * order given (the order of onilda_flow_results / onilda_results_rows).  Written to a temporary file and renamed. */
+int onilda_results_write(const char* path, const char* const* rows, int64_t m, const double* score_a, const double* score_b,
+                         const char* delimiter)
+{
+    if (!path || m < 0 || (m > 0 && (!rows || !score_a)) || !delimiter)
+        return onilda_fail(ONILDA_EINVAL, "results_write: bad argument");
+    size_t L = strlen(path);
+    char* tmpname = (char*)malloc(L + 8);
+    if (!tmpname) return onilda_fail(ONILDA_ENOMEM, "results_write: out of memory");
+    sprintf(tmpname, "%s.tmp", path);
+    int rc = ONILDA_OK;
+    FILE* f = fopen(tmpname, "w");
+    if (!f) { rc = onilda_fail(ONILDA_EIO, "cannot write %s", tmpname); free(tmpname); return rc; }
+    char num[40];
+    for (int64_t i = 0; i < m && rc == ONILDA_OK; i++) {
+        if (!rows[i]) { rc = onilda_fail(ONILDA_EINVAL, "results_write: row %lld is null", (long long)i); break; }
+        int k = onilda_format_java_double(score_a[i], num);
+        if (fputs(rows[i], f) < 0 || fputs(delimiter, f) < 0 || fwrite(num, 1, (size_t)k, f) != (size_t)k) rc = onilda_fail(ONILDA_EIO, "write failed on %s", tmpname);
+        if (rc == ONILDA_OK && score_b) {
+            k = onilda_format_java_double(score_b[i], num);
+            if (fputs(delimiter, f) < 0 || fwrite(num, 1, (size_t)k, f) != (size_t)k) rc = onilda_fail(ONILDA_EIO, "write failed on %s", tmpname);
+        }
+        if (rc == ONILDA_OK && fputc('\n', f) == EOF) rc = onilda_fail(ONILDA_EIO, "write failed on %s", tmpname);
+    }
+    if (fclose(f) != 0 && rc == ONILDA_OK) rc = onilda_fail(ONILDA_EIO, "close failed on %s", tmpname);
+    if (rc != ONILDA_OK) remove(tmpname);
+    else if (rename(tmpname, path) != 0) rc = onilda_fail(ONILDA_EIO, "cannot rename %s", tmpname);
+    free(tmpname);
+    return rc;
+}

@@ -20,6 +20,10 @@
  *     @native def topK(h: Long, score: Array[Double], threshold: Double, k: Long): Array[Long]
  *     @native def destroy(h: Long): Unit
  *   }
+ *
+ * Arrays are reached with Get<Type>ArrayElements / Release<Type>ArrayElements, not with the "critical" variants:
+ * every call here runs GPU work (copies, kernels, stream synchronisation) between get and release, and the JNI
+ * specification forbids blocking inside a critical region (the collector may be held off for its whole length).
  */
 #include <jni.h>
 #include <stdint.h>
@@ -29,6 +33,13 @@
 
 #define CLS "org_opennetworkinsight_OniGpuScorer_00024"
 #define FN(name) Java_org_opennetworkinsight_OniGpuScorer_00024_##name
+
+#define PIN_I(arr) ((arr) ? (*e)->GetIntArrayElements(e, (arr), NULL) : NULL)
+#define PIN_L(arr) ((arr) ? (*e)->GetLongArrayElements(e, (arr), NULL) : NULL)
+#define PIN_D(arr) ((arr) ? (*e)->GetDoubleArrayElements(e, (arr), NULL) : NULL)
+#define UNPIN_I(arr, p, mode) do { if (p) (*e)->ReleaseIntArrayElements(e, (arr), (p), (mode)); } while (0)
+#define UNPIN_L(arr, p, mode) do { if (p) (*e)->ReleaseLongArrayElements(e, (arr), (p), (mode)); } while (0)
+#define UNPIN_D(arr, p, mode) do { if (p) (*e)->ReleaseDoubleArrayElements(e, (arr), (p), (mode)); } while (0)
 
 static void throw_last(JNIEnv* e)
 {
@@ -40,12 +51,12 @@ JNIEXPORT jlong JNICALL FN(create)(JNIEnv* e, jobject self, jdoubleArray theta, 
                                    jint num_terms, jint k, jint device)
 {
     (void)self;
-    jdouble* t = (*e)->GetPrimitiveArrayCritical(e, theta, NULL);
-    jdouble* p = (*e)->GetPrimitiveArrayCritical(e, phi, NULL);
+    jdouble* t = PIN_D(theta);
+    jdouble* p = PIN_D(phi);
     onilda_scorer* s = NULL;
     int rc = (t && p) ? onilda_scorer_create(t, num_docs, p, num_terms, k, device, &s) : ONILDA_ENOMEM;
-    if (p) (*e)->ReleasePrimitiveArrayCritical(e, phi, p, JNI_ABORT);
-    if (t) (*e)->ReleasePrimitiveArrayCritical(e, theta, t, JNI_ABORT);
+    UNPIN_D(phi, p, JNI_ABORT);
+    UNPIN_D(theta, t, JNI_ABORT);
     if (rc != ONILDA_OK) { throw_last(e); return 0; }
     return (jlong)(intptr_t)s;
 }
@@ -55,21 +66,15 @@ static jdoubleArray score_common(JNIEnv* e, jlong h, jintArray a, jintArray b, j
     const jsize n = (*e)->GetArrayLength(e, a);
     jdoubleArray out = (*e)->NewDoubleArray(e, n);
     if (!out) return NULL;
-    jint* pa = (*e)->GetPrimitiveArrayCritical(e, a, NULL);
-    jint* pb = (*e)->GetPrimitiveArrayCritical(e, b, NULL);
-    jint* pc = c ? (*e)->GetPrimitiveArrayCritical(e, c, NULL) : NULL;
-    jint* pd = d ? (*e)->GetPrimitiveArrayCritical(e, d, NULL) : NULL;
-    jdouble* po = (*e)->GetPrimitiveArrayCritical(e, out, NULL);
+    jint *pa = PIN_I(a), *pb = PIN_I(b), *pc = PIN_I(c), *pd = PIN_I(d);
+    jdouble* po = PIN_D(out);
     int rc = ONILDA_ENOMEM;
     if (pa && pb && po && (!c || (pc && pd)))
         rc = c ? onilda_score_flow_min((onilda_scorer*)(intptr_t)h, (const int32_t*)pa, (const int32_t*)pb,
                                        (const int32_t*)pc, (const int32_t*)pd, n, po)
                : onilda_score((onilda_scorer*)(intptr_t)h, (const int32_t*)pa, (const int32_t*)pb, n, po);
-    if (po) (*e)->ReleasePrimitiveArrayCritical(e, out, po, 0);
-    if (pd) (*e)->ReleasePrimitiveArrayCritical(e, d, pd, JNI_ABORT);
-    if (pc) (*e)->ReleasePrimitiveArrayCritical(e, c, pc, JNI_ABORT);
-    if (pb) (*e)->ReleasePrimitiveArrayCritical(e, b, pb, JNI_ABORT);
-    if (pa) (*e)->ReleasePrimitiveArrayCritical(e, a, pa, JNI_ABORT);
+    UNPIN_D(out, po, 0);
+    UNPIN_I(d, pd, JNI_ABORT); UNPIN_I(c, pc, JNI_ABORT); UNPIN_I(b, pb, JNI_ABORT); UNPIN_I(a, pa, JNI_ABORT);
     if (rc != ONILDA_OK) { throw_last(e); return NULL; }
     return out;
 }
@@ -95,9 +100,9 @@ JNIEXPORT jlongArray JNICALL FN(topK)(JNIEnv* e, jobject self, jlong h, jdoubleA
     int64_t cap = (k < 0 || k > n) ? n : k, got = 0;
     int64_t* idx = malloc(sizeof(int64_t) * (size_t)(cap > 0 ? cap : 1));
     double* val = malloc(sizeof(double) * (size_t)(cap > 0 ? cap : 1));
-    jdouble* ps = (*e)->GetPrimitiveArrayCritical(e, score, NULL);
+    jdouble* ps = PIN_D(score);
     int rc = (idx && val && ps) ? onilda_topk((onilda_scorer*)(intptr_t)h, ps, n, threshold, k, idx, val, &got) : ONILDA_ENOMEM;
-    if (ps) (*e)->ReleasePrimitiveArrayCritical(e, score, ps, JNI_ABORT);
+    UNPIN_D(score, ps, JNI_ABORT);
     jlongArray out = NULL;
     if (rc == ONILDA_OK) {
         out = (*e)->NewLongArray(e, (jsize)got);
@@ -130,8 +135,6 @@ JNIEXPORT void JNICALL FN(destroy)(JNIEnv* e, jobject self, jlong h)
  *   @native def flowResults(h: Long, sdoc: Array[Int], sword: Array[Int], ddoc: Array[Int], dword: Array[Int],
  *                           threshold: Double, k: Long, idx: Array[Long], srcScore: Array[Double], dstScore: Array[Double]): Long
  */
-#define PIN(arr) ((arr) ? (*e)->GetPrimitiveArrayCritical(e, (arr), NULL) : NULL)
-#define UNPIN(arr, p, mode) do { if (p) (*e)->ReleasePrimitiveArrayCritical(e, (arr), (p), (mode)); } while (0)
 
 JNIEXPORT void JNICALL FN(flowWords)(JNIEnv* e, jobject self, jintArray hour, jintArray minute, jintArray second, jlongArray ibyt,
                                      jlongArray ipkt, jintArray sport, jintArray dport, jdoubleArray cuts, jintArray src_code,
@@ -139,9 +142,9 @@ JNIEXPORT void JNICALL FN(flowWords)(JNIEnv* e, jobject self, jintArray hour, ji
 {
     (void)self;
     const jsize n = (*e)->GetArrayLength(e, hour);
-    jint *h = PIN(hour), *m = PIN(minute), *s = PIN(second), *sp = PIN(sport), *dp = PIN(dport), *sc = PIN(src_code), *dc = PIN(dst_code);
-    jlong *b = PIN(ibyt), *p = PIN(ipkt);
-    jdouble* c = PIN(cuts);
+    jint *h = PIN_I(hour), *m = PIN_I(minute), *s = PIN_I(second), *sp = PIN_I(sport), *dp = PIN_I(dport), *sc = PIN_I(src_code), *dc = PIN_I(dst_code);
+    jlong *b = PIN_L(ibyt), *p = PIN_L(ipkt);
+    jdouble* c = PIN_D(cuts);
     onilda_flow_cuts fc;
     int rc = onilda_flow_words((const int32_t*)h, (const int32_t*)m, (const int32_t*)s, (const int64_t*)b, (const int64_t*)p,
                                (const int32_t*)sp, (const int32_t*)dp, n, -1, &fc, (int32_t*)sc, (int32_t*)dc);
@@ -149,9 +152,9 @@ JNIEXPORT void JNICALL FN(flowWords)(JNIEnv* e, jobject self, jintArray hour, ji
         for (int q = 0; q < 10; q++) { c[q] = fc.time[q]; c[10 + q] = fc.ibyt[q]; }
         for (int q = 0; q < 5; q++) c[20 + q] = fc.ipkt[q];
     }
-    UNPIN(cuts, c, 0); UNPIN(dst_code, dc, 0); UNPIN(src_code, sc, 0);
-    UNPIN(ipkt, p, JNI_ABORT); UNPIN(ibyt, b, JNI_ABORT); UNPIN(dport, dp, JNI_ABORT); UNPIN(sport, sp, JNI_ABORT);
-    UNPIN(second, s, JNI_ABORT); UNPIN(minute, m, JNI_ABORT); UNPIN(hour, h, JNI_ABORT);
+    UNPIN_D(cuts, c, 0); UNPIN_I(dst_code, dc, 0); UNPIN_I(src_code, sc, 0);
+    UNPIN_L(ipkt, p, JNI_ABORT); UNPIN_L(ibyt, b, JNI_ABORT); UNPIN_I(dport, dp, JNI_ABORT); UNPIN_I(sport, sp, JNI_ABORT);
+    UNPIN_I(second, s, JNI_ABORT); UNPIN_I(minute, m, JNI_ABORT); UNPIN_I(hour, h, JNI_ABORT);
     if (rc != ONILDA_OK) throw_last(e);
 }
 
@@ -168,11 +171,11 @@ JNIEXPORT jlong JNICALL FN(pairsCount)(JNIEnv* e, jobject self, jintArray doc, j
 {
     (void)self;
     const jsize n = (*e)->GetArrayLength(e, doc);
-    jint *d = PIN(doc), *w = PIN(word), *od = PIN(doc_out), *ow = PIN(word_out), *oc = PIN(count_out);
+    jint *d = PIN_I(doc), *w = PIN_I(word), *od = PIN_I(doc_out), *ow = PIN_I(word_out), *oc = PIN_I(count_out);
     int64_t m = 0;
     int rc = onilda_pairs_count((const int32_t*)d, (const int32_t*)w, n, num_docs, num_terms, -1, (int32_t*)od, (int32_t*)ow,
                                 (int32_t*)oc, &m);
-    UNPIN(count_out, oc, 0); UNPIN(word_out, ow, 0); UNPIN(doc_out, od, 0); UNPIN(word, w, JNI_ABORT); UNPIN(doc, d, JNI_ABORT);
+    UNPIN_I(count_out, oc, 0); UNPIN_I(word_out, ow, 0); UNPIN_I(doc_out, od, 0); UNPIN_I(word, w, JNI_ABORT); UNPIN_I(doc, d, JNI_ABORT);
     if (rc != ONILDA_OK) { throw_last(e); return 0; }
     return (jlong)m;
 }
@@ -182,10 +185,10 @@ JNIEXPORT jlong JNICALL FN(corpusFromTriples)(JNIEnv* e, jobject self, jintArray
 {
     (void)self;
     const jsize n = (*e)->GetArrayLength(e, doc);
-    jint *d = PIN(doc), *w = PIN(word), *c = PIN(count);
+    jint *d = PIN_I(doc), *w = PIN_I(word), *c = PIN_I(count);
     onilda_corpus* corpus = NULL;
     int rc = onilda_corpus_from_triples((const int32_t*)d, (const int32_t*)w, (const int32_t*)c, n, num_docs, num_terms, -1, &corpus);
-    UNPIN(count, c, JNI_ABORT); UNPIN(word, w, JNI_ABORT); UNPIN(doc, d, JNI_ABORT);
+    UNPIN_I(count, c, JNI_ABORT); UNPIN_I(word, w, JNI_ABORT); UNPIN_I(doc, d, JNI_ABORT);
     if (rc != ONILDA_OK) { throw_last(e); return 0; }
     return (jlong)(intptr_t)corpus;
 }
@@ -208,14 +211,32 @@ JNIEXPORT jlong JNICALL FN(flowResults)(JNIEnv* e, jobject self, jlong h, jintAr
 {
     (void)self;
     const jsize n = (*e)->GetArrayLength(e, sdoc);
-    jint *a = PIN(sdoc), *b = PIN(sword), *c = PIN(ddoc), *d = PIN(dword);
-    jlong* oi = PIN(idx);
-    jdouble *os = PIN(src_score), *od = PIN(dst_score);
+    jint *a = PIN_I(sdoc), *b = PIN_I(sword), *c = PIN_I(ddoc), *d = PIN_I(dword);
+    jlong* oi = PIN_L(idx);
+    jdouble *os = PIN_D(src_score), *od = PIN_D(dst_score);
     int64_t kept = 0;
     int rc = onilda_flow_results((onilda_scorer*)(intptr_t)h, (const int32_t*)a, (const int32_t*)b, (const int32_t*)c,
                                  (const int32_t*)d, n, threshold, k, (int64_t*)oi, os, od, &kept);
-    UNPIN(dst_score, od, 0); UNPIN(src_score, os, 0); UNPIN(idx, oi, 0);
-    UNPIN(dword, d, JNI_ABORT); UNPIN(ddoc, c, JNI_ABORT); UNPIN(sword, b, JNI_ABORT); UNPIN(sdoc, a, JNI_ABORT);
+    UNPIN_D(dst_score, od, 0); UNPIN_D(src_score, os, 0); UNPIN_L(idx, oi, 0);
+    UNPIN_I(dword, d, JNI_ABORT); UNPIN_I(ddoc, c, JNI_ABORT); UNPIN_I(sword, b, JNI_ABORT); UNPIN_I(sdoc, a, JNI_ABORT);
+    if (rc != ONILDA_OK) { throw_last(e); return 0; }
+    return (jlong)kept;
+}
+
+/* dns / proxy rows (onilda_results_rows):
+ *   @native def resultsRows(h: Long, doc: Array[Int], word: Array[Int], threshold: Double, k: Long,
+ *                           idx: Array[Long], score: Array[Double]): Long */
+JNIEXPORT jlong JNICALL FN(resultsRows)(JNIEnv* e, jobject self, jlong h, jintArray doc, jintArray word, jdouble threshold, jlong k,
+                                        jlongArray idx, jdoubleArray score)
+{
+    (void)self;
+    const jsize n = (*e)->GetArrayLength(e, doc);
+    jint *a = PIN_I(doc), *b = PIN_I(word);
+    jlong* oi = PIN_L(idx);
+    jdouble* os = PIN_D(score);
+    int64_t kept = 0;
+    int rc = onilda_results_rows((onilda_scorer*)(intptr_t)h, (const int32_t*)a, (const int32_t*)b, n, threshold, k, (int64_t*)oi, os, &kept);
+    UNPIN_D(score, os, 0); UNPIN_L(idx, oi, 0); UNPIN_I(word, b, JNI_ABORT); UNPIN_I(doc, a, JNI_ABORT);
     if (rc != ONILDA_OK) { throw_last(e); return 0; }
     return (jlong)kept;
 }

@@ -446,3 +446,43 @@ def run_ref(args, cwd, seed=None, nproc=1, timeout=3600):
         env.pop("ONI_MPI_STUB_NP", None)
     return subprocess.run([str(REF_BIN)] + [str(a) for a in args], cwd=str(cwd), env=env,
                           capture_output=True, text=True, timeout=timeout, check=True)
+
+
+def java_double_str(v):
+    """Java's Double.toString(v) as JDK 19+ prints it (shortest digits that read back as v; older JDKs print one
+    more digit for a small share of values): decimal for 1e-3 <= |v| < 1e7, else d.dddE[-]n.  Digits from Python's
+    repr (shortest round trip).  This is the form of the score columns of <type>_results.csv: the reference writes
+    rows with `_.mkString(outputDelimiter)` (netflow/FlowPostLDA.scala:80, dns/DNSPostLDA.scala:69)."""
+    import math
+    from decimal import Decimal
+    if math.isnan(v):
+        return "NaN"
+    sign = "-" if math.copysign(1.0, v) < 0 else ""
+    v = abs(v)
+    if math.isinf(v):
+        return sign + "Infinity"
+    if v == 0:
+        return sign + "0.0"
+    t = Decimal(repr(v)).as_tuple()
+    if len(t.digits) == 1:                          # Java prints two digits at least, the closest ones
+        t = Decimal("%.1e" % v).as_tuple()
+    digits = "".join(map(str, t.digits)).rstrip("0") or "0"
+    e10 = len(t.digits) + t.exponent - 1            # exponent of the first digit
+    if 1e-3 <= v < 1e7:
+        if e10 >= 0:
+            ip = (digits + "0" * (e10 + 1))[:e10 + 1]
+            fp = digits[e10 + 1:] or "0"
+            return f"{sign}{ip}.{fp}"
+        return f"{sign}0.{'0' * (-e10 - 1)}{digits}"
+    return f"{sign}{digits[0]}.{digits[1:] or '0'}E{e10}"
+
+
+def results_lines(rows, score_a, score_b=None, delimiter=","):
+    """Lines of <type>_results.csv: the event's own columns (already joined), then the score column(s)."""
+    out = []
+    for i, r in enumerate(rows):
+        cols = [r, java_double_str(float(score_a[i]))]
+        if score_b is not None:
+            cols.append(java_double_str(float(score_b[i])))
+        out.append(delimiter.join(cols))
+    return out

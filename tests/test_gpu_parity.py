@@ -266,6 +266,41 @@ def test_invariants_at_scale(oni, corpusgen):
     em.close()
 
 
+@pytest.mark.parametrize("long_kernel", [False, True])
+def test_log_space_redo_of_a_word(oni, oracle, long_kernel, monkeypatch):
+    """The product form phi = E beta' / s leaves its range when the only topics that give a word real probability
+    have exp(digamma(gamma)) underflown (gamma ~ alpha = 0.001, digamma ~ -1000) and the topics with mass have
+    log_beta = -700 for it: s ~ 1e-300.  Such a word is redone in log space, as the reference computes every word
+    (lda-inference.c:52-68).  Both kernels, against the oracle; the handle reports that the path was taken."""
+    if long_kernel:
+        monkeypatch.setenv("ONILDA_LONG_LEN", "1")
+    K, V = 4, 8
+    lb = np.full((K, V), -700.0)
+    lb[0, :4] = np.log(0.25)
+    lb[1, 4:] = np.log(0.25)
+    lb[3, :] = -650.0
+    docs = [[(0, 400), (1, 300), (2, 500), (5, 1)], [(4, 50), (5, 60), (0, 1), (6, 2)], [(1, 1), (6, 1)], [(3, 2000), (7, 3), (2, 5)]]
+    off = np.array([0] + list(np.cumsum([len(d) for d in docs])), np.int64)
+    w = np.array([x for d in docs for x, _ in d], np.int32)
+    cn = np.array([y for d in docs for _, y in d], np.int32)
+    c = oni.Corpus.from_csr(off, w, cn, num_terms=V)
+    for alpha, expect_redo in ((0.001, True), (0.02, None), (2.5, False)):
+        m = oni.Model.new(K, V)
+        m.log_beta[...] = lb
+        m.alpha = alpha
+        st = oni.Settings(20, 1e-6, 3, 1e-6, 0)
+        ref = oracle.e_step(off, w, cn, V, alpha, lb, st.var_max_iter, st.var_converged)
+        em = oni.EM(c, m, st)
+        em.estep()
+        if expect_redo is not None:
+            assert (em.log_space_words() > 0) == expect_redo, (alpha, em.log_space_words())
+        assert rel_err(em.doc_likelihood(), ref["doc_lik"], 1e-9) < 1e-10
+        assert rel_err(em.gamma(), ref["gamma"], 1e-9) < 1e-9
+        lik, _, _ = em.mstep()
+        assert abs(lik - ref["lik"]) / abs(ref["lik"]) < 1e-12
+        em.close()
+
+
 def test_var_max_iter_special_values(oni, oracle):
     """-1 = unbounded; 0 or below -1 = the sweep loop is never entered (lda-inference.c:46-47)."""
     d = GOLD / "k5"
@@ -788,6 +823,30 @@ def test_flow_results_rows(oni, oracle):
         assert np.array_equal(ss, rs[ridx]) and np.array_equal(ds, rd[ridx])
     idx, ss, ds = sc.flow_results([], [], [], [], 1.0, 10)
     assert len(idx) == 0
+    sc.close()
+
+
+def test_dns_proxy_results_rows(oni, oracle, tmp_path):
+    """N3 for the one-sided analyses: score(client ip, word), score <= threshold, takeOrdered(k) with k == -1 = all,
+    ascending (DNSPostLDA.scala:44-70, ProxySuspiciousConnectsAnalysis.scala:45-51, DataFrameUtils.scala:21-38) in
+    one call, bit for bit against the oracle, ties included; then the file."""
+    rng = np.random.default_rng(78)
+    D, V, K, n = 2000, 600, 20, 300_000
+    theta = rng.dirichlet(np.full(K, 0.1), D)
+    phi = rng.dirichlet(np.full(V, 0.05), K).T.copy()
+    doc, word = rng.integers(-1, D, n).astype(np.int32), rng.integers(-1, V, n).astype(np.int32)
+    doc[:4000], word[:4000] = doc[4000:8000], word[4000:8000]          # tied scores across events
+    sc = oni.Scorer(theta, phi)
+    ref = oracle.score(doc, word, theta, phi)                          # unknown ip or word: the uniform row, no join here
+    for threshold, k in [(1.0, 1000), (float(np.quantile(ref, 0.002)), -1), (0.0, 10), (1.0, 17), (1e-3, 5000)]:
+        idx, s = sc.results_rows(doc, word, threshold, k)
+        ridx, rs = oracle.topk(ref, threshold, k)
+        assert np.array_equal(idx, ridx) and np.array_equal(s, rs)
+    idx, s = sc.results_rows(doc, word, 1.0, 300)
+    rows = [f"ev{i},{doc[i]},{word[i]}" for i in idx]
+    oni.results_write(tmp_path / "dns_results.csv", rows, s, None, ",")
+    assert (tmp_path / "dns_results.csv").read_text().splitlines() == oracle.results_lines(rows, s, None, ",")
+    assert len(sc.results_rows([], [], 1.0, 10)[0]) == 0
     sc.close()
 
 

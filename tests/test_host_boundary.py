@@ -280,3 +280,51 @@ def test_parallel_writer_is_byte_identical(oni, tmp_path, monkeypatch):
     first = out["1"][0].split(b"\n", 1)[0].decode()
     assert first == " ".join("%5.10f" % v for v in g[0])
     assert out["1"][1].split(b"\n", 1)[0].decode() == "".join(" %5.10f" % v for v in m.log_beta[0])
+
+
+def test_java_double_layout(oni, oracle):
+    """The score columns of <type>_results.csv are Scala Doubles printed by mkString, i.e. Double.toString: the
+    documented examples of its layout, the doubles of OniLDACWrapperTest.scala, and random values against the
+    restatement (which takes its digits from Python's shortest repr)."""
+    known = {1.0: "1.0", 0.05: "0.05", 100.0: "100.0", 1234567.0: "1234567.0", 1.0e7: "1.0E7", 12345678.0: "1.2345678E7",
+             0.001: "0.001", 0.00099: "9.9E-4", 1e-4: "1.0E-4", 6.379973716629045E-4: "6.379973716629045E-4",
+             0.010333787125924218: "0.010333787125924218", 0.9993620026283371: "0.9993620026283371", 0.0: "0.0",
+             4.9e-324: "4.9E-324", 1.7976931348623157e308: "1.7976931348623157E308", -2.5: "-2.5", 3.0e-10: "3.0E-10",
+             float("inf"): "Infinity", 123456.789: "123456.789", 0.5: "0.5", 2e-3: "0.002"}
+    for v, want in known.items():
+        assert oni.java_double(v) == want == oracle.java_double_str(v), v
+    rng = np.random.default_rng(9)
+    vals = np.concatenate([rng.random(3000), np.exp(rng.uniform(-40, 20, 3000)), rng.random(500) * 1e-3, rng.random(500) * 2e7])
+    for v in vals:
+        got = oni.java_double(float(v))
+        assert got == oracle.java_double_str(float(v)) and float(got.replace("E", "e")) == v
+
+
+def test_results_file_writer(oni, oracle, tmp_path):
+    """flow_results.csv (two score columns) and dns_results.csv (one): the caller's rows, then the scores."""
+    rng = np.random.default_rng(10)
+    rows = [f"2016-07-08 0{i % 10}:11:2{i % 7},10.0.{i % 5}.{i},172.16.0.{i % 9},{i * 37 % 65536},80,TCP,{i}_word,-1_{i}_word" for i in range(200)]
+    a, b = rng.random(200) ** 8, rng.random(200) ** 8 * 1e-3
+    oni.results_write(tmp_path / "flow_results.csv", rows, a, b, ",")
+    assert (tmp_path / "flow_results.csv").read_text().splitlines() == oracle.results_lines(rows, a, b, ",")
+    oni.results_write(tmp_path / "dns_results.csv", rows[:50], a[:50], None, "\t")
+    assert (tmp_path / "dns_results.csv").read_text().splitlines() == oracle.results_lines(rows[:50], a[:50], None, "\t")
+    oni.results_write(tmp_path / "empty.csv", [], [], None, ",")
+    assert (tmp_path / "empty.csv").read_text() == ""
+    assert not list(tmp_path.glob("*.tmp"))
+
+
+def test_jni_shim_compiles(tmp_path):
+    """The JNI shim has no JDK to build against in this image; it is at least compiled (-Wall -Wextra -Werror, and
+    linked against libonilda so that every entry point it calls exists with that signature) against a
+    declaration-only subset of jni.h kept in tests/jni_stub/."""
+    import subprocess
+    pkg = ROOT / "open-network-insight_b200"
+    out = tmp_path / "libonilda_jni_check.so"
+    r = subprocess.run(["gcc", "-std=c11", "-Wall", "-Wextra", "-Werror", "-fPIC", "-shared", "-I", str(ROOT / "tests" / "jni_stub"),
+                        "-I", str(ROOT / "include"), str(pkg / "jni" / "onilda_jni.c"), "-L", str(pkg / "lib"), "-lonilda",
+                        "-Wl,--no-undefined", "-o", str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    syms = subprocess.run(["nm", "-D", "--defined-only", str(out)], capture_output=True, text=True).stdout
+    for name in ("create", "score", "scoreFlowMin", "topK", "destroy", "flowWords", "flowResults", "resultsRows", "corpusFromTriples"):
+        assert f"Java_org_opennetworkinsight_OniGpuScorer_00024_{name}" in syms
