@@ -169,7 +169,9 @@ __global__ void __launch_bounds__(ONILDA_ESTEP_MAX_THREADS) estep_kernel(EStepAr
         const double gamma0 = a.alpha + (total / ((double)K));
         double gam[TPL], psi[TPL], E[TPL];
 #pragma unroll
-        for (int t = 0; t < TPL; t++) gam[t] = valid[t] ? gamma0 : 1.0;
+        // a group without a document idles on gamma = 1: with its total of 0 it would start at alpha, and for
+        // alpha below ~0.0015 exp(digamma(alpha)) underflows, which would send every word of the warp down the rare path
+        for (int t = 0; t < TPL; t++) gam[t] = (valid[t] && has_doc) ? gamma0 : 1.0;
         psi_exp(gam, psi, E);
 
         double lik = 0.0, lik_old = 0.0, converged = 1.0;

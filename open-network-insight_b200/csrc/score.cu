@@ -147,7 +147,10 @@ __device__ __forceinline__ double2 ldg_pair(const double* p)
     return __ldg(reinterpret_cast<const double2*>(p));
 }
 
-template <bool FLOW>
+// CC: pairs per row when known at compile time (10 for ONI's K = 20, 25 for K = 50; 0: taken from K).  With it the
+// gather loop unrolls into 2*CC independent 16-byte loads per lane and side - the kernel waits on the memory system
+// (ncu: long scoreboard 16.8 per issued instruction with the rolled loop), so loads in flight are what it needs.
+template <bool FLOW, int CC>
 __global__ void __launch_bounds__(kScoreThreads) score_pairs_kernel(const double* __restrict__ theta, int64_t D,
                                                                     const double* __restrict__ phi, int32_t V, int K,
                                                                     const int32_t* __restrict__ sdoc,
@@ -159,8 +162,8 @@ __global__ void __launch_bounds__(kScoreThreads) score_pairs_kernel(const double
     extern __shared__ double smem[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    const int C = K >> 1;                 // pairs per row
-    const int stride = K + 2;             // C + 1 pairs: odd pair stride -> conflict-free 128-bit rows
+    const int C = CC ? CC : (K >> 1);     // pairs per row
+    const int stride = 2 * C + 2;         // C + 1 pairs: odd pair stride -> conflict-free 128-bit rows
     double* tile = smem + (size_t)warp * (32 * stride + 64);
     int* rows_t = reinterpret_cast<int*>(tile + 32 * stride);
     int* rows_p = rows_t + 32;
@@ -183,20 +186,44 @@ __global__ void __launch_bounds__(kScoreThreads) score_pairs_kernel(const double
             rows_p[lane] = (w0 >= 0 && w0 < V) ? w0 : (int)V;
             __syncwarp();
             int r = r0, q = q0;
-            for (int c = 0; c < C; c++) {
-                const double2 t2 = ldg_pair(theta + (int64_t)rows_t[r] * K + 2 * q);
-                const double2 p2 = ldg_pair(phi + (int64_t)rows_p[r] * K + 2 * q);
-                double2 pr;
-                pr.x = __dmul_rn(t2.x, p2.x);
-                pr.y = __dmul_rn(t2.y, p2.y);
-                *reinterpret_cast<double2*>(tile + r * stride + 2 * q) = pr;
-                r += dr;
-                q += dq;
-                if (q >= C) { q -= C; r++; }
+            if (CC) {
+                // all loads first, then the products: 2*CC requests in flight per lane
+                double2 t2[CC ? CC : 1], p2[CC ? CC : 1];
+                int rr[CC ? CC : 1], qq[CC ? CC : 1];
+#pragma unroll
+                for (int c = 0; c < CC; c++) {
+                    rr[c] = r;
+                    qq[c] = q;
+                    t2[c] = ldg_pair(theta + (int64_t)rows_t[r] * (2 * CC) + 2 * q);
+                    p2[c] = ldg_pair(phi + (int64_t)rows_p[r] * (2 * CC) + 2 * q);
+                    r += dr;
+                    q += dq;
+                    if (q >= C) { q -= C; r++; }
+                }
+#pragma unroll
+                for (int c = 0; c < CC; c++) {
+                    double2 pr;
+                    pr.x = __dmul_rn(t2[c].x, p2[c].x);
+                    pr.y = __dmul_rn(t2[c].y, p2[c].y);
+                    *reinterpret_cast<double2*>(tile + rr[c] * stride + 2 * qq[c]) = pr;
+                }
+            } else {
+                for (int c = 0; c < C; c++) {
+                    const double2 t2 = ldg_pair(theta + (int64_t)rows_t[r] * K + 2 * q);
+                    const double2 p2 = ldg_pair(phi + (int64_t)rows_p[r] * K + 2 * q);
+                    double2 pr;
+                    pr.x = __dmul_rn(t2.x, p2.x);
+                    pr.y = __dmul_rn(t2.y, p2.y);
+                    *reinterpret_cast<double2*>(tile + r * stride + 2 * q) = pr;
+                    r += dr;
+                    q += dq;
+                    if (q >= C) { q -= C; r++; }
+                }
             }
             __syncwarp();
             double s = 0.0;
             const double* mine = tile + lane * stride;
+#pragma unroll
             for (int c = 0; c < C; c++) {
                 const double2 v = *reinterpret_cast<const double2*>(mine + 2 * c);
                 s = __dadd_rn(s, v.x);      // no fma, fixed order: bit-identical to the sequential sum
@@ -556,8 +583,12 @@ int launch_score(onilda_scorer* s, cudaStream_t st, const int32_t* sdoc, const i
     if (blocks > cap) blocks = cap;
     if (use_pairs_kernel(s)) {
         const size_t sh = score_pairs_smem_bytes(s->K);
-        if (ddoc) score_pairs_kernel<true><<<(unsigned)blocks, kScoreThreads, sh, st>>>(s->d_theta, s->D, s->d_phi, s->V, s->K, sdoc, sword, ddoc, dword, n, out);
-        else score_pairs_kernel<false><<<(unsigned)blocks, kScoreThreads, sh, st>>>(s->d_theta, s->D, s->d_phi, s->V, s->K, sdoc, sword, nullptr, nullptr, n, out);
+#define ONILDA_PAIRS_LAUNCH(FLOWV, CCV) \
+        score_pairs_kernel<FLOWV, CCV><<<(unsigned)blocks, kScoreThreads, sh, st>>>(s->d_theta, s->D, s->d_phi, s->V, s->K, sdoc, sword, ddoc, dword, n, out)
+        if (s->K == 20) { if (ddoc) ONILDA_PAIRS_LAUNCH(true, 10); else ONILDA_PAIRS_LAUNCH(false, 10); }
+        else if (s->K == 50) { if (ddoc) ONILDA_PAIRS_LAUNCH(true, 25); else ONILDA_PAIRS_LAUNCH(false, 25); }
+        else { if (ddoc) ONILDA_PAIRS_LAUNCH(true, 0); else ONILDA_PAIRS_LAUNCH(false, 0); }
+#undef ONILDA_PAIRS_LAUNCH
         ONILDA_CUDA(cudaGetLastError());
         s->launches++;
         return ONILDA_OK;
@@ -615,11 +646,43 @@ extern "C" int onilda_scorer_create(const double* theta, int64_t num_docs, const
         fill_kernel<<<(K + 63) / 64, 64, 0, s->stream[0]>>>(s->d_phi + (size_t)num_terms * K, K, 1.0 / K);
         e = cudaGetLastError();
     }
+    // phi (16 MB at V = 100k, K = 20) is read by every event; ask L2 to keep it (a persisting access-policy window on
+    // the scorer's streams) so that the theta rows of rarely seen documents, streaming through, do not evict it.
+    // ONILDA_SCORE_L2_PERSIST=0 turns it off (for measurements).
+    {
+        const char* env = getenv("ONILDA_SCORE_L2_PERSIST");
+        int max_persist = 0, max_window = 0;
+        cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, device);
+        cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, device);
+        size_t bytes = sizeof(double) * (size_t)(num_terms + 1) * K;
+        if (!(env && atoi(env) == 0) && e == cudaSuccess && max_persist > 0 && max_window > 0 && bytes > 0) {
+            if (bytes > (size_t)max_window) bytes = (size_t)max_window;
+            size_t carve = bytes < (size_t)max_persist ? bytes : (size_t)max_persist;
+            if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve) == cudaSuccess) {
+                cudaStreamAttrValue av;
+                memset(&av, 0, sizeof av);
+                av.accessPolicyWindow.base_ptr = s->d_phi;
+                av.accessPolicyWindow.num_bytes = bytes;
+                av.accessPolicyWindow.hitRatio = carve >= bytes ? 1.0f : (float)carve / (float)bytes;
+                av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+                av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+                for (int i = 0; i < 2; i++) cudaStreamSetAttribute(s->stream[i], cudaStreamAttributeAccessPolicyWindow, &av);
+            }
+            cudaGetLastError();      // best effort: a refusal leaves the default policy
+        }
+    }
     const size_t shmem = score_smem_bytes(K);
     STEP(cudaFuncSetAttribute(score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
     STEP(cudaFuncSetAttribute(score_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
-    STEP(cudaFuncSetAttribute(score_pairs_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_pairs_smem_bytes(K)));
-    STEP(cudaFuncSetAttribute(score_pairs_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_pairs_smem_bytes(K)));
+    {
+        const int sh = (int)score_pairs_smem_bytes(K);
+        STEP(cudaFuncSetAttribute(score_pairs_kernel<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, sh));
+        STEP(cudaFuncSetAttribute(score_pairs_kernel<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, sh));
+        STEP(cudaFuncSetAttribute(score_pairs_kernel<true, 10>, cudaFuncAttributeMaxDynamicSharedMemorySize, sh));
+        STEP(cudaFuncSetAttribute(score_pairs_kernel<false, 10>, cudaFuncAttributeMaxDynamicSharedMemorySize, sh));
+        STEP(cudaFuncSetAttribute(score_pairs_kernel<true, 25>, cudaFuncAttributeMaxDynamicSharedMemorySize, sh));
+        STEP(cudaFuncSetAttribute(score_pairs_kernel<false, 25>, cudaFuncAttributeMaxDynamicSharedMemorySize, sh));
+    }
     STEP(cudaStreamSynchronize(s->stream[0]));
 #undef STEP
     if (e != cudaSuccess) {
