@@ -207,19 +207,28 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
                 return s;
             };
 
-            double s_prev = 1.0, c_prev = 0.0, lb_prev = 0.0;
+            // The likelihood needs sum_n c_n (lbmax_n + log s_n).  s_n is the same in every lane, so lane n mod 32 keeps word
+            // n's (s, c, lbmax) and every 32 words all lanes take ONE logarithm each: 1/32 of the logarithms per lane,
+            // and the word step loses ~20 instructions.  acc_lse is then a per-lane partial, summed with the other
+            // reductions at the end of the sweep.
+            double s_keep = 1.0, c_keep = 0.0, lb_keep = 0.0;
+            auto flush_logs = [&]() {
+                acc_lse = fma(c_keep, lb_keep + fast_log_tab(s_keep, tb), acc_lse);
+                c_keep = 0.0;
+                s_keep = 1.0;
+            };
             auto step = [&](const LongWord& it, int n) {
                 const double gam_in = gam, psi_in = psi, acc_psi_in = acc_psi;
                 const double x = E * it.beta;
                 const double s = sum_over_topics(x);
                 const double gpre = fma(-it.count, it.old_phi, gam);      // beside the chain
-                acc_lse = fma(c_prev, lb_prev + fast_log_tab(s_prev, tb), acc_lse);
                 const double r0 = rcp_seed(s);
                 double e = fma(-s, r0, 1.0);
                 e = fma(e, e, e);
-                s_prev = s;
-                c_prev = it.count;
-                lb_prev = it.lbmax;
+                const bool keeper = lane == (n & 31);
+                s_keep = keeper ? s : s_keep;
+                c_keep = keeper ? it.count : c_keep;
+                lb_keep = keeper ? it.lbmax : lb_keep;
                 const double xr = x * r0;
                 const double p = fma(xr, e, xr);
                 gam = fma(it.count, p, gpre);
@@ -243,9 +252,11 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
                     gam = fma(it.count, p2, fma(-it.count, it.old_phi, gam_in));
                     if (keep) *prow = p2;
                     acc_psi = fma(it.count * p2, psi_in, acc_psi_in);
-                    acc_lse = fma(it.count, it.lbmax + ls.lse, acc_lse);
-                    c_prev = 0.0;      // this word's log-sum is already in
-                    s_prev = 1.0;
+                    if (keeper) {      // this word's log-sum goes in directly
+                        acc_lse = fma(it.count, it.lbmax + ls.lse, acc_lse);
+                        c_keep = 0.0;
+                        s_keep = 1.0;
+                    }
                     const PsiExp pe2 = psi_exp_tab<true>(gam, tb);
                     psi = pe2.psi;
                     E = pe2.e;
@@ -276,6 +287,7 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
                     advance(n + 2, A, B);
                     advance(n + 3, B, A);
                 }
+                flush_logs();
                 blk++;
                 w0 = w1; c0 = c1;
                 w1 = w2; c1 = c2;
@@ -284,17 +296,17 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
             }
             cp_async_wait<0>();
             __syncwarp();
-            acc_lse = fma(c_prev, lb_prev + fast_log_tab(s_prev, tb), acc_lse);
 
             // likelihood bound of this sweep (lda-inference.c:93-127; estep.cu header)
-            double gs = valid ? gam : 0.0, lg = valid ? lgamma(gam) : 0.0, ap = acc_psi;
+            double gs = valid ? gam : 0.0, lg = valid ? lgamma(gam) : 0.0, ap = acc_psi, ls_all = acc_lse;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
                 gs += __shfl_xor_sync(FULL, gs, o);
                 lg += __shfl_xor_sync(FULL, lg, o);
                 ap += __shfl_xor_sync(FULL, ap, o);
+                ls_all += __shfl_xor_sync(FULL, ls_all, o);
             }
-            lik = a.lik_const - lgamma(gs) + lg - ap + acc_lse;
+            lik = a.lik_const - lgamma(gs) + lg - ap + ls_all;
             if (isnan(lik)) *a.error_flag = 1;   // the reference asserts here (lda-inference.c:78)
             converged = (lik_old - lik) / lik_old;
             lik_old = lik;
