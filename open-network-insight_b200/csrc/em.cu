@@ -25,7 +25,7 @@ struct onilda_em {
     int timing;
     int64_t num_long;           // documents of at least long_len entries: prefix of d_order
     int64_t long_max_total;     // most tokens in one of them (decides whether the table-only long kernel may run)
-    int long_len, long_group, long_smem, long_threads, long_per_sm, bulk_group, bulk_per_sm, bulk_threads;
+    int long_len, long_group, long_smem, long_threads, long_per_sm, bulk_group, bulk_per_sm, bulk_threads, pdl;
     // shard
     int64_t doc_begin, doc_end, num_docs, nnz;
     int K, V;
@@ -328,7 +328,9 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
         em->long_smem = env_smem ? atoi(env_smem) : 0;
         em->long_threads = env_lt ? atoi(env_lt) : 256;
         em->long_per_sm = env_lps ? atoi(env_lps) : 1;
-        em->bulk_threads = env_bt ? atoi(env_bt) : 256;
+        em->bulk_threads = env_bt ? atoi(env_bt) : 128;
+        const char* env_pdl = getenv("ONILDA_PDL");
+        em->pdl = env_pdl ? atoi(env_pdl) : 1;
         em->num_long = 0;
         if (em->long_len > 0 && em->long_group != lay.group)
             while (em->num_long < D && off[(size_t)order[(size_t)em->num_long] + 1] - off[(size_t)order[(size_t)em->num_long]] >= em->long_len) em->num_long++;
@@ -409,36 +411,56 @@ static int run_estep(onilda_em* em, bool accumulate)
     ONILDA_CUDA(cudaMemsetAsync(em->d_queue, 0, 2 * sizeof(unsigned long long), em->stream));
     ONILDA_CUDA(cudaMemsetAsync(em->d_error + 1, 0, sizeof(int), em->stream));
     int rc;
-    if (em->num_long > 0) {
-        // fork: long documents first, on their own stream, one warp per block so that the block
-        // scheduler spreads them over the SMs; the bulk launch fills the rest of the machine
-        ONILDA_CUDA(cudaEventRecord(em->ev_fork, em->stream));
-        ONILDA_CUDA(cudaStreamWaitEvent(em->long_stream, em->ev_fork, 0));
-        // ... and the main stream waits until the long stream has got past that wait: both launches then become
-        // runnable at the same moment and the long one, enqueued first on the higher-priority stream, gets its
-        // blocks placed first.  Without this the bulk launch can start alone, fill every SM with its persistent
-        // blocks, and the long documents run only after it (measured: 157 ms instead of 105 in one iteration of ten).
-        ONILDA_CUDA(cudaEventRecord(em->ev_forked, em->long_stream));
-        ONILDA_CUDA(cudaStreamWaitEvent(em->stream, em->ev_forked, 0));
+    if (em->num_long > 0 && em->pdl) {
+        // Both launches in ONE stream, the bulk one as the secondary of a programmatic dependent launch: its blocks are
+        // scheduled when every long-document block is resident (each executes griddepcontrol.launch_dependents when it
+        // starts), not when that kernel has finished.  With two streams the order in which the block scheduler took
+        // the two grids was a race: when the bulk grid, sized for the empty machine, got there first it filled every
+        // SM, the long documents ran only after it, and the E-step took 150-200 ms instead of 105 (about three
+        // iterations in eighteen of a bench run).
         EStepArgs b = a;
         b.order_begin = 0; b.order_count = em->num_long; b.queue = em->d_queue + 1;
-        // The staged one-document-per-warp kernel reads psi and exp(psi) from the tables only: every gamma of its
-        // documents, within [alpha, alpha + total], must lie inside their range (device_math.cuh).  Otherwise the
-        // general kernel, which has the closed forms, takes the long documents too.
         const bool tables_cover = em->alpha >= 1e-8 && em->alpha + (double)em->long_max_total + 1.0 < (double)(1 << kPsiOctaves) - 1.0;
         if (em->long_group == 32 && em->K <= 32 && tables_cover && !getenv("ONILDA_LONG_GENERIC"))
-            rc = launch_estep_long(b, em->sm_count, em->long_threads, em->long_per_sm, em->long_stream, &l);
+            rc = launch_estep_long(b, em->sm_count, em->long_threads, em->long_per_sm, em->stream, &l);
         else
-            rc = launch_estep(em->long_group, b, em->sm_count, em->long_threads, em->long_smem, em->long_per_sm, em->long_stream, &l);
+            rc = launch_estep(em->long_group, b, em->sm_count, em->long_threads, em->long_smem, em->long_per_sm, em->stream, &l);
         if (rc != ONILDA_OK) return rc;
-        if (em->timing) ONILDA_CUDA(cudaEventRecord(em->ev_long_end, em->long_stream));
-        ONILDA_CUDA(cudaEventRecord(em->ev_join, em->long_stream));
+        a.order_begin = em->num_long; a.order_count = em->num_docs - em->num_long; a.queue = em->d_queue;
+        rc = launch_estep(em->bulk_group, a, em->sm_count, em->bulk_threads, 0, em->bulk_per_sm, em->stream, &l, true);
+        if (rc != ONILDA_OK) return rc;
+    } else {
+        if (em->num_long > 0) {
+            // fork: long documents first, on their own stream, one warp per block so that the block
+            // scheduler spreads them over the SMs; the bulk launch fills the rest of the machine
+            ONILDA_CUDA(cudaEventRecord(em->ev_fork, em->stream));
+            ONILDA_CUDA(cudaStreamWaitEvent(em->long_stream, em->ev_fork, 0));
+            // ... and the main stream waits until the long stream has got past that wait: both launches then become
+            // runnable at the same moment and the long one, enqueued first on the higher-priority stream, gets its
+            // blocks placed first.  Without this the bulk launch can start alone, fill every SM with its persistent
+            // blocks, and the long documents run only after it (measured: 157 ms instead of 105 in one iteration of ten).
+            ONILDA_CUDA(cudaEventRecord(em->ev_forked, em->long_stream));
+            ONILDA_CUDA(cudaStreamWaitEvent(em->stream, em->ev_forked, 0));
+            EStepArgs b = a;
+            b.order_begin = 0; b.order_count = em->num_long; b.queue = em->d_queue + 1;
+            // The staged one-document-per-warp kernel reads psi and exp(psi) from the tables only: every gamma of its
+            // documents, within [alpha, alpha + total], must lie inside their range (device_math.cuh).  Otherwise the
+            // general kernel, which has the closed forms, takes the long documents too.
+            const bool tables_cover = em->alpha >= 1e-8 && em->alpha + (double)em->long_max_total + 1.0 < (double)(1 << kPsiOctaves) - 1.0;
+            if (em->long_group == 32 && em->K <= 32 && tables_cover && !getenv("ONILDA_LONG_GENERIC"))
+                rc = launch_estep_long(b, em->sm_count, em->long_threads, em->long_per_sm, em->long_stream, &l);
+            else
+                rc = launch_estep(em->long_group, b, em->sm_count, em->long_threads, em->long_smem, em->long_per_sm, em->long_stream, &l);
+            if (rc != ONILDA_OK) return rc;
+            if (em->timing) ONILDA_CUDA(cudaEventRecord(em->ev_long_end, em->long_stream));
+            ONILDA_CUDA(cudaEventRecord(em->ev_join, em->long_stream));
+        }
+        a.order_begin = em->num_long; a.order_count = em->num_docs - em->num_long; a.queue = em->d_queue;
+        rc = launch_estep(em->bulk_group, a, em->sm_count, em->bulk_threads, 0, em->num_long > 0 ? em->bulk_per_sm : 0, em->stream, &l);
+        if (rc != ONILDA_OK) return rc;
+        if (em->timing) ONILDA_CUDA(cudaEventRecord(em->ev_bulk_end, em->stream));
+        if (em->num_long > 0) ONILDA_CUDA(cudaStreamWaitEvent(em->stream, em->ev_join, 0));
     }
-    a.order_begin = em->num_long; a.order_count = em->num_docs - em->num_long; a.queue = em->d_queue;
-    rc = launch_estep(em->bulk_group, a, em->sm_count, em->bulk_threads, 0, em->num_long > 0 ? em->bulk_per_sm : 0, em->stream, &l);
-    if (rc != ONILDA_OK) return rc;
-    if (em->timing) ONILDA_CUDA(cudaEventRecord(em->ev_bulk_end, em->stream));
-    if (em->num_long > 0) ONILDA_CUDA(cudaStreamWaitEvent(em->stream, em->ev_join, 0));
     rc = launch_reduce_doc_stats(em->d_doc_lik, em->d_doc_ass, em->num_docs, em->d_partial, em->d_ss + table, em->stream, &l);
     if (rc != ONILDA_OK) return rc;
     ONILDA_CUDA(cudaEventRecord(em->ev1, em->stream));
@@ -570,7 +592,9 @@ static int mstep_group(onilda_em** ems, int n, double* likelihood, double* conve
         em->estep_done = 0;
         float ms = 0;
         if (cudaEventElapsedTime(&ms, em->ev0, em->ev1) == cudaSuccess) em->estep_ms = ms;
-        if (em->timing) {
+        if (em->timing && em->pdl && em->num_long > 0) {
+            fprintf(stderr, "[onilda] E-step %.2f ms (the two launches share one stream; ONILDA_PDL=0 times them apart)\n", em->estep_ms);
+        } else if (em->timing) {
             float tl = 0, tb = 0;
             if (em->num_long > 0) cudaEventElapsedTime(&tl, em->ev0, em->ev_long_end);
             cudaEventElapsedTime(&tb, em->ev0, em->ev_bulk_end);

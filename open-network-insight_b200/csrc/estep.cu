@@ -17,9 +17,7 @@
 //     Gauss-Seidel order of the reference is kept; parallelism is over topics
 //     and over documents only.
 //   * persistent warps take "bundles" of 32/G consecutive documents of a
-//     length-sorted order: the first bundle of every warp is fixed (warp w of
-//     block b takes bundle w*gridDim + b, which puts the longest documents on
-//     different SMs), the rest come from an atomic queue, so the groups of a
+//     length-sorted order from an atomic queue (longest first), so the groups of a
 //     warp run documents of near-equal length in lockstep and a warp that
 //     finishes early steals the next bundle.  Each document leaves the sweep
 //     loop on its own convergence test (in-kernel early exit).
@@ -104,6 +102,9 @@ __global__ void __launch_bounds__(ONILDA_ESTEP_MAX_THREADS) estep_kernel(EStepAr
     }
     // The shared-window addresses are taken once and pinned in registers (volatile asm): the compiler would
     // otherwise re-derive the window base from a special register at every use, a ~15-cycle read on the chain.
+    // a launch that must share the SMs with this one may be waiting for every block of this grid to be resident
+    // (programmatic dependent launch, em.cu); a no-op otherwise
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     SmemTables tb;
     tb.psi = (uint32_t)__cvta_generic_to_shared(smem_raw);
     tb.log = (uint32_t)__cvta_generic_to_shared(logtab);
@@ -112,25 +113,14 @@ __global__ void __launch_bounds__(ONILDA_ESTEP_MAX_THREADS) estep_kernel(EStepAr
 #endif
     tb.exp2 = tb.psi + (uint32_t)(sizeof(PsiRow) * kPsiRows);
 
-    const unsigned int warps_per_block = blockDim.x >> 5;
-    const unsigned long long first_bundle = (unsigned long long)(threadIdx.x >> 5) * gridDim.x + blockIdx.x;
-    const unsigned long long queue_base = (unsigned long long)gridDim.x * warps_per_block;
-    bool first_claim = true;
-
     for (;;) {
         // Warp-uniform values are produced with redux/vote (their results live in uniform
         // registers), so the compiler can prove the warp converged at every shuffle below and
         // emits them without a divergence branch (BRA.DIV), which would otherwise fence its
         // instruction scheduling around each one.
-        unsigned long long bundle;
-        if (first_claim) {
-            bundle = first_bundle;
-            first_claim = false;
-        } else {
-            unsigned int claimed = 0;
-            if (lane == 0) claimed = (unsigned int)atomicAdd(a.queue, 1ull);
-            bundle = queue_base + __reduce_max_sync(0xffffffffu, claimed);
-        }
+        unsigned int claimed = 0;
+        if (lane == 0) claimed = (unsigned int)atomicAdd(a.queue, 1ull);
+        const unsigned long long bundle = __reduce_max_sync(0xffffffffu, claimed);
         if (bundle >= num_bundles) break;
 
         const int64_t slot = (int64_t)bundle * DPW + grp;
@@ -389,7 +379,7 @@ __global__ void __launch_bounds__(ONILDA_ESTEP_MAX_THREADS) estep_kernel(EStepAr
 // capacity of `sm_count` SMs (or `max_blocks` when the launch shares the device with another).
 template <int G, int TPL, int KC>
 static int launch_one(const EStepArgs& args, int sm_count, int block_threads, int extra_smem, int max_per_sm,
-                      cudaStream_t stream)
+                      cudaStream_t stream, bool after_resident)
 {
     constexpr int DPW = 32 / G;
     const unsigned long long num_bundles = (unsigned long long)((args.order_count + DPW - 1) / DPW);
@@ -408,32 +398,49 @@ static int launch_one(const EStepArgs& args, int sm_count, int block_threads, in
     unsigned long long want = (num_bundles + wpb - 1) / wpb;
     unsigned long long grid = (unsigned long long)sm_count * per_sm;
     if (grid > want) grid = want;
-    estep_kernel<G, TPL, KC><<<(unsigned)grid, block_threads, smem, stream>>>(args, num_bundles);
+    if (after_resident) {
+        // secondary of a programmatic dependent launch: its blocks are scheduled once every block of the kernel before
+        // it in this stream has executed griddepcontrol.launch_dependents, i.e. is resident (it does not wait for
+        // that kernel to finish: no griddepcontrol.wait here)
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)grid);
+        cfg.blockDim = dim3((unsigned)block_threads);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        ONILDA_CUDA(cudaLaunchKernelEx(&cfg, estep_kernel<G, TPL, KC>, args, num_bundles));
+    } else {
+        estep_kernel<G, TPL, KC><<<(unsigned)grid, block_threads, smem, stream>>>(args, num_bundles);
+    }
     ONILDA_CUDA(cudaGetLastError());
     return ONILDA_OK;
 }
 
 template <int G>
 static int launch_group(int tpl, const EStepArgs& args, int sm_count, int block_threads, int extra_smem, int max_per_sm,
-                        cudaStream_t stream)
+                        cudaStream_t stream, bool after_resident)
 {
     // ONI's own topic counts (ml_ops.sh: TOPIC_COUNT=20; the proxy shape of BASELINE.json: 50) get kernels
     // with the count compiled in
     if (args.num_topics == 20 && args.kstride == kpad_for(20) && tpl == (20 + G - 1) / G)
-        return launch_one<G, (20 + G - 1) / G, 20>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
+        return launch_one<G, (20 + G - 1) / G, 20>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
     if (args.num_topics == 50 && args.kstride == kpad_for(50) && tpl == (50 + G - 1) / G) {
         if constexpr (G >= 8)
-            return launch_one<G, (50 + G - 1) / G, 50>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
+            return launch_one<G, (50 + G - 1) / G, 50>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
     }
     switch (tpl) {
-        case 1: return launch_one<G, 1, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
-        case 2: return launch_one<G, 2, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
-        case 3: return launch_one<G, 3, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
-        case 4: return launch_one<G, 4, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
-        case 5: return launch_one<G, 5, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
-        case 6: return launch_one<G, 6, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
-        case 7: return launch_one<G, 7, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
-        case 8: return launch_one<G, 8, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream);
+        case 1: return launch_one<G, 1, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
+        case 2: return launch_one<G, 2, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
+        case 3: return launch_one<G, 3, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
+        case 4: return launch_one<G, 4, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
+        case 5: return launch_one<G, 5, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
+        case 6: return launch_one<G, 6, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
+        case 7: return launch_one<G, 7, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
+        case 8: return launch_one<G, 8, 0>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
     }
     return onilda_fail(ONILDA_EINVAL, "unsupported topics-per-lane %d", tpl);
 }
@@ -442,16 +449,16 @@ static int launch_group(int tpl, const EStepArgs& args, int sm_count, int block_
 // document and `block_threads` threads per block.  args.queue must be zero (the caller
 // clears it on the same stream).
 int launch_estep(int group, const EStepArgs& args, int sm_count, int block_threads, int extra_smem, int max_per_sm,
-                 cudaStream_t stream, int* launches)
+                 cudaStream_t stream, int* launches, bool after_resident)
 {
     if (args.order_count <= 0) return ONILDA_OK;
     const int tpl = (args.num_topics + group - 1) / group;
     int rc;
     switch (group) {
-        case 4: rc = launch_group<4>(tpl, args, sm_count, block_threads, extra_smem, max_per_sm, stream); break;
-        case 8: rc = launch_group<8>(tpl, args, sm_count, block_threads, extra_smem, max_per_sm, stream); break;
-        case 16: rc = launch_group<16>(tpl, args, sm_count, block_threads, extra_smem, max_per_sm, stream); break;
-        case 32: rc = launch_group<32>(tpl, args, sm_count, block_threads, extra_smem, max_per_sm, stream); break;
+        case 4: rc = launch_group<4>(tpl, args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident); break;
+        case 8: rc = launch_group<8>(tpl, args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident); break;
+        case 16: rc = launch_group<16>(tpl, args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident); break;
+        case 32: rc = launch_group<32>(tpl, args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident); break;
         default: return onilda_fail(ONILDA_EINVAL, "unsupported lane group %d", group);
     }
     if (rc == ONILDA_OK && launches) *launches += 1;

@@ -89,6 +89,9 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
         for (int i = threadIdx.x; i < ring_doubles; i += blockDim.x) rings[i] = (i == 1) ? inv_K : 0.0;
         __syncthreads();
     }
+    // the bulk launch behind this one in the stream waits for every block of this grid to get here, i.e. to be
+    // resident (programmatic dependent launch, em.cu): the two launches then share every SM from the start
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     SmemTables tb;
     tb.psi = (uint32_t)__cvta_generic_to_shared(smem_raw);
     tb.log = (uint32_t)__cvta_generic_to_shared(logtab);
@@ -108,22 +111,20 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
     const bool stages = (uint32_t)piece < KS / 2;
     const uint32_t stage_dst = (stages_beta ? 0u : KS * 8u) + 16u * (uint32_t)piece;
 
-    const unsigned int warps_per_block = blockDim.x >> 5;
-    const unsigned long long first_doc = (unsigned long long)(threadIdx.x >> 5) * gridDim.x + blockIdx.x;
-    const unsigned long long queue_base = (unsigned long long)gridDim.x * warps_per_block;
-    bool first_claim = true;
+    // Documents are claimed from an atomic counter, longest first - but strided: claim q takes the document of rank
+    // (q mod 8) * ceil(n/8) + q / 8 of the length-sorted list, so the eight warps of a block, which claim together,
+    // get one document from each eighth of the list (one very long one per SM, not eight), and a block that the
+    // scheduler places late (it may have to wait for a bulk block to leave) simply takes shorter documents instead of
+    // holding back long ones that were promised to it.
+    const unsigned long long stratum = (num_docs + 7) / 8;
 
     for (;;) {
-        unsigned long long slot_in_order;
-        if (first_claim) {
-            slot_in_order = first_doc;
-            first_claim = false;
-        } else {
-            unsigned int claimed = 0;
-            if (lane == 0) claimed = (unsigned int)atomicAdd(a.queue, 1ull);
-            slot_in_order = queue_base + __reduce_max_sync(FULL, claimed);
-        }
-        if (slot_in_order >= num_docs) break;
+        unsigned int claimed = 0;
+        if (lane == 0) claimed = (unsigned int)atomicAdd(a.queue, 1ull);
+        const unsigned long long q = __reduce_max_sync(FULL, claimed);
+        if (q >= 8 * stratum) break;
+        const unsigned long long slot_in_order = (q & 7) * stratum + (q >> 3);
+        if (slot_in_order >= num_docs) continue;
 
         const int64_t d = a.order[a.order_begin + (int64_t)slot_in_order];
         const int64_t beg = a.offsets[d];

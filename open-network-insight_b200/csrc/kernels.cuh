@@ -80,7 +80,7 @@ struct EStepArgs {
 };
 
 int launch_estep(int group, const EStepArgs& args, int sm_count, int block_threads, int extra_smem, int max_per_sm,
-                 cudaStream_t stream, int* launches);
+                 cudaStream_t stream, int* launches, bool after_resident = false);
 
 // estep_long.cu: documents one per warp with staged rows (K <= 32)
 int launch_estep_long(const EStepArgs& args, int sm_count, int block_threads, int max_per_sm, cudaStream_t stream, int* launches);
