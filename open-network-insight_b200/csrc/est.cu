@@ -25,7 +25,8 @@ struct PeerPtrs {
 };
 
 // Device `me` owns elements [lo, hi): it reads that slice from every peer's
-// buffer (rank order 0..n-1, so every run gives the same bits), adds, and
+// buffer (rank order 0..n-1: the cross-device sum has a fixed order; each device's own buffer was filled
+// with fp64 atomics, so its inputs still vary in the last bits from run to run), adds, and
 // stores the sum into every peer's buffer.  Loads and stores on peer pointers
 // travel over NVLink; slices of different devices are disjoint.
 __global__ void __launch_bounds__(256) peer_sum_kernel(PeerPtrs p, int64_t lo, int64_t hi)
@@ -192,7 +193,7 @@ extern "C" int onilda_run_em(const char* start, const char* directory, const oni
         for (onilda_em* em : set.ems) { rc = onilda_em_estep(em); if (rc != ONILDA_OK) break; }
         double lik = 0, conv = 0;
         if (rc == ONILDA_OK && peer_sum) {
-            // the deterministic alternative: fixed-order sums over peer memory, then the whole M-step on every device
+            // the fixed-order alternative: sums over peer memory in rank order, then the whole M-step on every device
             if (ndev > 1) rc = onilda_em_allreduce_peer(set.ems.data(), ndev);
             if (rc == ONILDA_OK)
                 for (onilda_em* em : set.ems) { rc = onilda_em_mstep(em, &lik, &conv, &keep); if (rc != ONILDA_OK) break; }

@@ -8,7 +8,8 @@
 //     beta_scaled[w][k]   exp(log_beta_wk[w][k] - lbmax[w])   (what the E-step reads)
 // Sufficient statistics class_word are kept in the same [V][kpad] layout and
 // class_total[k] is formed here as its column sum (fixed-order two-stage
-// reduction, so the result does not depend on atomics order).
+// reduction: this step adds no order dependence of its own; class_word itself was
+// accumulated with fp64 atomics in the E-step and is reproducible only to ~1e-14 relative).
 #include "kernels.cuh"
 
 namespace onilda {
