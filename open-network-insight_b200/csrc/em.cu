@@ -421,7 +421,7 @@ static int run_estep(onilda_em* em, bool accumulate)
         EStepArgs b = a;
         b.order_begin = 0; b.order_count = em->num_long; b.queue = em->d_queue + 1;
         const bool tables_cover = em->alpha >= 1e-8 && em->alpha + (double)em->long_max_total + 1.0 < (double)(1 << kPsiOctaves) - 1.0;
-        if (em->long_group == 32 && em->K <= 32 && tables_cover && !getenv("ONILDA_LONG_GENERIC"))
+        if (em->long_group == 32 && em->K <= 64 && tables_cover && !getenv("ONILDA_LONG_GENERIC"))
             rc = launch_estep_long(b, em->sm_count, em->long_threads, em->long_per_sm, em->stream, &l);
         else
             rc = launch_estep(em->long_group, b, em->sm_count, em->long_threads, em->long_smem, em->long_per_sm, em->stream, &l);
@@ -447,7 +447,7 @@ static int run_estep(onilda_em* em, bool accumulate)
             // documents, within [alpha, alpha + total], must lie inside their range (device_math.cuh).  Otherwise the
             // general kernel, which has the closed forms, takes the long documents too.
             const bool tables_cover = em->alpha >= 1e-8 && em->alpha + (double)em->long_max_total + 1.0 < (double)(1 << kPsiOctaves) - 1.0;
-            if (em->long_group == 32 && em->K <= 32 && tables_cover && !getenv("ONILDA_LONG_GENERIC"))
+            if (em->long_group == 32 && em->K <= 64 && tables_cover && !getenv("ONILDA_LONG_GENERIC"))
                 rc = launch_estep_long(b, em->sm_count, em->long_threads, em->long_per_sm, em->long_stream, &l);
             else
                 rc = launch_estep(em->long_group, b, em->sm_count, em->long_threads, em->long_smem, em->long_per_sm, em->long_stream, &l);

@@ -1,4 +1,4 @@
-// E-step for LONG documents (K <= 32): one document per warp, one topic per lane, the rows of the
+// E-step for LONG documents (K <= 64): one document per warp, one topic per lane (two for K > 32), the rows of the
 // words ahead staged through a per-warp ring in shared memory.
 //
 // Why a kernel of its own.  The words of a document are a serial chain (Gauss-Seidel order of
@@ -54,13 +54,15 @@ __device__ __forceinline__ double lds64(uint32_t addr)
     return v;
 }
 
+template <int TPL>
 struct LongWord {
-    double count, lbmax, beta, old_phi;
+    double count, lbmax, beta[TPL], old_phi[TPL];
 };
 
 }  // namespace
 
-template <int KC>
+// TPL: topics per lane (1 for K <= 32, 2 for K <= 64); lane j holds topics j and j + 32
+template <int KC, int TPL>
 __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCKS) estep_long_kernel(EStepArgs a, unsigned long long num_docs)
 {
     constexpr unsigned FULL = 0xffffffffu;
@@ -68,7 +70,9 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
     const int K = KC ? KC : a.num_topics;
     const uint32_t KS = KC ? (uint32_t)kpad_for(KC) : (uint32_t)a.kstride;
     const int32_t idle_word = a.idle_row;
-    const bool valid = lane < K;
+    bool valid[TPL];
+#pragma unroll
+    for (int t = 0; t < TPL; t++) valid[t] = t * 32 + lane < K;
     const double inv_K = 1.0 / K;
 
     const double* __restrict__ beta_scaled = a.beta_scaled;
@@ -104,10 +108,14 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
     // two constants in front of the rings, read by address where a lane has nothing of its own to read:
     // 0.0 (beta' of a lane beyond K) and phi before the first sweep (1/K, lda-inference.c:41; 0 beyond K)
     const uint32_t zero_word = ring_base;
-    const uint32_t start_word = valid ? ring_base + 8u : ring_base;
-    // this lane's part in staging a word: lanes 0..15 move 16-byte pieces of the beta' row, lanes 16..31 of the phi row
-    const int piece = lane & 15;
-    const bool stages_beta = lane < 16;
+    uint32_t start_word[TPL];
+#pragma unroll
+    for (int t = 0; t < TPL; t++) start_word[t] = valid[t] ? ring_base + 8u : ring_base;
+    // this lane's part in staging a word.  One topic per lane (rows of at most 32 doubles): lanes 0..15 move 16-byte pieces
+    // of the beta' row, lanes 16..31 of the phi row, one copy instruction.  Two topics per lane (rows of up to 64 doubles):
+    // every lane moves a piece of the beta' row and, with a second instruction, the same piece of the phi row.
+    const int piece = TPL == 1 ? (lane & 15) : lane;
+    const bool stages_beta = TPL == 1 ? lane < 16 : true;
     const bool stages = (uint32_t)piece < KS / 2;
     const uint32_t stage_dst = (stages_beta ? 0u : KS * 8u) + 16u * (uint32_t)piece;
 
@@ -137,14 +145,19 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
 
         // every gamma of a document stays within [alpha, alpha + total]: the caller (em.cu) sends only documents for
         // which that interval lies inside the tables' range
-        auto psi_exp = [&](double g, double& psi, double& E) {
-            const PsiExp pe = psi_exp_tab<true>(g, tb);
-            psi = pe.psi;
-            E = pe.e;
+        auto psi_exp = [&](const double (&g)[TPL], double (&psi)[TPL], double (&E)[TPL]) {
+#pragma unroll
+            for (int t = 0; t < TPL; t++) {
+                const PsiExp pe = psi_exp_tab<true>(g[t], tb);
+                psi[t] = pe.psi;
+                E[t] = pe.e;
+            }
         };
 
         const double gamma0 = a.alpha + (total / ((double)K));
-        double gam = valid ? gamma0 : 1.0, psi, E;
+        double gam[TPL], psi[TPL], E[TPL];
+#pragma unroll
+        for (int t = 0; t < TPL; t++) gam[t] = valid[t] ? gamma0 : 1.0;
         psi_exp(gam, psi, E);
 
         double lik = 0.0, lik_old = 0.0, converged = 1.0;
@@ -185,17 +198,22 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
                 // past the end of the document the id is the table's idle row (beta' = 1, lbmax = 0): a phantom word
                 // then finds a harmless slot; phi rows past the end belong to other documents and are not touched
                 cp_async16_if(stages && (stages_beta || (!first && m < len)), slot + stage_dst, src);
+                if (TPL > 1) cp_async16_if(stages && !first && m < len, slot + KS * 8u + 16u * (uint32_t)piece, stage_src_phi + (uint64_t)(uint32_t)m * KS);
                 cp_async8_if(lane == 31, slot + 2u * KS * 8u, lbmax + w);
                 cp_async_commit();
             };
             // the staged rows of word m into registers (m's group has landed and the warp has synchronised)
-            auto fetch = [&](int m, LongWord& it) {
+            auto fetch = [&](int m, LongWord<TPL>& it) {
                 const uint32_t slot = ring + (uint32_t)(m & (kRing - 1)) * slot_bytes;
                 it.count = (double)__shfl_sync(FULL, ((m >> 5) == blk) ? c0 : c1, m & 31);
                 it.lbmax = lds64(slot + 2u * KS * 8u);
                 // lanes beyond K read the slot's zero word: beta' = 0 keeps them inert
-                it.beta = lds64(valid ? slot + 8u * (uint32_t)lane : zero_word);
-                it.old_phi = lds64((valid && !first) ? slot + KS * 8u + 8u * (uint32_t)lane : start_word);
+#pragma unroll
+                for (int t = 0; t < TPL; t++) {
+                    const uint32_t k8 = 8u * (uint32_t)(t * 32 + lane);
+                    it.beta[t] = lds64(valid[t] ? slot + k8 : zero_word);
+                    it.old_phi[t] = lds64((valid[t] && !first) ? slot + KS * 8u + k8 : start_word[t]);
+                }
             };
 
             // s = sum over the lanes of x by five butterfly rounds: the same bits in every lane.  (An all-gather through
@@ -218,11 +236,19 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
                 c_keep = 0.0;
                 s_keep = 1.0;
             };
-            auto step = [&](const LongWord& it, int n) {
-                const double gam_in = gam, psi_in = psi, acc_psi_in = acc_psi;
-                const double x = E * it.beta;
-                const double s = sum_over_topics(x);
-                const double gpre = fma(-it.count, it.old_phi, gam);      // beside the chain
+            auto step = [&](const LongWord<TPL>& it, int n) {
+                double gam_in[TPL], psi_in[TPL], x[TPL], gpre[TPL], part = 0.0;
+                const double acc_psi_in = acc_psi;
+#pragma unroll
+                for (int t = 0; t < TPL; t++) {
+                    gam_in[t] = gam[t];
+                    psi_in[t] = psi[t];
+                    x[t] = E[t] * it.beta[t];
+                    part += x[t];
+                }
+                const double s = sum_over_topics(part);
+#pragma unroll
+                for (int t = 0; t < TPL; t++) gpre[t] = fma(-it.count, it.old_phi[t], gam[t]);      // beside the chain
                 const double r0 = rcp_seed(s);
                 double e = fma(-s, r0, 1.0);
                 e = fma(e, e, e);
@@ -230,46 +256,52 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
                 s_keep = keeper ? s : s_keep;
                 c_keep = keeper ? it.count : c_keep;
                 lb_keep = keeper ? it.lbmax : lb_keep;
-                const double xr = x * r0;
-                const double p = fma(xr, e, xr);
-                gam = fma(it.count, p, gpre);
-                const bool keep = valid && n < len;
                 double* const prow = doc_phi + (uint64_t)(uint32_t)n * KS + lane;
-                if (keep) *prow = p;
-                acc_psi = fma(it.count * p, psi, acc_psi);
-                const PsiExp pe = psi_exp_tab<true>(gam, tb);
-                psi = pe.psi;
-                E = pe.e;
+                const bool in_doc = n < len;
+#pragma unroll
+                for (int t = 0; t < TPL; t++) {
+                    const double xr = x[t] * r0;
+                    const double p = fma(xr, e, xr);
+                    gam[t] = fma(it.count, p, gpre[t]);
+                    if (valid[t] && in_doc) prow[t * 32] = p;
+                    acc_psi = fma(it.count * p, psi[t], acc_psi);
+                }
+                psi_exp(gam, psi, E);
                 // s outside [2^-963, 2^963), zero, negative or NaN (an integer test on the exponent field; s is the
                 // same in every lane): the word is done again in log space, as the reference does
                 // (lda-inference.c:52-68), from the state saved above.  Rare; kept out of line.
                 if (__builtin_expect((uint32_t)(double_hi(s) - 0x03C00000) >= (uint32_t)(0x7C200000 - 0x03C00000), 0)) {
                     if (lane == 0) atomicAdd(a.error_flag + 1, 1);
-                    LogSpaceWord<1> ls;
-                    ls.psi[0] = psi_in;
-                    ls.beta[0] = it.beta;
-                    redo_word_in_log_space<32, 1>(&ls);
-                    const double p2 = ls.y[0] * ls.inv_sum;
-                    gam = fma(it.count, p2, fma(-it.count, it.old_phi, gam_in));
-                    if (keep) *prow = p2;
-                    acc_psi = fma(it.count * p2, psi_in, acc_psi_in);
+                    LogSpaceWord<TPL> ls;
+#pragma unroll
+                    for (int t = 0; t < TPL; t++) {
+                        ls.psi[t] = psi_in[t];
+                        ls.beta[t] = it.beta[t];
+                    }
+                    redo_word_in_log_space<32, TPL>(&ls);
+                    acc_psi = acc_psi_in;
+#pragma unroll
+                    for (int t = 0; t < TPL; t++) {
+                        const double p2 = ls.y[t] * ls.inv_sum;
+                        gam[t] = fma(it.count, p2, fma(-it.count, it.old_phi[t], gam_in[t]));
+                        if (valid[t] && in_doc) prow[t * 32] = p2;
+                        acc_psi = fma(it.count * p2, psi_in[t], acc_psi);
+                    }
                     if (keeper) {      // this word's log-sum goes in directly
                         acc_lse = fma(it.count, it.lbmax + ls.lse, acc_lse);
                         c_keep = 0.0;
                         s_keep = 1.0;
                     }
-                    const PsiExp pe2 = psi_exp_tab<true>(gam, tb);
-                    psi = pe2.psi;
-                    E = pe2.e;
+                    psi_exp(gam, psi, E);
                 }
             };
 
             for (int m = 0; m < kDepth; m++) stage(m);
             cp_async_wait<kDepth - 1>();
             __syncwarp();
-            LongWord A, B;
+            LongWord<TPL> A, B;
             fetch(0, A);
-            auto advance = [&](int n, LongWord& now, LongWord& next) {
+            auto advance = [&](int n, LongWord<TPL>& now, LongWord<TPL>& next) {
                 stage(n + kDepth);
                 cp_async_wait<kDepth - 1>();      // word n + 1 has landed
                 __syncwarp();
@@ -299,7 +331,14 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
             __syncwarp();
 
             // likelihood bound of this sweep (lda-inference.c:93-127; estep.cu header)
-            double gs = valid ? gam : 0.0, lg = valid ? lgamma(gam) : 0.0, ap = acc_psi, ls_all = acc_lse;
+            double gs = 0.0, lg = 0.0, ap = acc_psi, ls_all = acc_lse;
+#pragma unroll
+            for (int t = 0; t < TPL; t++) {
+                if (valid[t]) {
+                    gs += gam[t];
+                    lg += lgamma(gam[t]);
+                }
+            }
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
                 gs += __shfl_xor_sync(FULL, gs, o);
@@ -315,13 +354,20 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
         }
 
         // doc_e_step (lda-estimate.c:40-46)
-        double gs = valid ? gam : 0.0, ps = valid ? psi : 0.0;
+        double gs = 0.0, ps = 0.0;
+#pragma unroll
+        for (int t = 0; t < TPL; t++) {
+            if (valid[t]) {
+                gs += gam[t];
+                ps += psi[t];
+                a.gamma[d * K + t * 32 + lane] = gam[t];
+            }
+        }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             gs += __shfl_xor_sync(FULL, gs, o);
             ps += __shfl_xor_sync(FULL, ps, o);
         }
-        if (valid) a.gamma[d * K + lane] = gam;
         if (lane == 0) {
             a.doc_lik[d] = lik;
             a.doc_alpha_ss[d] = ps - K * digamma(gs);
@@ -329,56 +375,62 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
         }
         // class_word[k][w] += c_n phi_nk (lda-estimate.c:48-55)
         if (a.class_word != nullptr) {
-            constexpr int U = 8;
+            constexpr int U = TPL == 1 ? 8 : 4;
             double* __restrict__ class_word = a.class_word + lane;
             for (int n0 = 0; n0 < len; n0 += U) {
                 int w[U];
-                double c[U], p[U];
+                double c[U], p[U][TPL];
 #pragma unroll
                 for (int u = 0; u < U; u++) {
                     const bool in = n0 + u < len;
                     w[u] = in ? doc_words[n0 + u] : -1;
                     c[u] = in ? (double)doc_counts[n0 + u] : 0.0;
-                    p[u] = (in && valid && sweeps != 0) ? doc_phi[(uint64_t)(uint32_t)(n0 + u) * KS + lane] : inv_K;
+#pragma unroll
+                    for (int t = 0; t < TPL; t++)
+                        p[u][t] = (in && valid[t] && sweeps != 0) ? doc_phi[(uint64_t)(uint32_t)(n0 + u) * KS + t * 32 + lane] : inv_K;
                 }
 #pragma unroll
                 for (int u = 0; u < U; u++)
-                    if (w[u] >= 0 && valid) atomicAdd(class_word + (uint64_t)(uint32_t)w[u] * KS, c[u] * p[u]);
+#pragma unroll
+                    for (int t = 0; t < TPL; t++)
+                        if (w[u] >= 0 && valid[t]) atomicAdd(class_word + (uint64_t)(uint32_t)w[u] * KS + t * 32, c[u] * p[u][t]);
             }
         }
     }
 }
 
-template <int KC>
+template <int KC, int TPL>
 static int launch_long_one(const EStepArgs& args, int sm_count, int block_threads, int max_per_sm, cudaStream_t stream)
 {
     if (block_threads > ONILDA_LONG_MAX_THREADS || block_threads < 32 || (block_threads & 31))
         return onilda_fail(ONILDA_EINVAL, "long-document E-step block of %d threads (32..256, whole warps)", block_threads);
     const size_t slot_bytes = 2 * (size_t)args.kstride * 8 + 16;
     const size_t smem = kEstepTableBytes + 16 + (size_t)(block_threads / 32) * kRing * slot_bytes;
-    ONILDA_CUDA(cudaFuncSetAttribute(estep_long_kernel<KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ONILDA_CUDA(cudaFuncSetAttribute(estep_long_kernel<KC, TPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
-    ONILDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_long_kernel<KC>, block_threads, smem));
+    ONILDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_long_kernel<KC, TPL>, block_threads, smem));
     if (per_sm < 1) per_sm = 1;
     if (max_per_sm > 0 && per_sm > max_per_sm) per_sm = max_per_sm;
     const unsigned long long wpb = (unsigned long long)(block_threads / 32);
     const unsigned long long docs = (unsigned long long)args.order_count;
     unsigned long long grid = (unsigned long long)sm_count * per_sm;
     if (grid > (docs + wpb - 1) / wpb) grid = (docs + wpb - 1) / wpb;
-    estep_long_kernel<KC><<<(unsigned)grid, block_threads, smem, stream>>>(args, docs);
+    estep_long_kernel<KC, TPL><<<(unsigned)grid, block_threads, smem, stream>>>(args, docs);
     ONILDA_CUDA(cudaGetLastError());
     return ONILDA_OK;
 }
 
-// The documents order[order_begin, order_begin + order_count), one per warp.  K <= 32 and an even row stride <= 32.
+// The documents order[order_begin, order_begin + order_count), one per warp.  K <= 64 and an even row stride <= 64.
 int launch_estep_long(const EStepArgs& args, int sm_count, int block_threads, int max_per_sm, cudaStream_t stream, int* launches)
 {
     if (args.order_count <= 0) return ONILDA_OK;
-    if (args.num_topics > 32 || args.kstride > 32 || (args.kstride & 1))
+    if (args.num_topics > 64 || args.kstride > 64 || (args.kstride & 1))
         return onilda_fail(ONILDA_EINVAL, "long-document E-step: %d topics with row stride %d unsupported", args.num_topics, args.kstride);
     int rc;
-    if (args.num_topics == 20 && args.kstride == kpad_for(20)) rc = launch_long_one<20>(args, sm_count, block_threads, max_per_sm, stream);
-    else rc = launch_long_one<0>(args, sm_count, block_threads, max_per_sm, stream);
+    if (args.num_topics == 20 && args.kstride == kpad_for(20)) rc = launch_long_one<20, 1>(args, sm_count, block_threads, max_per_sm, stream);
+    else if (args.num_topics == 50 && args.kstride == kpad_for(50)) rc = launch_long_one<50, 2>(args, sm_count, block_threads, max_per_sm, stream);
+    else if (args.num_topics <= 32) rc = launch_long_one<0, 1>(args, sm_count, block_threads, max_per_sm, stream);
+    else rc = launch_long_one<0, 2>(args, sm_count, block_threads, max_per_sm, stream);
     if (rc == ONILDA_OK && launches) *launches += 1;
     return rc;
 }

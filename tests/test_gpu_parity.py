@@ -84,12 +84,13 @@ def test_sweep_counts_match_oracle(oni, oracle, case):
     em.close()
 
 
-@pytest.mark.parametrize("group", [8, 16, 32])
-def test_long_document_path(oni, oracle, group, monkeypatch):
-    """Every document through the long-document launch (more lanes per document, own stream)."""
+@pytest.mark.parametrize("group,case", [(8, "k20"), (16, "k20"), (32, "k20"), (32, "k50"), (32, "k5")])
+def test_long_document_path(oni, oracle, group, case, monkeypatch):
+    """Every document through the long-document launch: the general kernel with more lanes per document (groups 8, 16),
+    the staged one-document-per-warp kernel (group 32) with one topic per lane (k20, k5) and two (k50)."""
     monkeypatch.setenv("ONILDA_LONG_LEN", "1")
     monkeypatch.setenv("ONILDA_LONG_GROUP", str(group))
-    d, c, m, st = load_case(oni, "k20")
+    d, c, m, st = load_case(oni, case)
     off, w, cn, tot, V = oracle.read_dat(d / "c.dat")
     alpha, lb = oracle.load_model(d / "000")
     ref = oracle.e_step(off, w, cn, V, alpha, lb, st.var_max_iter, st.var_converged)
