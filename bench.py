@@ -910,10 +910,11 @@ def main():
         sampler.start()
     barrier()
     t_begin = time.perf_counter()
-    estep_ms, mstep_ms, launches = [], [], 0
+    estep_ms, mstep_ms, launches, word_steps = [], [], 0, []
     for _ in range(args.steps):
         liks.append(em_step()[0])
         s = em.stats()
+        word_steps.append(em.word_steps())
         estep_ms.append(s["estep_ms"])
         mstep_ms.append(s["mstep_ms"])
         launches += s["launches"]
@@ -1065,8 +1066,10 @@ def main():
             "em": {"estep_ms": [round(x, 3) for x in estep_ms], "mstep_ms_mean": float(np.mean(mstep_ms)),
                    "likelihood_first": liks[0], "likelihood_last": liks[-1], "sweeps_last_iter": int(sweeps),
                    "e2e_likelihood_last": e2e_liks[-1],
-                   "estep_ms_note": "EM iterations warmup+1 .. warmup+steps of one run: later iterations take more variational "
-                                    "sweeps per document as the topics sharpen (sweeps_last_iter), so estep_ms rises within the run"}}
+                   "word_steps_per_iter": [int(x) for x in word_steps],
+                   "estep_ms_note": "EM iterations warmup+1 .. warmup+steps of one run.  word_steps_per_iter = sum over documents of "
+                                    "entries x variational sweeps (all ranks), the E-step's unit of work: it grows as the topics "
+                                    "sharpen and more documents run towards the 20-sweep cap, and estep_ms follows it"}}
     emit(line)
     if dist is not None:
         dist.barrier()

@@ -331,6 +331,9 @@ int onilda_em_get_doc_sweeps(onilda_em* em, int32_t* out);
 /* How many (document, word) steps of the last estep were redone in log space because their sum over topics left
  * the range of the product form (a diagnostic; the reference computes every word that way, lda-inference.c:52-68). */
 int onilda_em_log_space_words(onilda_em* em, int64_t* count);
+/* Work of the last iteration's E-step: sum over all documents (of all shards, after onilda_em_mstep) of
+ * entries x variational sweeps, i.e. how many times lda_inference's word loop body ran (lda-inference.c:50-75). */
+int onilda_em_word_steps(onilda_em* em, double* steps);
 /* Counters of the last estep: kernel time in ms (CUDA events on the handle's
  * stream), number of kernel launches issued by the last estep+mstep pair, and
  * total variational sweeps summed over documents. */

@@ -128,6 +128,7 @@ def lib():
     L.onilda_em_stats.argtypes = [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int64),
                                   C.POINTER(C.c_int64)]
     L.onilda_em_log_space_words.argtypes = [_vp, C.POINTER(C.c_int64)]
+    L.onilda_em_word_steps.argtypes = [_vp, C.POINTER(C.c_double)]
     L.onilda_em_stream.argtypes = [_vp]
     L.onilda_em_stream.restype = _vp
     L.onilda_run_em.argtypes = [C.c_char_p, C.c_char_p, _vp, C.c_int, C.c_double, C.POINTER(Settings), C.c_int,
@@ -473,6 +474,11 @@ class EM:
         out = np.zeros(self.doc_end - self.doc_begin, np.int32)
         _check(lib().onilda_em_get_doc_sweeps(self._h, out))
         return out
+
+    def word_steps(self):
+        v = C.c_double()
+        _check(lib().onilda_em_word_steps(self._h, C.byref(v)))
+        return v.value
 
     def log_space_words(self):
         n = C.c_int64()

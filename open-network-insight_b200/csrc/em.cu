@@ -54,6 +54,7 @@ struct onilda_em {
     double estep_ms, mstep_ms;
     int64_t launches;
     int64_t sweeps;
+    double word_steps;          // entries x sweeps of the last E-step, summed over all shards at the M-step
     int estep_done;
     // sufficient statistics across shards (NCCL); nranks == 1: none
     ncclComm_t comm;
@@ -461,7 +462,8 @@ static int run_estep(onilda_em* em, bool accumulate)
         if (em->timing) ONILDA_CUDA(cudaEventRecord(em->ev_bulk_end, em->stream));
         if (em->num_long > 0) ONILDA_CUDA(cudaStreamWaitEvent(em->stream, em->ev_join, 0));
     }
-    rc = launch_reduce_doc_stats(em->d_doc_lik, em->d_doc_ass, em->num_docs, em->d_partial, em->d_ss + table, em->stream, &l);
+    rc = launch_reduce_doc_stats(em->d_doc_lik, em->d_doc_ass, em->d_offsets, em->d_doc_sweeps, em->num_docs, em->d_partial,
+                                 em->d_ss + table, em->stream, &l);
     if (rc != ONILDA_OK) return rc;
     ONILDA_CUDA(cudaEventRecord(em->ev1, em->stream));
     em->launches = l;
@@ -625,6 +627,7 @@ static int mstep_group(onilda_em** ems, int n, double* likelihood, double* conve
         em->converged = conv;
         if (em->converged < 0) em->var_max_iter = em->var_max_iter * 2;
         em->likelihood_old = lik;
+        em->word_steps = tail[SS_STEPS];
     }
     if (likelihood) *likelihood = lik;
     if (converged) *converged = conv;
@@ -844,6 +847,16 @@ extern "C" int onilda_em_log_space_words(onilda_em* em, int64_t* count)
     ONILDA_CUDA(cudaMemcpyAsync(&v, em->d_error + 1, sizeof v, cudaMemcpyDeviceToHost, em->stream));
     ONILDA_CUDA(cudaStreamSynchronize(em->stream));
     *count = v;
+    return ONILDA_OK;
+}
+
+// (document, word, sweep) steps of the last iteration's E-step - entries x variational sweeps, summed over all
+// documents of all shards: the E-step's unit of work.  It grows as the topics sharpen (more documents run to
+// the sweep cap), which is why an EM iteration late in a run takes longer than an early one on the same corpus.
+extern "C" int onilda_em_word_steps(onilda_em* em, double* steps)
+{
+    if (!em || !steps) return onilda_fail(ONILDA_EINVAL, "em_word_steps: null argument");
+    *steps = em->word_steps;
     return ONILDA_OK;
 }
 

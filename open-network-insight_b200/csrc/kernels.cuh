@@ -41,7 +41,7 @@ inline bool choose_layout(int K, TopicLayout* out)
 }
 
 // Tail of the packed sufficient-statistics buffer, after the V*kpad table.
-enum { SS_LIK = 0, SS_ALPHA = 1, SS_NDOCS = 2, SS_SPARE = 3, SS_TAIL = 4 };
+enum { SS_LIK = 0, SS_ALPHA = 1, SS_NDOCS = 2, SS_STEPS = 3, SS_TAIL = 4 };   // SS_STEPS: sum over documents of entries x sweeps
 // The tables carry kTablePadRows spare rows after row V: with P <= 16 ranks each owning ceil(V/P) rows, the
 // reduce-scatter / all-gather of the distributed M-step covers at most V + 15 rows; the idle row sits behind them.
 enum { kTablePadRows = 16 };
@@ -88,7 +88,8 @@ int launch_estep_long(const EStepArgs& args, int sm_count, int block_threads, in
 // M-step and table kernels (mstep.cu)
 int launch_tables_from_log_beta(const double* log_beta_kv, int K, int V, const TopicLayout& lay, double* log_beta_wk,
                                 double* beta_scaled, double* lbmax, cudaStream_t stream, int* launches);
-int launch_reduce_doc_stats(const double* doc_lik, const double* doc_alpha_ss, int64_t num_docs, double* partial,
+int launch_reduce_doc_stats(const double* doc_lik, const double* doc_alpha_ss, const int64_t* offsets, const int32_t* doc_sweeps,
+                            int64_t num_docs, double* partial,
                             double* ss_tail, cudaStream_t stream, int* launches);
 int launch_column_sums(const double* table, int rows, const TopicLayout& lay, int sm_count, double* partial, double* total,
                        cudaStream_t stream, int* launches);

@@ -108,41 +108,48 @@ static constexpr int kDocBlocks = 296;
 static constexpr int kDocThreads = 256;
 
 __global__ void __launch_bounds__(kDocThreads) doc_partial_kernel(const double* __restrict__ doc_lik,
-                                                                  const double* __restrict__ doc_ass, int64_t D,
+                                                                  const double* __restrict__ doc_ass,
+                                                                  const int64_t* __restrict__ offsets,
+                                                                  const int32_t* __restrict__ doc_sweeps, int64_t D,
                                                                   double* __restrict__ partial)
 {
-    __shared__ double sl[kDocThreads], sa[kDocThreads];
+    __shared__ double sl[kDocThreads], sa[kDocThreads], sw[kDocThreads];
     const int64_t chunk = (D + gridDim.x - 1) / gridDim.x;
     const int64_t lo = chunk * blockIdx.x;
     int64_t hi = lo + chunk;
     if (hi > D) hi = D;
-    double l = 0.0, s = 0.0;
-    for (int64_t d = lo + threadIdx.x; d < hi; d += kDocThreads) { l += doc_lik[d]; s += doc_ass[d]; }
+    double l = 0.0, s = 0.0, w = 0.0;      // w: (document, word, sweep) steps = entries x sweeps, the E-step's unit of work
+    for (int64_t d = lo + threadIdx.x; d < hi; d += kDocThreads) {
+        l += doc_lik[d];
+        s += doc_ass[d];
+        w += (double)(offsets[d + 1] - offsets[d]) * (double)doc_sweeps[d];
+    }
     sl[threadIdx.x] = l;
     sa[threadIdx.x] = s;
+    sw[threadIdx.x] = w;
     __syncthreads();
     for (int o = kDocThreads / 2; o > 0; o >>= 1) {
-        if (threadIdx.x < o) { sl[threadIdx.x] += sl[threadIdx.x + o]; sa[threadIdx.x] += sa[threadIdx.x + o]; }
+        if (threadIdx.x < o) { sl[threadIdx.x] += sl[threadIdx.x + o]; sa[threadIdx.x] += sa[threadIdx.x + o]; sw[threadIdx.x] += sw[threadIdx.x + o]; }
         __syncthreads();
     }
-    if (threadIdx.x == 0) { partial[2 * blockIdx.x] = sl[0]; partial[2 * blockIdx.x + 1] = sa[0]; }
+    if (threadIdx.x == 0) { partial[3 * blockIdx.x] = sl[0]; partial[3 * blockIdx.x + 1] = sa[0]; partial[3 * blockIdx.x + 2] = sw[0]; }
 }
 
 __global__ void doc_final_kernel(const double* __restrict__ partial, int nblocks, int64_t D, double* __restrict__ tail)
 {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    double l = 0.0, s = 0.0;
-    for (int b = 0; b < nblocks; b++) { l += partial[2 * b]; s += partial[2 * b + 1]; }
+    double l = 0.0, s = 0.0, w = 0.0;
+    for (int b = 0; b < nblocks; b++) { l += partial[3 * b]; s += partial[3 * b + 1]; w += partial[3 * b + 2]; }
     tail[SS_LIK] = l;
     tail[SS_ALPHA] = s;
     tail[SS_NDOCS] = (double)D;
-    tail[SS_SPARE] = 0.0;
+    tail[SS_STEPS] = w;
 }
 
 int mstep_partial_doubles(int V, const TopicLayout& lay, int64_t num_docs)
 {
     (void)V; (void)num_docs;
-    int a = kMaxColBlocks * lay.kpad, b = 2 * kDocBlocks;
+    int a = kMaxColBlocks * lay.kpad, b = 3 * kDocBlocks;
     return a > b ? a : b;
 }
 
@@ -168,10 +175,11 @@ int launch_export_log_beta(const double* log_beta_wk, int K, int V, const TopicL
     return ONILDA_OK;
 }
 
-int launch_reduce_doc_stats(const double* doc_lik, const double* doc_alpha_ss, int64_t num_docs, double* partial,
+int launch_reduce_doc_stats(const double* doc_lik, const double* doc_alpha_ss, const int64_t* offsets, const int32_t* doc_sweeps,
+                            int64_t num_docs, double* partial,
                             double* ss_tail, cudaStream_t stream, int* launches)
 {
-    doc_partial_kernel<<<kDocBlocks, kDocThreads, 0, stream>>>(doc_lik, doc_alpha_ss, num_docs, partial);
+    doc_partial_kernel<<<kDocBlocks, kDocThreads, 0, stream>>>(doc_lik, doc_alpha_ss, offsets, doc_sweeps, num_docs, partial);
     ONILDA_CUDA(cudaGetLastError());
     doc_final_kernel<<<1, 32, 0, stream>>>(partial, kDocBlocks, num_docs, ss_tail);
     ONILDA_CUDA(cudaGetLastError());

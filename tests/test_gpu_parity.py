@@ -256,8 +256,10 @@ def test_invariants_at_scale(oni, corpusgen):
     totals = np.add.reduceat(g.counts.astype(np.float64), g.offsets[:-1])
     assert np.max(np.abs(gam.sum(axis=1) - (20 * 0.7 + totals)) / (20 * 0.7 + totals)) < 1e-12
     assert np.all(gam > 0)
+    sweeps = em.doc_sweeps()
     lik, conv, keep = em.mstep()
     assert np.isfinite(lik) and lik < 0 and keep
+    assert em.word_steps() == float(np.sum(np.diff(g.offsets) * sweeps.astype(np.int64)))      # entries x sweeps, summed on the device
     beta = np.exp(em.model().log_beta)
     assert np.max(np.abs(beta.sum(axis=1) - 1.0)) < 1e-9          # rows of exp(log_beta) are distributions
     lik2, conv2, _ = em.iterate()
