@@ -230,7 +230,7 @@ __global__ void __launch_bounds__(ONILDA_ESTEP_MAX_THREADS) estep_kernel(EStepAr
                 double gpre[TPL];
 #pragma unroll
                 for (int t = 0; t < TPL; t++) gpre[t] = fma(-it.count, it.old_phi[t], gam[t]);
-                const double s = group_sum<G>(part);
+                const double s = chain_sum<G>(part);
                 acc_lse = fma(c_prev, lb_prev + fast_log_tab(s_prev, tb), acc_lse);
                 // s outside [2^-963, 2^963) (about 1e-290 .. 1e290), zero, negative or NaN: an integer test
                 // on the exponent field, off the FP64 pipe

@@ -18,6 +18,47 @@ __device__ __forceinline__ double group_sum(double v)
     return v;
 }
 
+// The same sums through the FP64 tensor-core instruction, used for its LATENCY (measured on B200,
+// tools/warp_sum_latency.cu: a warp-wide sum costs 60 cycles this way against 168 for five butterfly rounds, and the
+// word-by-word chain of a document waits for exactly this sum).  mma.m8n8k4.f64 computes D[m][n] = sum_k A[m][k] B[k][n];
+// lane l holds A[l/4][l%4], B[l%4][l/4] and D[l/4][2(l%4)], D[l/4][2(l%4)+1].  The products are by 1.0, the additions
+// run in the fixed order k = 0..3 in fp64: a deterministic sum like the butterfly's, in another order.
+#ifndef ONILDA_MMA_SUM
+#define ONILDA_MMA_SUM 3      // bit 0: one document per warp, bit 1: groups of four lanes
+#endif
+__device__ __forceinline__ void dmma884(double a, double b, double& d0, double& d1)
+{
+    const double z = 0.0;
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%4,%5};"
+                 : "=d"(d0), "=d"(d1) : "d"(a), "d"(b), "d"(z), "d"(z));
+}
+
+// every lane receives the sum of v over the warp
+__device__ __forceinline__ double warp_sum_mma(double v)
+{
+    double c0, c1, t0, t1;
+    dmma884(1.0, v, c0, c1);          // with A = 1: the sums of lanes 8q..8q+3 and 8q+4..8q+7, q = lane % 4
+    dmma884(1.0, c0 + c1, t0, t1);    // the four partials p[q] sit in B[q][*]: their sum, in every lane
+    return t0;
+}
+
+// every lane receives the sum of v over its aligned group of four lanes
+__device__ __forceinline__ double quad_sum_mma(double v)
+{
+    double d0, d1;
+    dmma884(v, 1.0, d0, d1);          // with B = 1: row m = lane / 4 of D is the sum of A's row m, the lane's own four
+    return d0;
+}
+
+// the per-word sum on the serial chain
+template <int G>
+__device__ __forceinline__ double chain_sum(double v)
+{
+    if constexpr (G == 32 && (ONILDA_MMA_SUM & 1)) return warp_sum_mma(v);
+    if constexpr (G == 4 && (ONILDA_MMA_SUM & 2)) return quad_sum_mma(v);
+    return group_sum<G>(v);
+}
+
 template <int G>
 __device__ __forceinline__ double group_max(double v)
 {

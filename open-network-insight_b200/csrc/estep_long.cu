@@ -216,15 +216,11 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
                 }
             };
 
-            // s = sum over the lanes of x by five butterfly rounds: the same bits in every lane.  (An all-gather through
-            // shared memory - every lane stores x, reads all K back with broadcast 16-byte loads and adds them in one
-            // fixed tree - was measured: 85.0 ms against 81.3 ms for 592 hub documents alone.)
-            auto sum_over_topics = [&](double x) -> double {
-                double s = x;
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(FULL, s, o);
-                return s;
-            };
+            // s = sum over the lanes of x, the same bits in every lane: two FP64 tensor-core instructions and one add
+            // (estep_common.cuh), 108 cycles shorter than five butterfly rounds.  (An all-gather through shared
+            // memory - every lane stores x, reads all K back with broadcast 16-byte loads and adds them in one fixed
+            // tree - was measured slower than the butterfly: 85.0 ms against 81.3 ms for 592 hub documents alone.)
+            auto sum_over_topics = [&](double x) -> double { return chain_sum<32>(x); };
 
             // The likelihood needs sum_n c_n (lbmax_n + log s_n).  s_n is the same in every lane, so lane n mod 32 keeps word
             // n's (s, c, lbmax) and every 32 words all lanes take ONE logarithm each: 1/32 of the logarithms per lane,
@@ -236,19 +232,30 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
                 c_keep = 0.0;
                 s_keep = 1.0;
             };
-            auto step = [&](const LongWord<TPL>& it, int n) {
-                double gam_in[TPL], psi_in[TPL], x[TPL], gpre[TPL], part = 0.0;
-                const double acc_psi_in = acc_psi;
+            // One word of the chain E -> s -> phi -> gamma -> psi -> E, in two parts so that the staging work of a later word
+            // (advance, below) runs while the sum is in the tensor pipe.  head: x = E beta', s = sum over the lanes.
+            auto head = [&](const LongWord<TPL>& it, double (&x)[TPL]) -> double {
+#pragma unroll
+                for (int t = 0; t < TPL; t++) x[t] = E[t] * it.beta[t];
+                double part = x[0];
+#pragma unroll
+                for (int t = 1; t < TPL; t++) part += x[t];
+                return sum_over_topics(part);
+            };
+            // the state before the word, for the log-space redo
+            double gam_in[TPL], psi_in[TPL], acc_psi_in = 0.0;
+            // tail: phi = x / s, gamma, psi, E.  True when s is outside [2^-963, 2^963), zero, negative or NaN (an integer
+            // test on the exponent field; s is the same in every lane, the vote only tells the compiler so): the word
+            // must then be done again in log space (redo, below) before the next one.
+            auto tail = [&](const LongWord<TPL>& it, int n, const double (&x)[TPL], double s) -> bool {
+                double gpre[TPL];
+                acc_psi_in = acc_psi;
 #pragma unroll
                 for (int t = 0; t < TPL; t++) {
                     gam_in[t] = gam[t];
                     psi_in[t] = psi[t];
-                    x[t] = E[t] * it.beta[t];
-                    part += x[t];
+                    gpre[t] = fma(-it.count, it.old_phi[t], gam[t]);      // beside the chain
                 }
-                const double s = sum_over_topics(part);
-#pragma unroll
-                for (int t = 0; t < TPL; t++) gpre[t] = fma(-it.count, it.old_phi[t], gam[t]);      // beside the chain
                 const double r0 = rcp_seed(s);
                 double e = fma(-s, r0, 1.0);
                 e = fma(e, e, e);
@@ -267,33 +274,34 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
                     acc_psi = fma(it.count * p, psi[t], acc_psi);
                 }
                 psi_exp(gam, psi, E);
-                // s outside [2^-963, 2^963), zero, negative or NaN (an integer test on the exponent field; s is the
-                // same in every lane): the word is done again in log space, as the reference does
-                // (lda-inference.c:52-68), from the state saved above.  Rare; kept out of line.
-                if (__builtin_expect((uint32_t)(double_hi(s) - 0x03C00000) >= (uint32_t)(0x7C200000 - 0x03C00000), 0)) {
-                    if (lane == 0) atomicAdd(a.error_flag + 1, 1);
-                    LogSpaceWord<TPL> ls;
+                return __any_sync(FULL, (uint32_t)(double_hi(s) - 0x03C00000) >= (uint32_t)(0x7C200000 - 0x03C00000));
+            };
+            // the word again in log space, as the reference does it (lda-inference.c:52-68), from the saved state.  Rare;
+            // reached only from behind the word loop, so that the loop itself has no taken branch.
+            auto redo = [&](const LongWord<TPL>& it, int n) {
+                if (lane == 0) atomicAdd(a.error_flag + 1, 1);
+                LogSpaceWord<TPL> ls;
 #pragma unroll
-                    for (int t = 0; t < TPL; t++) {
-                        ls.psi[t] = psi_in[t];
-                        ls.beta[t] = it.beta[t];
-                    }
-                    redo_word_in_log_space<32, TPL>(&ls);
-                    acc_psi = acc_psi_in;
-#pragma unroll
-                    for (int t = 0; t < TPL; t++) {
-                        const double p2 = ls.y[t] * ls.inv_sum;
-                        gam[t] = fma(it.count, p2, fma(-it.count, it.old_phi[t], gam_in[t]));
-                        if (valid[t] && in_doc) prow[t * 32] = p2;
-                        acc_psi = fma(it.count * p2, psi_in[t], acc_psi);
-                    }
-                    if (keeper) {      // this word's log-sum goes in directly
-                        acc_lse = fma(it.count, it.lbmax + ls.lse, acc_lse);
-                        c_keep = 0.0;
-                        s_keep = 1.0;
-                    }
-                    psi_exp(gam, psi, E);
+                for (int t = 0; t < TPL; t++) {
+                    ls.psi[t] = psi_in[t];
+                    ls.beta[t] = it.beta[t];
                 }
+                redo_word_in_log_space<32, TPL>(&ls);
+                acc_psi = acc_psi_in;
+                double* const prow = doc_phi + (uint64_t)(uint32_t)n * KS + lane;
+#pragma unroll
+                for (int t = 0; t < TPL; t++) {
+                    const double p2 = ls.y[t] * ls.inv_sum;
+                    gam[t] = fma(it.count, p2, fma(-it.count, it.old_phi[t], gam_in[t]));
+                    if (valid[t] && n < len) prow[t * 32] = p2;
+                    acc_psi = fma(it.count * p2, psi_in[t], acc_psi);
+                }
+                if (lane == (n & 31)) {      // this word's log-sum goes in directly
+                    acc_lse = fma(it.count, it.lbmax + ls.lse, acc_lse);
+                    c_keep = 0.0;
+                    s_keep = 1.0;
+                }
+                psi_exp(gam, psi, E);
             };
 
             for (int m = 0; m < kDepth; m++) stage(m);
@@ -301,31 +309,52 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
             __syncwarp();
             LongWord<TPL> A, B;
             fetch(0, A);
-            auto advance = [&](int n, LongWord<TPL>& now, LongWord<TPL>& next) {
+            // word n: its sum first, then - while the sum is on its way - the copies for word n + kDepth are issued and the
+            // rows of word n + 1 (landed by now) are read, then the rest of word n
+            auto advance = [&](int n, const LongWord<TPL>& now, LongWord<TPL>& next) -> bool {
+                double x[TPL];
+                const double s = head(now, x);
                 stage(n + kDepth);
-                cp_async_wait<kDepth - 1>();      // word n + 1 has landed
+                cp_async_wait<kDepth - 1>();
                 __syncwarp();
                 fetch(n + 1, next);
-                step(now, n);
+                return tail(now, n, x, s);
             };
-            // words in pairs (an odd document ends on a phantom word: count 0, nothing stored), 32 to a block of ids
-            // words four at a time (a document may end on up to three phantom words: the idle row, count 0, nothing
-            // stored), 32 to a block of ids.  The block loaded at a rotation is first copied a whole block later:
-            // a register move of a value still in flight would wait for its load.
-            for (int n0 = 0; n0 < len; n0 += 32) {
-                const int n1 = (n0 + 32 < len) ? n0 + 32 : len;
-                for (int n = n0; n < n1; n += 4) {
-                    advance(n, A, B);
-                    advance(n + 1, B, A);
-                    advance(n + 2, A, B);
-                    advance(n + 3, B, A);
-                }
+            // Words four at a time (a document may end on up to three phantom words: the idle row, count 0, nothing
+            // stored), 32 to a block of ids.  The block loaded at a rotation is first copied a whole block later: a
+            // register move of a value still in flight would wait for its load.  The loop is left at a word that needs
+            // the redo and entered again behind it.
+            auto next_block = [&]() {
                 flush_logs();
                 blk++;
                 w0 = w1; c0 = c1;
                 w1 = w2; c1 = c2;
                 w2 = w3; c2 = c3;
                 load_block(blk + 3, w3, c3);
+            };
+            int n = 0;
+            for (;;) {
+                int sub = -1;
+                while (n < len) {
+                    const int n1 = ((n | 31) + 1 < len) ? (n | 31) + 1 : len;
+                    do {
+                        if (__builtin_expect(advance(n, A, B), 0)) { sub = 0; break; }
+                        if (__builtin_expect(advance(n + 1, B, A), 0)) { sub = 1; break; }
+                        if (__builtin_expect(advance(n + 2, A, B), 0)) { sub = 2; break; }
+                        if (__builtin_expect(advance(n + 3, B, A), 0)) { sub = 3; break; }
+                        n += 4;
+                    } while (n < n1);
+                    if (sub >= 0) break;
+                    next_block();
+                }
+                if (sub < 0) break;
+                redo((sub & 1) ? B : A, n + sub);
+                for (int j = sub + 1; j < 4; j++) {
+                    const bool again = (j & 1) ? advance(n + j, B, A) : advance(n + j, A, B);
+                    if (again) redo((j & 1) ? B : A, n + j);
+                }
+                n += 4;
+                if ((n & 31) == 0 || n >= len) next_block();
             }
             cp_async_wait<0>();
             __syncwarp();
