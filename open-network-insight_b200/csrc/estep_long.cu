@@ -24,6 +24,9 @@
 #ifndef ONILDA_LONG_RING
 #define ONILDA_LONG_RING 8
 #endif
+#ifndef ONILDA_LONG_KEEP_ROWS
+#define ONILDA_LONG_KEEP_ROWS 1
+#endif
 #ifndef ONILDA_LONG_MIN_BLOCKS
 #define ONILDA_LONG_MIN_BLOCKS 2
 #endif
@@ -66,6 +69,7 @@ template <int KC, int TPL>
 __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCKS) estep_long_kernel(EStepArgs a, unsigned long long num_docs)
 {
     constexpr unsigned FULL = 0xffffffffu;
+    constexpr bool kKeepRows = ONILDA_LONG_KEEP_ROWS && TPL == 1;      // two rows per lane do not fit the registers
     const int lane = threadIdx.x & 31;
     const int K = KC ? KC : a.num_topics;
     const uint32_t KS = KC ? (uint32_t)kpad_for(KC) : (uint32_t)a.kstride;
@@ -154,11 +158,41 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
             }
         };
 
+        // The same with the lane's table row kept in registers.  A long document's gamma_k seldom leaves its cell of the
+        // table (1/64 octave of gamma + 1) from one word to the next, and the row's three 16-byte loads - 20 lanes, 20
+        // different rows, bank conflicts - are 70 cycles of the chain.  psi_exp_kept evaluates with the row it holds and
+        // reports a lane whose cell has changed; the caller then leaves the word loop, reloads (psi_exp_reload) and
+        // comes back.
+        double row[TPL][6], row_at[TPL];      // the row and (its cell's centre) - 1: u = t - centre = gamma - row_at, one operation from gamma
+        int row_key[TPL];
+        auto psi_exp_reload = [&](const double (&g)[TPL], double (&psi)[TPL], double (&E)[TPL]) {
+#pragma unroll
+            for (int t = 0; t < TPL; t++) {
+                const double tt = g[t] + 1.0;
+                row_key[t] = psi_row_of(tt);
+                tb.psi_row(row_key[t], row[t]);
+                row_at[t] = (tt - psi_cell_offset(tt)) - 1.0;      // exact: the centre has seven significant bits
+                psi[t] = psi_poly<true>(row[t], g[t] - row_at[t]) - fast_rcp(g[t]);
+                E[t] = fast_exp_tab<true>(psi[t], tb);
+            }
+        };
+        auto psi_exp_kept = [&](const double (&g)[TPL], double (&psi)[TPL], double (&E)[TPL]) -> bool {
+            bool moved = false;
+#pragma unroll
+            for (int t = 0; t < TPL; t++) {
+                moved |= psi_row_of(g[t] + 1.0) != row_key[t];      // beside the chain
+                psi[t] = psi_poly<true>(row[t], g[t] - row_at[t]) - fast_rcp(g[t]);
+                E[t] = fast_exp_tab<true>(psi[t], tb);
+            }
+            return moved;
+        };
+
         const double gamma0 = a.alpha + (total / ((double)K));
         double gam[TPL], psi[TPL], E[TPL];
 #pragma unroll
         for (int t = 0; t < TPL; t++) gam[t] = valid[t] ? gamma0 : 1.0;
-        psi_exp(gam, psi, E);
+        if (kKeepRows) psi_exp_reload(gam, psi, E);
+        else psi_exp(gam, psi, E);
 
         double lik = 0.0, lik_old = 0.0, converged = 1.0;
         int sweeps = 0;
@@ -243,7 +277,7 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
                 return sum_over_topics(part);
             };
             // the state before the word, for the log-space redo
-            double gam_in[TPL], psi_in[TPL], acc_psi_in = 0.0;
+            double gam_in[TPL], psi_in[TPL], acc_psi_in = 0.0, s_in = 1.0;
             // tail: phi = x / s, gamma, psi, E.  True when s is outside [2^-963, 2^963), zero, negative or NaN (an integer
             // test on the exponent field; s is the same in every lane, the vote only tells the compiler so): the word
             // must then be done again in log space (redo, below) before the next one.
@@ -269,16 +303,25 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
                 for (int t = 0; t < TPL; t++) {
                     const double xr = x[t] * r0;
                     const double p = fma(xr, e, xr);
-                    gam[t] = fma(it.count, p, gpre[t]);
+                    // gamma - c phi_old + c phi with phi = xr + xr e: the part without e is formed while e is computed
+                    const double cx = it.count * xr;
+                    gam[t] = fma(cx, e, cx + gpre[t]);
                     if (valid[t] && in_doc) prow[t * 32] = p;
                     acc_psi = fma(it.count * p, psi[t], acc_psi);
                 }
-                psi_exp(gam, psi, E);
-                return __any_sync(FULL, (uint32_t)(double_hi(s) - 0x03C00000) >= (uint32_t)(0x7C200000 - 0x03C00000));
+                s_in = s;
+                bool leave = (uint32_t)(double_hi(s) - 0x03C00000) >= (uint32_t)(0x7C200000 - 0x03C00000);
+                if (kKeepRows) leave |= psi_exp_kept(gam, psi, E);
+                else psi_exp(gam, psi, E);
+                return __any_sync(FULL, leave);
             };
             // the word again in log space, as the reference does it (lda-inference.c:52-68), from the saved state.  Rare;
             // reached only from behind the word loop, so that the loop itself has no taken branch.
             auto redo = [&](const LongWord<TPL>& it, int n) {
+                if ((uint32_t)(double_hi(s_in) - 0x03C00000) < (uint32_t)(0x7C200000 - 0x03C00000)) {
+                    psi_exp_reload(gam, psi, E);      // the sum was fine: a lane's gamma has moved to another cell of the table
+                    return;
+                }
                 if (lane == 0) atomicAdd(a.error_flag + 1, 1);
                 LogSpaceWord<TPL> ls;
 #pragma unroll
@@ -301,7 +344,8 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
                     c_keep = 0.0;
                     s_keep = 1.0;
                 }
-                psi_exp(gam, psi, E);
+                if (kKeepRows) psi_exp_reload(gam, psi, E);
+                else psi_exp(gam, psi, E);
             };
 
             for (int m = 0; m < kDepth; m++) stage(m);

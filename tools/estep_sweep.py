@@ -62,9 +62,13 @@ def main():
                 lik = em.mstep()[0]
                 ms.append(em.stats()["estep_ms"])
                 liks.append(lik)
+            rare = steps = None
+            if os.environ.get("ONILDA_SWEEP_COUNTS"):
+                rare, steps = em.log_space_words(), em.word_steps()
             em.close()
             print(f"[{conf or 'default'}] estep_ms " + " ".join(f"{x:.1f}" for x in ms) +
-                  f" | mean(4..) {np.mean(ms[3:]):.2f} | lik_last {liks[-1]:.10e}", flush=True)
+                  f" | mean(4..) {np.mean(ms[3:]):.2f} | lik_last {liks[-1]:.10e}" +
+                  (f" | word steps {steps:.4g}, out-of-loop words {rare}" if rare is not None else ""), flush=True)
         except Exception as e:          # keep sweeping
             print(f"[{conf}] FAILED: {e}", flush=True)
         torch.cuda.empty_cache()
