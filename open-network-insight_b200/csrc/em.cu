@@ -25,7 +25,7 @@ struct onilda_em {
     int timing;
     int64_t num_long;           // documents of at least long_len entries: prefix of d_order
     int64_t long_max_total;     // most tokens in one of them (decides whether the table-only long kernel may run)
-    int long_len, long_group, long_smem, long_threads, long_per_sm, bulk_group, bulk_per_sm, bulk_threads, pdl;
+    int long_len, long_group, long_smem, long_threads, long_per_sm, bulk_group, bulk_per_sm, bulk_threads, pdl, carveout_pct;
     // shard
     int64_t doc_begin, doc_end, num_docs, nnz;
     int K, V;
@@ -329,7 +329,14 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
         em->long_smem = env_smem ? atoi(env_smem) : 0;
         em->long_threads = env_lt ? atoi(env_lt) : 256;
         em->long_per_sm = env_lps ? atoi(env_lps) : 1;
-        em->bulk_threads = env_bt ? atoi(env_bt) : 128;
+        em->bulk_threads = env_bt ? atoi(env_bt) : 256;    // eight warps share one copy of the tables
+        const char* env_co = getenv("ONILDA_CARVEOUT_PCT");
+        // Both launches ask for the SAME shared-memory carve-out, large enough for what is to be resident together (one
+        // long-document block, 25 KB, and two bulk blocks, 62 KB each: the 132 KB setting).  Left to the driver, each
+        // kernel gets the carve-out that suits it alone; an SM set up for the first one then cannot take blocks of the
+        // other (the split is only changed on an idle SM) and the E-step was 110 ms instead of 90.  More than needed
+        // costs L1: 106 ms at the 196 / 228 KB settings.
+        em->carveout_pct = env_co ? atoi(env_co) : 58;
         const char* env_pdl = getenv("ONILDA_PDL");
         em->pdl = env_pdl ? atoi(env_pdl) : 1;
         em->num_long = 0;
@@ -399,6 +406,7 @@ static int run_estep(onilda_em* em, bool accumulate)
     EStepArgs a;
     a.offsets = em->d_offsets; a.words = em->d_words; a.counts = em->d_counts; a.totals = em->d_totals;
     a.order = em->d_order;
+    a.carveout_pct = em->num_long > 0 ? em->carveout_pct : 0;
     a.psi_tab = em->d_math_tab; a.exp_tab = em->d_math_tab + (size_t)6 * kPsiRows;
     a.beta_scaled = em->d_beta_scaled; a.lbmax = em->d_lbmax; a.num_topics = em->K; a.num_terms = em->V; a.idle_row = em->V + kTablePadRows; a.kstride = em->lay.kpad;
     a.alpha = em->alpha;

@@ -390,6 +390,8 @@ static int launch_one(const EStepArgs& args, int sm_count, int block_threads, in
         return onilda_fail(ONILDA_EINVAL, "E-step block of %d threads (32..%d, whole warps)", block_threads, ONILDA_ESTEP_MAX_THREADS);
     const size_t smem = kEstepTableBytes + (size_t)extra_smem;
     ONILDA_CUDA(cudaFuncSetAttribute(estep_kernel<G, TPL, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (args.carveout_pct > 0)
+        ONILDA_CUDA(cudaFuncSetAttribute(estep_kernel<G, TPL, KC>, cudaFuncAttributePreferredSharedMemoryCarveout, args.carveout_pct));
     int per_sm = 0;
     ONILDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_kernel<G, TPL, KC>, block_threads, smem));
     if (per_sm < 1) per_sm = 1;

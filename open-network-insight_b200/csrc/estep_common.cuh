@@ -24,7 +24,7 @@ __device__ __forceinline__ double group_sum(double v)
 // lane l holds A[l/4][l%4], B[l%4][l/4] and D[l/4][2(l%4)], D[l/4][2(l%4)+1].  The products are by 1.0, the additions
 // run in the fixed order k = 0..3 in fp64: a deterministic sum like the butterfly's, in another order.
 #ifndef ONILDA_MMA_SUM
-#define ONILDA_MMA_SUM 3      // bit 0: one document per warp, bit 1: groups of four lanes
+#define ONILDA_MMA_SUM 1      // bit 0: one document per warp; bit 1: groups of four lanes (measured: no gain where several documents share a warp, 153 against 150 ms)
 #endif
 __device__ __forceinline__ void dmma884(double a, double b, double& d0, double& d1)
 {

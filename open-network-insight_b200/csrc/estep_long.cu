@@ -57,6 +57,12 @@ __device__ __forceinline__ double lds64(uint32_t addr)
     return v;
 }
 
+// bytes of math tables a block keeps in shared memory (see the kernel)
+template <int TPL>
+struct LongTables {
+    static constexpr uint32_t bytes = (ONILDA_LONG_KEEP_ROWS && TPL == 1) ? (uint32_t)(8u * kExpTabSize) : (uint32_t)kEstepTableBytes;
+};
+
 template <int TPL>
 struct LongWord {
     double count, lbmax, beta[TPL], old_phi[TPL];
@@ -83,16 +89,21 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
     const double* __restrict__ lbmax = a.lbmax;
     asm volatile("" : "+l"(beta_scaled), "+l"(lbmax));
 
+    // Shared memory: [psi rows, only where the lanes do not keep their row in registers] [2^(i/64)] [constants, rings].
+    // With kept rows the psi table is read from global memory on the rare reload (it stays in L1: 61 KB, and the
+    // 61 KB of shared memory not taken here are L1 for this block and the bulk blocks beside it).
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ LogTabEntry logtab[128];
+    constexpr uint32_t kPsiBytes = (uint32_t)(sizeof(PsiRow) * kPsiRows);
+    constexpr uint32_t kTabBytes = LongTables<TPL>::bytes;
     {
-        const int4* src = reinterpret_cast<const int4*>(a.psi_tab);
+        const int4* src = reinterpret_cast<const int4*>(static_cast<const unsigned char*>(a.psi_tab) + (kPsiBytes + 8u * kExpTabSize - kTabBytes));
         int4* dst = reinterpret_cast<int4*>(smem_raw);
-        constexpr int chunks = (int)(kEstepTableBytes / sizeof(int4));
+        constexpr int chunks = (int)(kTabBytes / sizeof(int4));
         for (int i = threadIdx.x; i < chunks; i += blockDim.x) dst[i] = src[i];
         for (int i = threadIdx.x; i < 128; i += blockDim.x) logtab[i] = kLogTab[i];
         // constants and rings start as zeros (a phantom word may read a slot that was never staged)
-        double* rings = reinterpret_cast<double*>(smem_raw + kEstepTableBytes);
+        double* rings = reinterpret_cast<double*>(smem_raw + kTabBytes);
         const int ring_doubles = 2 + (int)(blockDim.x >> 5) * kRing * (int)(2 * KS + 2);
         for (int i = threadIdx.x; i < ring_doubles; i += blockDim.x) rings[i] = (i == 1) ? inv_K : 0.0;
         __syncthreads();
@@ -101,13 +112,15 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
     // resident (programmatic dependent launch, em.cu): the two launches then share every SM from the start
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     SmemTables tb;
-    tb.psi = (uint32_t)__cvta_generic_to_shared(smem_raw);
+    const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem_raw);
+    tb.exp2 = smem_base + kTabBytes - 8u * kExpTabSize;
+    tb.psi = smem_base;                                  // meaningful only when the rows are in shared memory
     tb.log = (uint32_t)__cvta_generic_to_shared(logtab);
-    asm volatile("" : "+r"(tb.psi), "+r"(tb.log));
-    tb.exp2 = tb.psi + (uint32_t)(sizeof(PsiRow) * kPsiRows);
+    asm volatile("" : "+r"(tb.exp2), "+r"(tb.log));
+    const PsiRow* __restrict__ psi_rows_global = static_cast<const PsiRow*>(a.psi_tab);
     // slot: beta'[KS] | phi_old[KS] | lbmax | pad
     const uint32_t slot_bytes = 2u * KS * 8u + 16u;
-    const uint32_t ring_base = tb.psi + (uint32_t)kEstepTableBytes;
+    const uint32_t ring_base = smem_base + kTabBytes;
     const uint32_t ring = ring_base + 16u + (uint32_t)(threadIdx.x >> 5) * (uint32_t)kRing * slot_bytes;
     // two constants in front of the rings, read by address where a lane has nothing of its own to read:
     // 0.0 (beta' of a lane beyond K) and phi before the first sweep (1/K, lda-inference.c:41; 0 beyond K)
@@ -170,7 +183,13 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
             for (int t = 0; t < TPL; t++) {
                 const double tt = g[t] + 1.0;
                 row_key[t] = psi_row_of(tt);
-                tb.psi_row(row_key[t], row[t]);
+                const double2* src = reinterpret_cast<const double2*>(psi_rows_global + row_key[t]);
+#pragma unroll
+                for (int i = 0; i < 3; i++) {
+                    const double2 v = __ldg(src + i);
+                    row[t][2 * i] = v.x;
+                    row[t][2 * i + 1] = v.y;
+                }
                 row_at[t] = (tt - psi_cell_offset(tt)) - 1.0;      // exact: the centre has seven significant bits
                 psi[t] = psi_poly<true>(row[t], g[t] - row_at[t]) - fast_rcp(g[t]);
                 E[t] = fast_exp_tab<true>(psi[t], tb);
@@ -478,8 +497,10 @@ static int launch_long_one(const EStepArgs& args, int sm_count, int block_thread
     if (block_threads > ONILDA_LONG_MAX_THREADS || block_threads < 32 || (block_threads & 31))
         return onilda_fail(ONILDA_EINVAL, "long-document E-step block of %d threads (32..256, whole warps)", block_threads);
     const size_t slot_bytes = 2 * (size_t)args.kstride * 8 + 16;
-    const size_t smem = kEstepTableBytes + 16 + (size_t)(block_threads / 32) * kRing * slot_bytes;
+    const size_t smem = LongTables<TPL>::bytes + 16 + (size_t)(block_threads / 32) * kRing * slot_bytes;
     ONILDA_CUDA(cudaFuncSetAttribute(estep_long_kernel<KC, TPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (args.carveout_pct > 0)
+        ONILDA_CUDA(cudaFuncSetAttribute(estep_long_kernel<KC, TPL>, cudaFuncAttributePreferredSharedMemoryCarveout, args.carveout_pct));
     int per_sm = 0;
     ONILDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_long_kernel<KC, TPL>, block_threads, smem));
     if (per_sm < 1) per_sm = 1;
