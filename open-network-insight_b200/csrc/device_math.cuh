@@ -427,25 +427,29 @@ ONILDA_CONST double kExpTabP[4] = {0.5, 0.16666666666666666, 0.04166666666666666
 template <bool kShallow, class Tables>
 ONILDA_HD double fast_exp_tab(double x, const Tables& tb)
 {
+    // the constants as literals: the instructions then take them from the compiler's own constant bank as operands (an
+    // element of a __constant__ array costs a load instruction per use when registers are short)
     const double magic = 6755399441055744.0;
-    const double t = fma(x, kExpTabC[0], magic);
+    const double c_hi = 92.33248261689366, c_lo = 0.010830424696249145;      // kExpTabC
+    const double p2 = 0.5, p3 = 0.16666666666666666, p4 = 0.041666666666666664, p5 = 0.008333333333333333;      // kExpTabP
+    const double t = fma(x, c_hi, magic);
     const int n = double_lo(t);
     const double kd = t - magic;
-    const double r = fma(kd, -kExpTabC[1], x);
+    const double r = fma(kd, -c_lo, x);
     const double T = tb.exp2_frac(n & (kExpTabSize - 1));
     int k = n >> 6;
     double q;                                              // exp(r) - 1 = r + r^2/2 + ... + r^5/120
     if (kShallow) {
         const double r2 = r * r;
-        const double qa = fma(kExpTabP[0], r, 1.0);
-        const double q34 = fma(kExpTabP[2], r, kExpTabP[1]);
+        const double qa = fma(p2, r, 1.0);
+        const double q34 = fma(p4, r, p3);
         const double r3 = r2 * r;
-        const double qb = fma(kExpTabP[3], r2, q34);
+        const double qb = fma(p5, r2, q34);
         q = fma(r3, qb, r * qa);
     } else {
-        q = fma(kExpTabP[3], r, kExpTabP[2]);
-        q = fma(q, r, kExpTabP[1]);
-        q = fma(q, r, kExpTabP[0]);
+        q = fma(p5, r, p4);
+        q = fma(q, r, p3);
+        q = fma(q, r, p2);
         q = fma(q, r, 1.0);
         q = q * r;
     }
