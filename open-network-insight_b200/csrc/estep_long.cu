@@ -4,18 +4,24 @@
 // Why a kernel of its own.  The words of a document are a serial chain (Gauss-Seidel order of
 // lda-inference.c:50-75: gamma and digamma(gamma) change after every word), so the E-step cannot end
 // before the longest document has walked len x sweeps dependent steps.  This kernel is built around the
-// latency of ONE step (measured with ncu, profiles/): nothing that can be known in advance may sit on
-// the chain E -> s -> phi -> gamma -> psi -> E.
-//   * rows (beta' of the word, last sweep's phi, lbmax) are fetched kDepth = 14 words ahead with
-//     cp.async into a ring of kRing = 16 slots per warp and read from shared memory one word ahead:
-//     a step is ~450 cycles, a trip to L2 under load up to ~1000, to HBM more - register prefetch two
-//     words ahead still left 340 cycles of scoreboard stall per word on the first multiply.
-//   * word ids come 32 at a time in one coalesced load per lane, two blocks ahead; a word's id is a
+// latency of ONE step (measured with ncu, profiles/ncu_r2_long_word_trace.txt: 340 cycles): nothing that can be
+// known in advance may sit on the chain E -> s -> phi -> gamma -> psi -> E.
+//   * rows (beta' of the word, last sweep's phi, lbmax) are fetched kDepth = 6 words ahead with cp.async into a
+//     ring of kRing = 8 slots per warp and read from shared memory one word ahead: a trip to L2 under load is
+//     up to ~1000 cycles, to HBM more - register prefetch two words ahead still left 340 cycles of scoreboard
+//     stall per word on the first multiply.
+//   * word ids come 32 at a time in one coalesced load per lane, three blocks ahead; a word's id is a
 //     shuffle from the lane that holds it.
-//   * phi = x/s is x*r + (x*r)*e with the hardware reciprocal seed r (three dependent operations),
-//     gamma is updated with one fma (gamma - c*phi_old is formed beside the chain).
-// The arithmetic is that of estep.cu (see its header): psi and exp(psi) from the shared-memory tables,
-// the likelihood bound in the algebraic form, a log-space redo of a word whose sum leaves the safe range.
+//   * s = sum over the lanes of x = E beta' through the FP64 tensor pipe: two mma.m8n8k4.f64 and one add,
+//     60 cycles against 168 for five butterfly rounds (estep_common.cuh).  A word starts with them; the
+//     staging work for later words is issued while they are in flight.
+//   * phi = x/s is x*r + (x*r)*e with the hardware reciprocal seed r, gamma is updated with one fma after e
+//     (gamma - c*phi_old + c*x*r is formed beside the chain).
+//   * K <= 32: the lane keeps the psi-table row of its gamma in registers; a word whose gamma left the row's
+//     cell, like a word whose s is unusable, makes the warp leave the word loop, repair (reload the row /
+//     redo the word in log space) and enter again - the loop itself has no taken branch.
+// The arithmetic is that of estep.cu (see its header): psi and exp(psi) from tables, the likelihood bound in
+// the algebraic form, a log-space redo of a word whose sum leaves the safe range.
 #include "estep_common.cuh"
 
 #ifndef ONILDA_LONG_MAX_THREADS
