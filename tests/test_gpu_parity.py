@@ -106,6 +106,30 @@ def test_long_document_path(oni, oracle, group, case, monkeypatch):
     em.close()
 
 
+@pytest.mark.parametrize("long_len", ["1024", "1"])
+def test_documents_beyond_the_math_tables(oni, oracle, long_len, monkeypatch):
+    """psi and exp(psi) come from tables that end at gamma + 1 = 2^20.  Documents with more tokens than that take the
+    closed forms: per bundle in the bulk launch (long_len 1024: the documents here are short), per launch for the
+    long-document kernels (long_len 1: every document goes there, and the staged kernel hands over to the general one)."""
+    monkeypatch.setenv("ONILDA_LONG_LEN", long_len)
+    d, c, m, st = load_case(oni, "k20")
+    off, w, cn, tot, V = oracle.read_dat(d / "c.dat")
+    cn = cn.copy()
+    for doc in range(0, len(off) - 1, 7):          # every seventh document: about 100 entries x 40 000 = 4 M tokens
+        cn[off[doc]:off[doc + 1]] *= 40000
+    assert np.add.reduceat(cn.astype(np.int64), off[:-1]).max() > 2 ** 21
+    alpha, lb = oracle.load_model(d / "000")
+    ref = oracle.e_step(off, w, cn, V, alpha, lb, st.var_max_iter, st.var_converged)
+    big = oni.Corpus.from_csr(off, w, cn, num_terms=V)
+    em = oni.EM(big, m, st)
+    em.estep()
+    assert rel_err(em.doc_likelihood(), ref["doc_lik"], 1e-9) < 1e-9
+    assert rel_err(em.gamma(), ref["gamma"], 1e-9) < 1e-9
+    lik, _, _ = em.mstep()
+    assert abs(lik - ref["lik"]) / abs(ref["lik"]) < 1e-11
+    em.close()
+
+
 @pytest.mark.parametrize("case", CASES)
 def test_full_em_against_reference_files(oni, case, tmp_path):
     """The whole run from 000 against what the reference binary wrote (likelihood.dat, final.*)."""
