@@ -25,6 +25,7 @@ struct onilda_em {
     int timing;
     int64_t num_long;           // documents of at least long_len entries: prefix of d_order
     int64_t long_max_total;     // most tokens in one of them (decides whether the table-only long kernel may run)
+    int64_t bulk_max_total;     // most tokens in a document of the bulk launch (decides which variant of the kernel runs)
     int long_len, long_group, long_smem, long_threads, long_per_sm, bulk_group, bulk_per_sm, bulk_threads, pdl, carveout_pct;
     // shard
     int64_t doc_begin, doc_end, num_docs, nnz;
@@ -347,6 +348,11 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
             const int64_t t = c->totals[doc_begin + order[(size_t)i]];
             if (t > em->long_max_total) em->long_max_total = t;
         }
+        em->bulk_max_total = 0;
+        for (int64_t i = em->num_long; i < D; i++) {
+            const int64_t t = c->totals[doc_begin + order[(size_t)i]];
+            if (t > em->bulk_max_total) em->bulk_max_total = t;
+        }
         TRYCUDA(cudaMemcpyAsync(em->d_offsets, off.data(), sizeof(int64_t) * (size_t)(D + 1), cudaMemcpyHostToDevice, em->stream));
         if (D > 0) {
             TRYCUDA(cudaMemcpyAsync(em->d_totals, c->totals + doc_begin, sizeof(int32_t) * (size_t)D, cudaMemcpyHostToDevice, em->stream));
@@ -419,6 +425,14 @@ static int run_estep(onilda_em* em, bool accumulate)
     a.error_flag = em->d_error;
     ONILDA_CUDA(cudaMemsetAsync(em->d_queue, 0, 2 * sizeof(unsigned long long), em->stream));
     ONILDA_CUDA(cudaMemsetAsync(em->d_error + 1, 0, sizeof(int), em->stream));
+    // The general kernel without its rare paths (estep.cu) where no gamma can leave the math tables (every gamma of a
+    // document lies within [alpha, alpha + its tokens]) and no word's sum can leave the range of its reciprocal
+    // (alpha >= 0.0016).  ONILDA_RARE_PATHS=1 forces the full variant.
+    auto needs_rare_paths = [&](int64_t max_total) {
+        return getenv("ONILDA_RARE_PATHS") != nullptr ||
+               !(em->alpha >= 0.0016 && em->alpha + (double)max_total + 1.0 < (double)(1 << kPsiOctaves) - 1.0);
+    };
+    a.rare_paths = 1;
     int rc;
     if (em->num_long > 0 && em->pdl) {
         // Both launches in ONE stream, the bulk one as the secondary of a programmatic dependent launch: its blocks are
@@ -429,6 +443,7 @@ static int run_estep(onilda_em* em, bool accumulate)
         // iterations in eighteen of a bench run).
         EStepArgs b = a;
         b.order_begin = 0; b.order_count = em->num_long; b.queue = em->d_queue + 1;
+        b.rare_paths = needs_rare_paths(em->long_max_total);
         const bool tables_cover = em->alpha >= 1e-8 && em->alpha + (double)em->long_max_total + 1.0 < (double)(1 << kPsiOctaves) - 1.0;
         if (em->long_group == 32 && em->K <= 64 && tables_cover && !getenv("ONILDA_LONG_GENERIC"))
             rc = launch_estep_long(b, em->sm_count, em->long_threads, em->long_per_sm, em->stream, &l);
@@ -436,6 +451,7 @@ static int run_estep(onilda_em* em, bool accumulate)
             rc = launch_estep(em->long_group, b, em->sm_count, em->long_threads, em->long_smem, em->long_per_sm, em->stream, &l);
         if (rc != ONILDA_OK) return rc;
         a.order_begin = em->num_long; a.order_count = em->num_docs - em->num_long; a.queue = em->d_queue;
+        a.rare_paths = needs_rare_paths(em->bulk_max_total);
         rc = launch_estep(em->bulk_group, a, em->sm_count, em->bulk_threads, 0, em->bulk_per_sm, em->stream, &l, true);
         if (rc != ONILDA_OK) return rc;
     } else {
@@ -452,6 +468,7 @@ static int run_estep(onilda_em* em, bool accumulate)
             ONILDA_CUDA(cudaStreamWaitEvent(em->stream, em->ev_forked, 0));
             EStepArgs b = a;
             b.order_begin = 0; b.order_count = em->num_long; b.queue = em->d_queue + 1;
+            b.rare_paths = needs_rare_paths(em->long_max_total);
             // The staged one-document-per-warp kernel reads psi and exp(psi) from the tables only: every gamma of its
             // documents, within [alpha, alpha + total], must lie inside their range (device_math.cuh).  Otherwise the
             // general kernel, which has the closed forms, takes the long documents too.
@@ -465,6 +482,7 @@ static int run_estep(onilda_em* em, bool accumulate)
             ONILDA_CUDA(cudaEventRecord(em->ev_join, em->long_stream));
         }
         a.order_begin = em->num_long; a.order_count = em->num_docs - em->num_long; a.queue = em->d_queue;
+        a.rare_paths = needs_rare_paths(em->bulk_max_total);
         rc = launch_estep(em->bulk_group, a, em->sm_count, em->bulk_threads, 0, em->num_long > 0 ? em->bulk_per_sm : 0, em->stream, &l);
         if (rc != ONILDA_OK) return rc;
         if (em->timing) ONILDA_CUDA(cudaEventRecord(em->ev_bulk_end, em->stream));

@@ -58,7 +58,13 @@ namespace onilda {
 
 // KC: the number of topics when known at compile time (0: taken from the arguments).  With it the
 // row stride, the padding tests and every row address are constants or one multiply-add.
-template <int G, int TPL, int KC>
+// kRare: the kernel carries its two rare paths - the closed forms of psi / exp(psi) for a bundle whose gamma may leave
+// the tables (alpha < 1e-8 or alpha + tokens >= 2^20 - 2) and the log-space redo of a word whose sum s leaves
+// [2^-963, 2^963).  Both are decided on the host per launch (em.cu): s >= min_k exp(psi(gamma_k)) >= exp(psi(alpha))
+// because the largest beta' of a word is exactly 1, so for alpha >= 0.0016 (psi > -626, exp > 2^-903) no sum can
+// leave the range, and the documents' token counts are known.  Without them the word loop has no call, no taken
+// branch and no spills (2.6 % of the E-step at cfg 2).
+template <int G, int TPL, int KC, bool kRare>
 __global__ void __launch_bounds__(ONILDA_ESTEP_MAX_THREADS) estep_kernel(EStepArgs a, unsigned long long num_bundles)
 {
     constexpr int DPW = 32 / G;      // documents per warp
@@ -136,7 +142,7 @@ __global__ void __launch_bounds__(ONILDA_ESTEP_MAX_THREADS) estep_kernel(EStepAr
 
         // Every gamma of a document stays within [alpha, alpha + total] up to rounding.  Where that
         // interval leaves the tables' range the whole bundle takes the closed forms (warp-uniform).
-        const bool closed_forms = __any_sync(0xffffffffu, !(a.alpha >= kPsiTableMin && a.alpha + total + 1.0 < kPsiTableMax));
+        const bool closed_forms = kRare && __any_sync(0xffffffffu, !(a.alpha >= kPsiTableMin && a.alpha + total + 1.0 < kPsiTableMax));
         auto psi_exp = [&](double (&g)[TPL], double (&psi)[TPL], double (&E)[TPL]) {
             if (__builtin_expect(closed_forms, 0)) {
 #pragma unroll
@@ -243,7 +249,7 @@ __global__ void __launch_bounds__(ONILDA_ESTEP_MAX_THREADS) estep_kernel(EStepAr
                 s_prev = s;
                 c_prev = it.count;
                 lb_prev = it.lbmax;
-                if (__builtin_expect(__any_sync(0xffffffffu, bad), 0)) {
+                if (kRare && __builtin_expect(__any_sync(0xffffffffu, bad), 0)) {
                     // rare: redo this word in log space, as the reference does (lda-inference.c:52-68); out of
                     // line, through a scratch block that only this branch touches
                     if (bad && j == 0) atomicAdd(a.error_flag + 1, 1);
@@ -377,7 +383,7 @@ __global__ void __launch_bounds__(ONILDA_ESTEP_MAX_THREADS) estep_kernel(EStepAr
 
 // Grid for `num_bundles` bundles of one (G, TPL) instantiation: persistent, at most the resident
 // capacity of `sm_count` SMs (or `max_blocks` when the launch shares the device with another).
-template <int G, int TPL, int KC>
+template <int G, int TPL, int KC, bool kRare = false>
 static int launch_one(const EStepArgs& args, int sm_count, int block_threads, int extra_smem, int max_per_sm,
                       cudaStream_t stream, bool after_resident)
 {
@@ -389,11 +395,11 @@ static int launch_one(const EStepArgs& args, int sm_count, int block_threads, in
     if (block_threads > ONILDA_ESTEP_MAX_THREADS || block_threads < 32 || (block_threads & 31))
         return onilda_fail(ONILDA_EINVAL, "E-step block of %d threads (32..%d, whole warps)", block_threads, ONILDA_ESTEP_MAX_THREADS);
     const size_t smem = kEstepTableBytes + (size_t)extra_smem;
-    ONILDA_CUDA(cudaFuncSetAttribute(estep_kernel<G, TPL, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ONILDA_CUDA(cudaFuncSetAttribute(estep_kernel<G, TPL, KC, kRare>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (args.carveout_pct > 0)
-        ONILDA_CUDA(cudaFuncSetAttribute(estep_kernel<G, TPL, KC>, cudaFuncAttributePreferredSharedMemoryCarveout, args.carveout_pct));
+        ONILDA_CUDA(cudaFuncSetAttribute(estep_kernel<G, TPL, KC, kRare>, cudaFuncAttributePreferredSharedMemoryCarveout, args.carveout_pct));
     int per_sm = 0;
-    ONILDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_kernel<G, TPL, KC>, block_threads, smem));
+    ONILDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_kernel<G, TPL, KC, kRare>, block_threads, smem));
     if (per_sm < 1) per_sm = 1;
     if (max_per_sm > 0 && per_sm > max_per_sm) per_sm = max_per_sm;
     const unsigned long long wpb = (unsigned long long)(block_threads / 32);
@@ -414,9 +420,9 @@ static int launch_one(const EStepArgs& args, int sm_count, int block_threads, in
         at[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = at;
         cfg.numAttrs = 1;
-        ONILDA_CUDA(cudaLaunchKernelEx(&cfg, estep_kernel<G, TPL, KC>, args, num_bundles));
+        ONILDA_CUDA(cudaLaunchKernelEx(&cfg, estep_kernel<G, TPL, KC, kRare>, args, num_bundles));
     } else {
-        estep_kernel<G, TPL, KC><<<(unsigned)grid, block_threads, smem, stream>>>(args, num_bundles);
+        estep_kernel<G, TPL, KC, kRare><<<(unsigned)grid, block_threads, smem, stream>>>(args, num_bundles);
     }
     ONILDA_CUDA(cudaGetLastError());
     return ONILDA_OK;
@@ -426,6 +432,19 @@ template <int G>
 static int launch_group(int tpl, const EStepArgs& args, int sm_count, int block_threads, int extra_smem, int max_per_sm,
                         cudaStream_t stream, bool after_resident)
 {
+    if (args.rare_paths) {      // no kernels with the topic count compiled in for these
+        switch (tpl) {
+            case 1: return launch_one<G, 1, 0, true>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
+            case 2: return launch_one<G, 2, 0, true>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
+            case 3: return launch_one<G, 3, 0, true>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
+            case 4: return launch_one<G, 4, 0, true>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
+            case 5: return launch_one<G, 5, 0, true>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
+            case 6: return launch_one<G, 6, 0, true>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
+            case 7: return launch_one<G, 7, 0, true>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
+            case 8: return launch_one<G, 8, 0, true>(args, sm_count, block_threads, extra_smem, max_per_sm, stream, after_resident);
+        }
+        return onilda_fail(ONILDA_EINVAL, "unsupported topics-per-lane %d", tpl);
+    }
     // ONI's own topic counts (ml_ops.sh: TOPIC_COUNT=20; the proxy shape of BASELINE.json: 50) get kernels
     // with the count compiled in
     if (args.num_topics == 20 && args.kstride == kpad_for(20) && tpl == (20 + G - 1) / G)

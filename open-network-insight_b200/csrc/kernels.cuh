@@ -58,6 +58,7 @@ struct EStepArgs {
     // model tables, word-major [V][kpad]
     const double* beta_scaled;  // exp(log_beta[w][k] - lbmax[w]); 0 in padding
     const double* lbmax;        // [V] max_k log_beta[w][k]
+    int rare_paths;             // host side only: the launch needs the kernel variant with the closed forms and the log-space redo (estep.cu)
     int carveout_pct;           // host side only: preferred shared-memory carve-out of the launch (percent of the maximum; 0 = the driver's choice)
     const void* psi_tab;        // device_math.cuh PsiRow[kPsiRows] (hostmath.c builds it)
     const double* exp_tab;      // 2^(i/64), i < 64
