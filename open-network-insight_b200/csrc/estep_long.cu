@@ -77,7 +77,9 @@ struct LongWord {
 }  // namespace
 
 // TPL: topics per lane (1 for K <= 32, 2 for K <= 64); lane j holds topics j and j + 32
-template <int KC, int TPL>
+// kGuard: test every word's sum s for the range of its reciprocal and redo the word in log space where it fails.
+// The host leaves it out when alpha >= 0.0016: no sum can then leave the range (estep.cu, kRare).
+template <int KC, int TPL, bool kGuard>
 __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCKS) estep_long_kernel(EStepArgs a, unsigned long long num_docs)
 {
     constexpr unsigned FULL = 0xffffffffu;
@@ -334,16 +336,17 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
                     if (valid[t] && in_doc) prow[t * 32] = p;
                     acc_psi = fma(it.count * p, psi[t], acc_psi);
                 }
-                s_in = s;
-                bool leave = (uint32_t)(double_hi(s) - 0x03C00000) >= (uint32_t)(0x7C200000 - 0x03C00000);
+                if (kGuard) s_in = s;
+                bool leave = kGuard && (uint32_t)(double_hi(s) - 0x03C00000) >= (uint32_t)(0x7C200000 - 0x03C00000);
                 if (kKeepRows) leave |= psi_exp_kept(gam, psi, E);
                 else psi_exp(gam, psi, E);
+                if (!kGuard && !kKeepRows) return false;
                 return __any_sync(FULL, leave);
             };
             // the word again in log space, as the reference does it (lda-inference.c:52-68), from the saved state.  Rare;
             // reached only from behind the word loop, so that the loop itself has no taken branch.
             auto redo = [&](const LongWord<TPL>& it, int n) {
-                if ((uint32_t)(double_hi(s_in) - 0x03C00000) < (uint32_t)(0x7C200000 - 0x03C00000)) {
+                if (!kGuard || (uint32_t)(double_hi(s_in) - 0x03C00000) < (uint32_t)(0x7C200000 - 0x03C00000)) {
                     psi_exp_reload(gam, psi, E);      // the sum was fine: a lane's gamma has moved to another cell of the table
                     return;
                 }
@@ -497,25 +500,25 @@ __global__ void __launch_bounds__(ONILDA_LONG_MAX_THREADS, ONILDA_LONG_MIN_BLOCK
     }
 }
 
-template <int KC, int TPL>
+template <int KC, int TPL, bool kGuard = false>
 static int launch_long_one(const EStepArgs& args, int sm_count, int block_threads, int max_per_sm, cudaStream_t stream)
 {
     if (block_threads > ONILDA_LONG_MAX_THREADS || block_threads < 32 || (block_threads & 31))
         return onilda_fail(ONILDA_EINVAL, "long-document E-step block of %d threads (32..256, whole warps)", block_threads);
     const size_t slot_bytes = 2 * (size_t)args.kstride * 8 + 16;
     const size_t smem = LongTables<TPL>::bytes + 16 + (size_t)(block_threads / 32) * kRing * slot_bytes;
-    ONILDA_CUDA(cudaFuncSetAttribute(estep_long_kernel<KC, TPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ONILDA_CUDA(cudaFuncSetAttribute(estep_long_kernel<KC, TPL, kGuard>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (args.carveout_pct > 0)
-        ONILDA_CUDA(cudaFuncSetAttribute(estep_long_kernel<KC, TPL>, cudaFuncAttributePreferredSharedMemoryCarveout, args.carveout_pct));
+        ONILDA_CUDA(cudaFuncSetAttribute(estep_long_kernel<KC, TPL, kGuard>, cudaFuncAttributePreferredSharedMemoryCarveout, args.carveout_pct));
     int per_sm = 0;
-    ONILDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_long_kernel<KC, TPL>, block_threads, smem));
+    ONILDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_long_kernel<KC, TPL, kGuard>, block_threads, smem));
     if (per_sm < 1) per_sm = 1;
     if (max_per_sm > 0 && per_sm > max_per_sm) per_sm = max_per_sm;
     const unsigned long long wpb = (unsigned long long)(block_threads / 32);
     const unsigned long long docs = (unsigned long long)args.order_count;
     unsigned long long grid = (unsigned long long)sm_count * per_sm;
     if (grid > (docs + wpb - 1) / wpb) grid = (docs + wpb - 1) / wpb;
-    estep_long_kernel<KC, TPL><<<(unsigned)grid, block_threads, smem, stream>>>(args, docs);
+    estep_long_kernel<KC, TPL, kGuard><<<(unsigned)grid, block_threads, smem, stream>>>(args, docs);
     ONILDA_CUDA(cudaGetLastError());
     return ONILDA_OK;
 }
@@ -527,7 +530,10 @@ int launch_estep_long(const EStepArgs& args, int sm_count, int block_threads, in
     if (args.num_topics > 64 || args.kstride > 64 || (args.kstride & 1))
         return onilda_fail(ONILDA_EINVAL, "long-document E-step: %d topics with row stride %d unsupported", args.num_topics, args.kstride);
     int rc;
-    if (args.num_topics == 20 && args.kstride == kpad_for(20)) rc = launch_long_one<20, 1>(args, sm_count, block_threads, max_per_sm, stream);
+    if (args.rare_paths) {      // the guarded variant, topic count not compiled in
+        if (args.num_topics <= 32) rc = launch_long_one<0, 1, true>(args, sm_count, block_threads, max_per_sm, stream);
+        else rc = launch_long_one<0, 2, true>(args, sm_count, block_threads, max_per_sm, stream);
+    } else if (args.num_topics == 20 && args.kstride == kpad_for(20)) rc = launch_long_one<20, 1>(args, sm_count, block_threads, max_per_sm, stream);
     else if (args.num_topics == 50 && args.kstride == kpad_for(50)) rc = launch_long_one<50, 2>(args, sm_count, block_threads, max_per_sm, stream);
     else if (args.num_topics <= 32) rc = launch_long_one<0, 1>(args, sm_count, block_threads, max_per_sm, stream);
     else rc = launch_long_one<0, 2>(args, sm_count, block_threads, max_per_sm, stream);
