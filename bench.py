@@ -161,6 +161,29 @@ class ClockSampler:
 
 # ----------------------------------------------------------------- reference lda-c on the host cores
 
+def bind_near_gpu(local_rank):
+    """One process per GPU: run on the cores NVML lists for this rank's GPU, so that the host buffers this process
+    allocates from here on (first touch) and the copies to and from them stay on the GPU's own NUMA node instead of all
+    ranks sharing whichever node they were started on.  Returns the number of cores bound to (0: left as it was)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        index = local_rank
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+        if vis and all(x.strip().isdigit() for x in vis.split(",")):
+            index = int(vis.split(",")[local_rank])
+        mask = pynvml.nvmlDeviceGetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(index), (os.cpu_count() + 63) // 64)
+        near = {64 * i + b for i, w in enumerate(mask) for b in range(64) if (int(w) >> b) & 1}
+        cpus = sorted(near & os.sched_getaffinity(0))
+        if not cpus:
+            return 0
+        os.sched_setaffinity(0, cpus)
+        return len(cpus)
+    except Exception as e:          # no NVML, no such call on this platform: leave the affinity alone
+        log(f"[rank {local_rank}] no NUMA binding: {e}")
+        return 0
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -862,6 +885,7 @@ def main():
     if oni.device_count() < 1:
         raise SystemExit("bench.py needs a CUDA device: libonilda has no CPU path")
     dist = None
+    host_cpus = bind_near_gpu(local_rank) if world > 1 else 0
     if world > 1:
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")    # stdout carries the one JSON line only
         import torch.distributed as dist
@@ -969,6 +993,8 @@ def main():
     d2h = K * V * 8 + D * K * 8 + 32 + 4
     e2e = {"value": T_all / (e2e_elapsed / args.steps), "unit": "tokens/s", "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * e2e_elapsed / args.steps}
+    if world > 1:
+        e2e["host_cores_bound_per_rank"] = host_cpus      # bind_near_gpu: the cores NVML lists for the rank's GPU (0: not bound)
 
     gamma = em.gamma()
     log_beta = np.array(em.model().log_beta)

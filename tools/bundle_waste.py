@@ -34,6 +34,23 @@ def executed(order):
     return int((l.max(1) * w.max(1)).sum()) * DPW, int((l.max(1) * w.max(1)).sum())
 
 by_len = bulk[np.argsort(-lens[bulk], kind="stable")]
+
+
+def windows(order, max_size=2048, ratio=1.1):
+    """boundaries over the length-sorted order: at most max_size documents, longest / shortest <= ratio"""
+    l = lens[order]
+    b = [0]
+    while b[-1] < len(order):
+        lo = b[-1]
+        hi = min(lo + max_size, len(order))
+        # first position where the length falls below l[lo] / ratio
+        cut = lo + int(np.searchsorted(-l[lo:hi], -l[lo] / ratio, side="right"))
+        b.append(max(lo + 1, min(hi, cut)))
+    return np.array(b)
+
+
+win = windows(by_len)
+win_id = np.repeat(np.arange(len(win) - 1), np.diff(win))
 prev = None
 for it in range(iters):
     em.estep(); em.mstep()
@@ -50,6 +67,9 @@ for it in range(iters):
         o2 = bulk[np.lexsort((-lens[bulk], -prev[bulk], -cls))]
         ex_c, warp_c = executed(o2)
         line += f"  | by prev sweeps x{ex_p / useful:.2f} (warp-steps {warp_p:.3e})  | len class, prev sweeps x{ex_c / useful:.2f} (warp-steps {warp_c:.3e})"
+        o3 = by_len[np.lexsort((np.arange(len(by_len)), -prev[by_len], win_id))]      # stable sort by previous sweeps inside each window
+        ex_w, warp_w = executed(o3)
+        line += f"  | windows x{ex_w / useful:.2f} (warp-steps {warp_w:.3e})"
         line += f"  corr {np.corrcoef(prev[bulk], sw[bulk])[0, 1]:.3f}"
     print(line, flush=True)
     prev = sw

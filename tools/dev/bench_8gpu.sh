@@ -1,8 +1,8 @@
-( time python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29563 bench.py --gpus 8 --steps 18 --warmup 3 > gpurun_out/r2_bench_n8c.json 2> gpurun_out/r2_bench_n8c.err ) 2>&1 | grep real
-grep -i "error\|failed\|Traceback" gpurun_out/r2_bench_n8c.err | head
+( time python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29563 bench.py --gpus 8 --steps 18 --warmup 3 > gpurun_out/r2_bench_n8.json 2> gpurun_out/r2_bench_n8.err ) 2>&1 | grep real
+grep -i "error\|failed\|Traceback" gpurun_out/r2_bench_n8.err | head
 python - <<'PY'
 import json
-d=json.load(open('gpurun_out/r2_bench_n8c.json'))
+d=json.load(open('gpurun_out/r2_bench_n8.json'))
 print({k:d[k] for k in ('value','ms_per_step','n_gpus')}, d['e2e']['value'])
 print(d['em']['estep_ms'])
 for k in ('strong','strong_dns','strong_proxy'):
