@@ -818,6 +818,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--no-double-buffer", action="store_true", help="skip the double-buffered variant of the end-to-end leg")
     ap.add_argument("--scale", type=float, default=1.0, help="development only: shrink the number of documents")
     ap.add_argument("--hub-frac", type=float, default=None, help="development only: fraction of hub documents")
     ap.add_argument("--no-e2e", action="store_true", help="development only")
@@ -995,6 +996,64 @@ def main():
            "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * e2e_elapsed / args.steps}
     if world > 1:
         e2e["host_cores_bound_per_rank"] = host_cpus      # bind_near_gpu: the cores NVML lists for the rank's GPU (0: not bound)
+
+    # The same step with the NEXT step's corpus copy under way while this one computes (what a caller with a stream of
+    # corpora in host memory does): two handles, each with its own stream and device buffers; the CSR arrays of step
+    # i + 1 go up from a second host thread during step i (onilda_em_reload_corpus), the model, which step i produces,
+    # follows when it is there (onilda_em_reload_model).  Every step moves the same bytes in and out, inside the timed
+    # region.  This is the end-to-end value; the one-call-at-a-time figure stays beside it as e2e.serial.
+    if not args.no_e2e and not args.no_double_buffer:
+        import threading
+        em2 = None
+        try:
+            em2 = oni.EM(corpus, model0, settings, device=local_rank)
+            if dist is not None:
+                oni.comm_attach(em2, comm_id(), world, rank)
+        except oni.OnildaError as e:          # no room for a second set of device buffers: the serial figure stands
+            log(f"[rank {rank}] double-buffered leg skipped: {e}")
+            em2 = None
+        ok = torch.tensor([1.0 if em2 is not None else 0.0], device=device, dtype=torch.float64)
+        if dist is not None:
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if float(ok.item()) > 0:
+            pair = [em, em2]
+            cur.log_beta[...] = model0.log_beta
+            cur.alpha = model0.alpha
+            pair[0].reload_corpus()
+
+            def db_step(i):
+                x, y = pair[i % 2], pair[(i + 1) % 2]
+                x.reload_model(cur)               # H2D: model (before the big copy is queued: copies of one direction run in order)
+                th = threading.Thread(target=y.reload_corpus)      # H2D: the next step's CSR words + counts + totals
+                th.start()
+                x.estep()
+                out = x.mstep()
+                oni._check(lib.onilda_em_get_model(x._h, cur._h))      # D2H: new model
+                oni._check(lib.onilda_em_get_gamma(x._h, g_host))      # D2H: gamma
+                th.join()
+                return out
+
+            db_liks = [db_step(i)[0] for i in range(args.warmup)]
+            barrier()
+            t_begin = time.perf_counter()
+            for i in range(args.warmup, args.warmup + args.steps):
+                db_liks.append(db_step(i)[0])
+            barrier()
+            db_elapsed = time.perf_counter() - t_begin
+            if dist is not None:
+                t = torch.tensor([db_elapsed], device=device, dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                db_elapsed = float(t.item())
+            e2e["serial"] = {"value": e2e["value"], "ms_per_step": e2e["ms_per_step"],
+                             "note": "reload -> estep -> mstep -> get_model -> get_gamma, one call after the other on one handle, nothing overlapped"}
+            e2e["value"] = T_all / (db_elapsed / args.steps)
+            e2e["ms_per_step"] = 1e3 * db_elapsed / args.steps
+            e2e["likelihoods_equal_to_serial"] = bool(np.allclose(db_liks, e2e_liks[1:], rtol=1e-9, atol=0.0))
+            e2e["note"] = ("double-buffered: two EM handles; the CSR arrays of step i + 1 are copied host -> device "
+                           "(onilda_em_reload_corpus, second host thread, the other handle's stream) while step i computes; "
+                           "every step copies h2d_bytes_per_step in and d2h_bytes_per_step out inside the timed region")
+        if em2 is not None:
+            em2.close()
 
     gamma = em.gamma()
     log_beta = np.array(em.model().log_beta)

@@ -280,6 +280,12 @@ int onilda_em_mstep(onilda_em* em, double* likelihood, double* converged, int* k
  * reallocating.  Returns once the copies are done (the caller may reuse `m`).  With it one call sequence reload -> iterate -> get_model /
  * get_gamma is a stateless EM step on HOST buffers. */
 int onilda_em_reload(onilda_em* em, const onilda_model* m);
+/* The two halves of onilda_em_reload.  A caller that feeds a stream of corpora from host memory keeps two handles and
+ * sends the next one's CSR arrays (reload_corpus, from another thread: handles are independent and each has its own
+ * stream) while the current one iterates; the model, which depends on the step before, follows with reload_model.
+ * No reference counterpart (the reference reads its corpus once, lda-estimate.c:434). */
+int onilda_em_reload_corpus(onilda_em* em);
+int onilda_em_reload_model(onilda_em* em, const onilda_model* m);
 /* estep + mstep for a single shard. */
 int onilda_em_iterate(onilda_em* em, double* likelihood, double* converged, int* keep_going);
 /* In-process sum of the packed statistics of `n` handles (one per device, same

@@ -111,6 +111,8 @@ def lib():
     L.onilda_em_destroy.restype = None
     L.onilda_em_estep.argtypes = [_vp]
     L.onilda_em_reload.argtypes = [_vp, _vp]
+    L.onilda_em_reload_corpus.argtypes = [_vp]
+    L.onilda_em_reload_model.argtypes = [_vp, _vp]
     L.onilda_em_suffstats_device.argtypes = [_vp, C.POINTER(_vp), C.POINTER(C.c_int64)]
     L.onilda_em_mstep.argtypes = [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int)]
     L.onilda_em_iterate.argtypes = [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int)]
@@ -435,6 +437,14 @@ class EM:
 
     def reload(self, model: "Model"):
         _check(lib().onilda_em_reload(self._h, model._h))
+
+    def reload_corpus(self):
+        """host -> device copy of the shard's CSR arrays alone (the first half of reload)"""
+        _check(lib().onilda_em_reload_corpus(self._h))
+
+    def reload_model(self, model: "Model"):
+        """alpha + log_beta host -> device and the EM loop state reset (the second half of reload)"""
+        _check(lib().onilda_em_reload_model(self._h, model._h))
 
     def mstep(self):
         lik, conv, keep = C.c_double(), C.c_double(), C.c_int()

@@ -374,20 +374,33 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
     return ONILDA_OK;
 }
 
-extern "C" int onilda_em_reload(onilda_em* em, const onilda_model* m)
+extern "C" int onilda_em_reload_corpus(onilda_em* em)
 {
-    if (!em || !m) return onilda_fail(ONILDA_EINVAL, "em_reload: null argument");
-    if (m->num_topics != em->K || m->num_terms != em->V)
-        return onilda_fail(ONILDA_EINVAL, "em_reload: model is %d x %d, handle is %d x %d", m->num_topics, m->num_terms, em->K, em->V);
+    if (!em) return onilda_fail(ONILDA_EINVAL, "em_reload_corpus: null argument");
     DeviceGuard g(em->device);
     const onilda_corpus* c = em->corpus;
     const int64_t base = c->offsets[em->doc_begin];
-    if (em->nnz > 0) {
-        ONILDA_CUDA(cudaMemcpyAsync(em->d_words, c->words + base, sizeof(int32_t) * (size_t)em->nnz, cudaMemcpyHostToDevice, em->stream));
-        ONILDA_CUDA(cudaMemcpyAsync(em->d_counts, c->counts + base, sizeof(int32_t) * (size_t)em->nnz, cudaMemcpyHostToDevice, em->stream));
+    // In pieces of 16 MB: a copy engine works through its queue in order, and a small copy or memset of ANOTHER handle
+    // (its model, its cleared statistics: the start of its E-step) that lands behind one 430 MB copy waits for all of it.
+    const size_t piece = (size_t)4 << 20;      // elements
+    for (size_t at = 0; at < (size_t)em->nnz; at += piece) {
+        const size_t n = (size_t)em->nnz - at < piece ? (size_t)em->nnz - at : piece;
+        ONILDA_CUDA(cudaMemcpyAsync(em->d_words + at, c->words + base + at, sizeof(int32_t) * n, cudaMemcpyHostToDevice, em->stream));
+        ONILDA_CUDA(cudaMemcpyAsync(em->d_counts + at, c->counts + base + at, sizeof(int32_t) * n, cudaMemcpyHostToDevice, em->stream));
     }
     if (em->num_docs > 0)
         ONILDA_CUDA(cudaMemcpyAsync(em->d_totals, c->totals + em->doc_begin, sizeof(int32_t) * (size_t)em->num_docs, cudaMemcpyHostToDevice, em->stream));
+    // the host arrays belong to the caller: they may be reused as soon as this returns
+    ONILDA_CUDA(cudaStreamSynchronize(em->stream));
+    return ONILDA_OK;
+}
+
+extern "C" int onilda_em_reload_model(onilda_em* em, const onilda_model* m)
+{
+    if (!em || !m) return onilda_fail(ONILDA_EINVAL, "em_reload_model: null argument");
+    if (m->num_topics != em->K || m->num_terms != em->V)
+        return onilda_fail(ONILDA_EINVAL, "em_reload_model: model is %d x %d, handle is %d x %d", m->num_topics, m->num_terms, em->K, em->V);
+    DeviceGuard g(em->device);
     int rc = upload_model(em, m->log_beta);
     if (rc != ONILDA_OK) return rc;
     em->alpha = m->alpha;
@@ -396,9 +409,18 @@ extern "C" int onilda_em_reload(onilda_em* em, const onilda_model* m)
     em->likelihood_old = 0;
     em->converged = 1;
     em->estep_done = 0;
-    // the host arrays belong to the caller: they may be reused as soon as this returns
     ONILDA_CUDA(cudaStreamSynchronize(em->stream));
     return ONILDA_OK;
+}
+
+extern "C" int onilda_em_reload(onilda_em* em, const onilda_model* m)
+{
+    if (!em || !m) return onilda_fail(ONILDA_EINVAL, "em_reload: null argument");
+    if (m->num_topics != em->K || m->num_terms != em->V)
+        return onilda_fail(ONILDA_EINVAL, "em_reload: model is %d x %d, handle is %d x %d", m->num_topics, m->num_terms, em->K, em->V);
+    int rc = onilda_em_reload_corpus(em);
+    if (rc != ONILDA_OK) return rc;
+    return onilda_em_reload_model(em, m);
 }
 
 static int run_estep(onilda_em* em, bool accumulate)

@@ -106,6 +106,32 @@ def test_long_document_path(oni, oracle, group, case, monkeypatch):
     em.close()
 
 
+def test_reload_in_two_halves_on_two_handles(oni):
+    """onilda_em_reload_corpus + onilda_em_reload_model are onilda_em_reload; a second handle may take its corpus copy
+    from another thread while the first iterates (what bench.py's end-to-end leg does)."""
+    import threading
+    d, c, m, st = load_case(oni, "k20")
+    c.pin()
+    a, b = oni.EM(c, m, st), oni.EM(c, m, st)
+    ref = []
+    for _ in range(3):
+        a.reload(m)
+        ref.append(a.iterate()[0])
+    got = []
+    pair = [a, b]
+    pair[0].reload_corpus()
+    for i in range(3):
+        x, y = pair[i % 2], pair[(i + 1) % 2]
+        x.reload_model(m)
+        th = threading.Thread(target=y.reload_corpus)
+        th.start()
+        got.append(x.iterate()[0])
+        th.join()
+    assert np.allclose(got, ref, rtol=1e-12, atol=0.0)
+    a.close()
+    b.close()
+
+
 @pytest.mark.parametrize("long_len", ["1024", "1"])
 def test_documents_beyond_the_math_tables(oni, oracle, long_len, monkeypatch):
     """psi and exp(psi) come from tables that end at gamma + 1 = 2^20.  Documents with more tokens than that take the
