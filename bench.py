@@ -857,18 +857,25 @@ def main():
         cores = host_cores()
         n_docs = reference_sample_docs(offsets, cores)
         n_iters = args.steps + args.warmup
-        with tempfile.TemporaryDirectory() as td:
-            ref = run_reference(td, offsets, words, counts, n_docs, K, V, n_iters, cores, start_model_numpy(K, V, 20161102))
-        if ref is None:
-            emit({"impl": "reference", "unavailable": "oracle/_ref/lda missing or failed on this box"})
-            return 0
-        secs = ref[0]
+        # as in the other arm: a run is the reference's own (settings.txt: em max iter 20 -> 21 iterations); steps beyond it
+        # are the first iterations of another run from the same start model
+        run_len = 21
+        secs = []
+        while len(secs) < n_iters:
+            with tempfile.TemporaryDirectory() as td:
+                ref = run_reference(td, offsets, words, counts, n_docs, K, V, min(run_len, n_iters - len(secs)), cores,
+                                    start_model_numpy(K, V, 20161102))
+            if ref is None:
+                emit({"impl": "reference", "unavailable": "oracle/_ref/lda missing or failed on this box"})
+                return 0
+            secs += ref[0]
         timed = secs[args.warmup:] if len(secs) > args.warmup else secs
         nnz = int(offsets[n_docs])
         tok = int(np.asarray(counts[:nnz], np.int64).sum())
         val = tok / float(np.mean(timed))
-        sample = (f"first {n_docs} docs ({nnz} nnz, {tok} tokens) of the workload, EM iterations {len(secs) - len(timed) + 1}-{len(secs)} "
-                  f"timed ({len(timed)}), {cores} forked ranks of the unmodified lda-c")
+        sample = (f"first {n_docs} docs ({nnz} nnz, {tok} tokens) of the workload, steps {len(secs) - len(timed) + 1}-{len(secs)} "
+                  f"timed ({len(timed)}; a run has {run_len} EM iterations, the steps after it start a new run), "
+                  f"{cores} forked ranks of the unmodified lda-c")
         emit({"metric": "lda_em_tokens_per_sec_per_iter", "value": val, "unit": "tokens/s", "n_gpus": 0,
               "steps": len(timed), "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(timed)),
               "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -909,17 +916,29 @@ def main():
     model0 = oni.Model.new(K, V)
     model0.init_random(20161102)
     model0.alpha = float(np.float32(ALPHA0))
+    # the reference's settings.txt (em max iter 20: run_em stops after 21 iterations, lda-estimate.c:186).  A run of the
+    # bench ends by that rule too; the step after it is iteration 1 of a new run from the same start model.  (Letting
+    # one run go on to iteration 25, as rounds before did, times iterations the reference never executes - and they are
+    # the heaviest: by then alpha has fallen below 0.3 and ordinary documents take 9-12 sweeps instead of 3.)
     settings = oni.Settings.default()
-    settings.em_max_iter = max(settings.em_max_iter, args.steps + args.warmup)
 
     # ------------------------------------------------------------ resident-in-HBM leg
     em = oni.EM(corpus, model0, settings, device=local_rank)
     if dist is not None:
         oni.comm_attach(em, comm_id(), world, rank)      # the exchange is the library's: reduce-scatter, lda_mle, all-gather
 
+    run_lengths = []            # EM iterations of each finished run
+    in_run = [0]
+
     def em_step():
         em.estep()
-        return em.mstep()
+        out = em.mstep()
+        in_run[0] += 1
+        if not out[2]:          # run_em's loop condition no longer holds: the next step starts a new run
+            run_lengths.append(in_run[0])
+            in_run[0] = 0
+            em.reload_model(model0)
+        return out
 
     def barrier():
         torch.cuda.synchronize()
@@ -967,12 +986,24 @@ def main():
     cur.alpha = model0.alpha
     lib = oni.lib()
 
+    # the end-to-end legs reset the handle's loop state at every step (reload), so they count the run's iterations here
+    run_len = run_lengths[0] if run_lengths else settings.em_max_iter + 1
+    e2e_in_run = [0]
+
+    def next_model():
+        e2e_in_run[0] += 1
+        if e2e_in_run[0] >= run_len:          # the run is over: the next step starts from the start model again
+            e2e_in_run[0] = 0
+            cur.log_beta[...] = model0.log_beta
+            cur.alpha = model0.alpha
+
     def e2e_step():
         em.reload(cur)                        # H2D: CSR words+counts+totals, model
         em.estep()
         out = em.mstep()                      # exchange (N > 1), M-step; D2H: likelihood + statistics tail
         oni._check(lib.onilda_em_get_model(em._h, cur._h))      # D2H: new model
         oni._check(lib.onilda_em_get_gamma(em._h, g_host))      # D2H: gamma
+        next_model()
         return out
 
     e2e_liks = [float("nan")]
@@ -1019,6 +1050,7 @@ def main():
             pair = [em, em2]
             cur.log_beta[...] = model0.log_beta
             cur.alpha = model0.alpha
+            e2e_in_run[0] = 0
             pair[0].reload_corpus()
 
             def db_step(i):
@@ -1030,6 +1062,7 @@ def main():
                 out = x.mstep()
                 oni._check(lib.onilda_em_get_model(x._h, cur._h))      # D2H: new model
                 oni._check(lib.onilda_em_get_gamma(x._h, g_host))      # D2H: gamma
+                next_model()
                 th.join()
                 return out
 
@@ -1152,9 +1185,13 @@ def main():
                    "likelihood_first": liks[0], "likelihood_last": liks[-1], "sweeps_last_iter": int(sweeps),
                    "e2e_likelihood_last": e2e_liks[-1],
                    "word_steps_per_iter": [int(x) for x in word_steps],
-                   "estep_ms_note": "EM iterations warmup+1 .. warmup+steps of one run.  word_steps_per_iter = sum over documents of "
-                                    "entries x variational sweeps (all ranks), the E-step's unit of work: it grows as the topics "
-                                    "sharpen and more documents run towards the 20-sweep cap, and estep_ms follows it"}}
+                   "runs_finished_in_resident_leg": run_lengths,
+                   "estep_ms_note": "steps warmup+1 .. warmup+steps.  A run ends by the reference's own rule (settings.txt: em max "
+                                    "iter 20, i.e. 21 iterations, or convergence) and the next step is iteration 1 of a new run "
+                                    "from the same start model, so with steps + warmup > 21 the list wraps around.  "
+                                    "word_steps_per_iter = sum over documents of entries x variational sweeps (all ranks), the "
+                                    "E-step's unit of work: it grows as the topics sharpen and more documents run towards the "
+                                    "20-sweep cap, and estep_ms follows it"}}
     emit(line)
     if dist is not None:
         dist.barrier()
