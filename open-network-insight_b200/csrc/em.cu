@@ -41,6 +41,8 @@ struct onilda_em {
     // device buffers
     int64_t* d_offsets;
     int32_t *d_words, *d_counts, *d_totals, *d_order;
+    int32_t *d_order_dyn, *d_win_off;   // the order the bulk launch uses (re-bundled by the last sweep counts) and its windows
+    int num_windows, rebundle, sweeps_valid;
     double *d_log_beta_wk, *d_beta_scaled, *d_lbmax;
     double* d_ss;               // [(V + kTablePadRows)*kpad statistics | SS_TAIL scalars | kpad class_total]
     double* d_partial;
@@ -170,7 +172,7 @@ extern "C" void onilda_em_destroy(onilda_em* em)
 {
     if (!em) return;
     DeviceGuard g(em->device);
-    cudaFree(em->d_offsets); cudaFree(em->d_words); cudaFree(em->d_counts); cudaFree(em->d_totals); cudaFree(em->d_order);
+    cudaFree(em->d_offsets); cudaFree(em->d_words); cudaFree(em->d_counts); cudaFree(em->d_totals); cudaFree(em->d_order); cudaFree(em->d_order_dyn); cudaFree(em->d_win_off);
     cudaFree(em->d_log_beta_wk); cudaFree(em->d_beta_scaled); cudaFree(em->d_lbmax); cudaFree(em->d_ss);
     cudaFree(em->d_partial); cudaFree(em->d_phi); cudaFree(em->d_gamma);
     cudaFree(em->d_doc_lik); cudaFree(em->d_doc_ass); cudaFree(em->d_doc_sweeps); cudaFree(em->d_queue);
@@ -259,6 +261,7 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
     TRY(dev_alloc(&em->d_counts, (size_t)N));
     TRY(dev_alloc(&em->d_totals, (size_t)D));
     TRY(dev_alloc(&em->d_order, (size_t)D));
+    TRY(dev_alloc(&em->d_order_dyn, (size_t)D));
     // every table has kTablePadRows spare rows (kernels.cuh); beta_scaled and lbmax one more, the idle row
     const size_t table_pad = table + (size_t)kTablePadRows * lay.kpad;
     TRY(dev_alloc(&em->d_log_beta_wk, table_pad));
@@ -357,6 +360,33 @@ extern "C" int onilda_em_create(const onilda_corpus* c, int64_t doc_begin, int64
         if (D > 0) {
             TRYCUDA(cudaMemcpyAsync(em->d_totals, c->totals + doc_begin, sizeof(int32_t) * (size_t)D, cudaMemcpyHostToDevice, em->stream));
             TRYCUDA(cudaMemcpyAsync(em->d_order, order.data(), sizeof(int32_t) * (size_t)D, cudaMemcpyHostToDevice, em->stream));
+            TRYCUDA(cudaMemcpyAsync(em->d_order_dyn, order.data(), sizeof(int32_t) * (size_t)D, cudaMemcpyHostToDevice, em->stream));
+        }
+        // windows of the bulk part of the order for the re-bundling (mstep.cu): at most 2048 documents, the longest at
+        // most 1.1 times the shortest
+        std::vector<int32_t> win;
+        const char* env_rb = getenv("ONILDA_REBUNDLE");
+        em->rebundle = env_rb ? atoi(env_rb) : 1;
+        em->sweeps_valid = 0;
+        if (em->rebundle && D < ((int64_t)1 << 31)) {
+            int64_t at = em->num_long;
+            win.push_back((int32_t)at);
+            while (at < D) {
+                const int64_t first_len = off[(size_t)order[(size_t)at] + 1] - off[(size_t)order[(size_t)at]];
+                int64_t end = at + 1;
+                while (end < D && end - at < 2048) {
+                    const int64_t len = off[(size_t)order[(size_t)end] + 1] - off[(size_t)order[(size_t)end]];
+                    if (len * 11 < first_len * 10) break;
+                    end++;
+                }
+                win.push_back((int32_t)end);
+                at = end;
+            }
+        }
+        em->num_windows = win.empty() ? 0 : (int)win.size() - 1;
+        if (em->num_windows > 0) {
+            TRY(dev_alloc(&em->d_win_off, win.size()));
+            TRYCUDA(cudaMemcpyAsync(em->d_win_off, win.data(), sizeof(int32_t) * win.size(), cudaMemcpyHostToDevice, em->stream));
         }
         if (N > 0) {
             TRYCUDA(cudaMemcpyAsync(em->d_words, c->words + base, sizeof(int32_t) * (size_t)N, cudaMemcpyHostToDevice, em->stream));
@@ -409,6 +439,7 @@ extern "C" int onilda_em_reload_model(onilda_em* em, const onilda_model* m)
     em->likelihood_old = 0;
     em->converged = 1;
     em->estep_done = 0;
+    em->sweeps_valid = 0;      // the next E-step is iteration 1 of another run: its sweep counts are not these
     ONILDA_CUDA(cudaStreamSynchronize(em->stream));
     return ONILDA_OK;
 }
@@ -434,6 +465,13 @@ static int run_estep(onilda_em* em, bool accumulate)
     EStepArgs a;
     a.offsets = em->d_offsets; a.words = em->d_words; a.counts = em->d_counts; a.totals = em->d_totals;
     a.order = em->d_order;
+    // bundles of documents that stopped together in the last EM iteration (not after a reload: another run's sweeps)
+    if (em->num_windows > 0 && em->sweeps_valid) {
+        int rl = 0;
+        int rrc = launch_rebundle(em->d_order, em->d_win_off, em->num_windows, em->d_doc_sweeps, em->d_order_dyn, em->stream, &rl);
+        if (rrc != ONILDA_OK) return rrc;
+        l += rl;
+    }
     a.carveout_pct = em->num_long > 0 ? em->carveout_pct : 0;
     a.psi_tab = em->d_math_tab; a.exp_tab = em->d_math_tab + (size_t)6 * kPsiRows;
     a.beta_scaled = em->d_beta_scaled; a.lbmax = em->d_lbmax; a.num_topics = em->K; a.num_terms = em->V; a.idle_row = em->V + kTablePadRows; a.kstride = em->lay.kpad;
@@ -473,6 +511,7 @@ static int run_estep(onilda_em* em, bool accumulate)
             rc = launch_estep(em->long_group, b, em->sm_count, em->long_threads, em->long_smem, em->long_per_sm, em->stream, &l);
         if (rc != ONILDA_OK) return rc;
         a.order_begin = em->num_long; a.order_count = em->num_docs - em->num_long; a.queue = em->d_queue;
+        a.order = em->d_order_dyn;
         a.rare_paths = needs_rare_paths(em->bulk_max_total);
         rc = launch_estep(em->bulk_group, a, em->sm_count, em->bulk_threads, 0, em->bulk_per_sm, em->stream, &l, true);
         if (rc != ONILDA_OK) return rc;
@@ -504,6 +543,7 @@ static int run_estep(onilda_em* em, bool accumulate)
             ONILDA_CUDA(cudaEventRecord(em->ev_join, em->long_stream));
         }
         a.order_begin = em->num_long; a.order_count = em->num_docs - em->num_long; a.queue = em->d_queue;
+        a.order = em->d_order_dyn;
         a.rare_paths = needs_rare_paths(em->bulk_max_total);
         rc = launch_estep(em->bulk_group, a, em->sm_count, em->bulk_threads, 0, em->num_long > 0 ? em->bulk_per_sm : 0, em->stream, &l);
         if (rc != ONILDA_OK) return rc;
@@ -516,6 +556,7 @@ static int run_estep(onilda_em* em, bool accumulate)
     ONILDA_CUDA(cudaEventRecord(em->ev1, em->stream));
     em->launches = l;
     em->estep_done = 1;
+    em->sweeps_valid = 1;
     return ONILDA_OK;
 }
 

@@ -90,6 +90,8 @@ int launch_estep_long(const EStepArgs& args, int sm_count, int block_threads, in
 // M-step and table kernels (mstep.cu)
 int launch_tables_from_log_beta(const double* log_beta_kv, int K, int V, const TopicLayout& lay, double* log_beta_wk,
                                 double* beta_scaled, double* lbmax, cudaStream_t stream, int* launches);
+int launch_rebundle(const int32_t* order_static, const int32_t* win_off, int num_windows, const int32_t* doc_sweeps,
+                    int32_t* order_out, cudaStream_t stream, int* launches);
 int launch_reduce_doc_stats(const double* doc_lik, const double* doc_alpha_ss, const int64_t* offsets, const int32_t* doc_sweeps,
                             int64_t num_docs, double* partial,
                             double* ss_tail, cudaStream_t stream, int* launches);

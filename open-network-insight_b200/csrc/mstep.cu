@@ -146,6 +146,66 @@ __global__ void doc_final_kernel(const double* __restrict__ partial, int nblocks
     tail[SS_STEPS] = w;
 }
 
+// Re-bundling of the bulk launch's documents.  A warp of the general kernel sweeps its documents together until the
+// slowest has converged; the sweeps a document took in the last EM iteration predict the next ones well (correlation
+// 0.7-0.95 at cfg 2).  Inside windows of the length-sorted order (at most 2048 documents of nearly the same length,
+// boundaries from the host) the documents are put in the order of their last sweep counts, most first, stably: bundles
+// then hold documents that stop together.  One warp per window; a window is walked 32 positions at a time.
+__global__ void __launch_bounds__(32) rebundle_kernel(const int32_t* __restrict__ order_static, const int32_t* __restrict__ win_off,
+                                                      const int32_t* __restrict__ doc_sweeps, int32_t* __restrict__ order_out)
+{
+    constexpr int kKeys = 64;
+    __shared__ unsigned int cursor[kKeys];
+    const int lane = threadIdx.x;
+    const int b = win_off[blockIdx.x], e = win_off[blockIdx.x + 1];
+    for (int k = lane; k < kKeys; k += 32) cursor[k] = 0;
+    __syncwarp();
+    // key 0 = most sweeps
+    auto key_of = [&](int pos) {
+        const int s = doc_sweeps[order_static[pos]];
+        return kKeys - 1 - (s < 0 ? 0 : (s > kKeys - 1 ? kKeys - 1 : s));
+    };
+    for (int p = b + lane; p < e; p += 32) atomicAdd(&cursor[key_of(p)], 1u);
+    __syncwarp();
+    // exclusive scan of the 64 counts: two per lane
+    unsigned int c0 = cursor[2 * lane], c1 = cursor[2 * lane + 1], inc = c0 + c1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    __syncwarp();
+    cursor[2 * lane] = inc - c0 - c1;
+    cursor[2 * lane + 1] = inc - c1;
+    __syncwarp();
+    const unsigned int lt = (1u << lane) - 1u;
+    for (int p0 = b; p0 < e; p0 += 32) {
+        const int p = p0 + lane;
+        const bool live = p < e;
+        const int doc = live ? order_static[p] : 0;
+        const int k = live ? key_of(p) : kKeys;          // dead lanes match only each other
+        const unsigned int peers = __match_any_sync(0xffffffffu, k);
+        unsigned int base = 0;
+        if (live) base = cursor[k];
+        __syncwarp();
+        if (live) {
+            order_out[b + base + __popc(peers & lt)] = doc;
+            if ((peers & lt) == 0) cursor[k] = base + __popc(peers);
+        }
+        __syncwarp();
+    }
+}
+
+int launch_rebundle(const int32_t* order_static, const int32_t* win_off, int num_windows, const int32_t* doc_sweeps,
+                    int32_t* order_out, cudaStream_t stream, int* launches)
+{
+    if (num_windows <= 0) return ONILDA_OK;
+    rebundle_kernel<<<(unsigned)num_windows, 32, 0, stream>>>(order_static, win_off, doc_sweeps, order_out);
+    ONILDA_CUDA(cudaGetLastError());
+    if (launches) *launches += 1;
+    return ONILDA_OK;
+}
+
 int mstep_partial_doubles(int V, const TopicLayout& lay, int64_t num_docs)
 {
     (void)V; (void)num_docs;
