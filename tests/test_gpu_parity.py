@@ -106,6 +106,25 @@ def test_long_document_path(oni, oracle, group, case, monkeypatch):
     em.close()
 
 
+def test_rebundling_changes_no_result(oni, monkeypatch):
+    """From the second E-step of a run on the bulk launch takes its documents in the order of their last sweep counts
+    (rebundle_kernel): which documents share a warp must not change any document's result."""
+    d, c, m, st = load_case(oni, "k20")
+    out = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("ONILDA_REBUNDLE", flag)
+        em = oni.EM(c, m, st)
+        liks = [em.iterate()[0] for _ in range(4)]
+        em.estep()
+        out[flag] = (np.array(liks), em.gamma().copy(), em.doc_sweeps().copy(), em.doc_likelihood().copy())
+        em.mstep()
+        em.close()
+    assert np.allclose(out["0"][0], out["1"][0], rtol=1e-12, atol=0.0)
+    assert rel_err(out["1"][1], out["0"][1], 1e-9) < 1e-9
+    assert np.mean(out["0"][2] != out["1"][2]) <= 0.01      # a convergence test within rounding of its threshold may flip
+    assert rel_err(out["1"][3], out["0"][3], 1e-9) < 1e-9
+
+
 def test_reload_in_two_halves_on_two_handles(oni):
     """onilda_em_reload_corpus + onilda_em_reload_model are onilda_em_reload; a second handle may take its corpus copy
     from another thread while the first iterates (what bench.py's end-to-end leg does)."""
